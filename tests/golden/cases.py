@@ -1,0 +1,30 @@
+"""Case tables shared by gen_golden.py (build container) and the tests."""
+VQ_CASES = {
+    # north_star configuration: Euclidean, 1 head, EMA decay 0.8
+    "vq_euclid_ema": dict(dim=32, codebook_size=24, decay=0.8, commitment_weight=1.0),
+    "vq_euclid_eval": dict(dim=32, codebook_size=24, _eval=True),
+    "vq_cosine_ema": dict(dim=32, codebook_size=24, use_cosine_sim=True, decay=0.9),
+    # shipped configuration (pretrain.py:105-119), scaled down
+    "vq_shipped": dict(dim=32, codebook_size=16, codebook_dim=32, heads=4,
+                       separate_codebook_per_head=True, decay=0.8, commitment_weight=10,
+                       use_cosine_sim=True, orthogonal_reg_weight=1, orthogonal_reg_max_codes=8,
+                       orthogonal_reg_active_codes_only=False, kmeans_init=False,
+                       ema_update=False),
+    "vq_shared_heads": dict(dim=32, codebook_size=16, codebook_dim=8, heads=4,
+                            separate_codebook_per_head=False),
+    "vq_learnable": dict(dim=32, codebook_size=16, ema_update=False, learnable_codebook=True,
+                         commitment_weight=0.25),
+    # exact duplicate code rows -> ties -> lower index must win (vq.py:79)
+    "vq_ties": dict(dim=16, codebook_size=8, _dup=True),
+}
+
+
+
+ENC_CASES = {
+    "enc_sage": dict(backbone="sage", normalize="batch", in_dim=20, hid=24, layers=2, xe=False),
+    "enc_sage_xe": dict(backbone="sage", normalize="none", in_dim=24, hid=24, layers=2, xe=True),
+    "enc_gcn": dict(backbone="gcn", normalize="none", in_dim=20, hid=24, layers=2, xe=False),
+    "enc_gin": dict(backbone="gin", normalize="batch", in_dim=20, hid=24, layers=3, xe=False),
+    "enc_moe": dict(backbone="sage", normalize="none", in_dim=24, hid=24, layers=2, xe=False,
+                    moe=True),
+}

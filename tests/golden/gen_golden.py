@@ -1,0 +1,105 @@
+"""Generates the golden fixtures in this directory by executing the UNMODIFIED reference code
+from /root/reference (only available in the build container, never on the GPU box):
+
+* vq_*.npz  -- /root/reference/STEM-GNN/model/vq.py VectorQuantize (imports torch + einops only)
+* enc_*.npz -- /root/reference/STEM-GNN/model/encoder.py Encoder, executed on oracle/pyg_shim
+               (torch_geometric / torch_scatter are not installable here; see oracle/__init__.py)
+
+Run:  python tests/golden/gen_golden.py      (CPU, fp32, seeded; a few seconds)
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+OUT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle", "pyg_shim"))
+sys.path.insert(0, "/root/reference/STEM-GNN")
+warnings.filterwarnings("ignore")
+
+from model.vq import VectorQuantize  # noqa: E402  (the reference's own module)
+from model.encoder import Encoder    # noqa: E402  (the reference's own module, on the shim)
+
+from tests.golden.cases import ENC_CASES, VQ_CASES  # noqa: E402
+
+
+def gen_vq(name, cfg):
+    cfg = dict(cfg)
+    is_eval, dup = cfg.pop("_eval", False), cfg.pop("_dup", False)
+    torch.manual_seed(0)
+    vq = VectorQuantize(**cfg)
+    vq.train(not is_eval)
+    if dup:
+        with torch.no_grad():
+            vq._codebook.embed[0, 5] = vq._codebook.embed[0, 2]
+            vq._codebook.embed[0, 7] = vq._codebook.embed[0, 2]
+    n = 200
+    x = torch.randn(n, cfg["dim"])
+    if dup:
+        x[:40] = vq._codebook.embed[0, 2] + 0.01 * torch.randn(40, cfg["dim"])
+    x.requires_grad_(True)
+    before = {k: v.detach().clone().numpy() for k, v in vq.state_dict().items()}
+    torch.manual_seed(1)  # fixes the randperm inside the orthogonal loss (vq.py:1024)
+    q, ind, loss, oq = vq(x)
+    out = dict(x=x.detach().numpy(), quantize=q.detach().numpy(), embed_ind=ind.numpy(),
+               loss=loss.detach().numpy(), orig_quantize=oq.detach().numpy())
+    if not is_eval:
+        g = torch.randn(q.shape, generator=torch.Generator().manual_seed(2))
+        ((q * g).sum() + loss.sum()).backward()
+        out["g_quantize"] = g.numpy()
+        out["g_x"] = x.grad.numpy()
+        emb = vq._codebook.embed
+        if isinstance(emb, nn.Parameter) and emb.grad is not None:
+            out["g_embed"] = emb.grad.numpy()
+    for k, v in before.items():
+        out["before." + k] = v
+    for k, v in vq.state_dict().items():
+        out["after." + k] = v.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(name, {k: v.shape for k, v in out.items() if not k.startswith(("before", "after"))})
+
+
+def gen_enc(name, c):
+    torch.manual_seed(3)
+    n, e = 96, 400
+    enc = Encoder(c["in_dim"], c["hid"], nn.ReLU, c["layers"], backbone=c["backbone"],
+                  normalize=c["normalize"], dropout=0.0, moe=c.get("moe", False),
+                  num_experts=3, moe_layers="all")
+    enc.train(not c.get("moe", False))  # MoE: eval branch (softmax gate) is deterministic
+    x = torch.randn(n, c["in_dim"], requires_grad=True)
+    ei = torch.randint(0, n, (2, e))
+    ei[:, :8] = ei[:, 8:16]          # duplicate edges
+    ei[1, 16:24] = ei[0, 16:24]      # self loops
+    ei[1][ei[1] == 5] = 6            # node 5 has no in-edges
+    ei[0][ei[0] == 7] = 8            # node 7 has no out-edges
+    xe = None
+    if c["xe"]:
+        table = torch.randn(3, c["in_dim"])
+        xe = table[torch.randint(0, 3, (e,))]
+    before = {k: v.detach().clone().numpy() for k, v in enc.state_dict().items()}
+    z = enc(x, ei, xe)
+    g = torch.randn(z.shape, generator=torch.Generator().manual_seed(4))
+    (z * g).sum().backward()
+    out = dict(x=x.detach().numpy(), edge_index=ei.numpy(), z=z.detach().numpy(), g_z=g.numpy(),
+               g_x=x.grad.numpy())
+    if xe is not None:
+        out["edge_attr"] = xe.numpy()
+    for k, v in before.items():
+        out["state." + k] = v
+    for k, p in enc.named_parameters():
+        if p.grad is not None:
+            out["grad." + k] = p.grad.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(name, z.shape, len(before), "state tensors")
+
+
+if __name__ == "__main__":
+    for k, v in VQ_CASES.items():
+        gen_vq(k, v)
+    for k, v in ENC_CASES.items():
+        gen_enc(k, v)

@@ -1,0 +1,150 @@
+"""CPU: the oracle restatements against the golden vectors produced by the reference's own
+code (tests/golden/gen_golden.py), and the torch oracle against the sequential C oracle."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+from oracle import c_agg, graph_ref
+from oracle import propagate_ref as P
+from oracle.encoder_ref import EncoderRef
+from oracle.vq_ref import vq_forward_ref
+from tests.golden.cases import ENC_CASES, VQ_CASES
+
+
+def _load(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name + ".npz")))
+
+
+def vq_kwargs(cfg):
+    """Reference ctor kwargs (vq.py:693-728) -> oracle.vq_forward_ref kwargs."""
+    return dict(heads=cfg.get("heads", 1),
+                separate_codebook_per_head=cfg.get("separate_codebook_per_head", False),
+                cosine=cfg.get("use_cosine_sim", False), ema_update=cfg.get("ema_update", True),
+                decay=cfg.get("decay", 0.8), eps=cfg.get("eps", 1e-5),
+                commitment_weight=cfg.get("commitment_weight", 1.0),
+                learnable_codebook=cfg.get("learnable_codebook", False),
+                orthogonal_reg_weight=cfg.get("orthogonal_reg_weight", 0.0),
+                orthogonal_reg_max_codes=cfg.get("orthogonal_reg_max_codes"))
+
+
+@pytest.mark.parametrize("name", sorted(VQ_CASES))
+def test_vq_oracle_matches_reference_golden(golden_dir, name):
+    cfg = dict(VQ_CASES[name])
+    g = _load(golden_dir, name)
+    training = not cfg.pop("_eval", False)
+    cfg.pop("_dup", None)
+    kw = vq_kwargs(cfg)
+    state = {k: torch.from_numpy(g["before._codebook." + k].copy())
+             for k in ("embed", "embed_avg", "cluster_size")}
+    if "g_embed" in g:
+        state["embed"].requires_grad_(True)
+    pin = pout = None
+    if "before.project_in.weight" in g:
+        pin = nn.Linear(*g["before.project_in.weight"].shape[::-1])
+        pout = nn.Linear(*g["before.project_out.weight"].shape[::-1])
+        with torch.no_grad():
+            pin.weight.copy_(torch.from_numpy(g["before.project_in.weight"]))
+            pin.bias.copy_(torch.from_numpy(g["before.project_in.bias"]))
+            pout.weight.copy_(torch.from_numpy(g["before.project_out.weight"]))
+            pout.bias.copy_(torch.from_numpy(g["before.project_out.bias"]))
+    x = torch.from_numpy(g["x"].copy()).requires_grad_(training)
+    torch.manual_seed(1)
+    q, ind, loss, oq = vq_forward_ref(x, state, training=training, project_in=pin,
+                                      project_out=pout, **kw)
+    assert ind.dtype == torch.int64 and tuple(ind.shape) == g["embed_ind"].shape
+    assert np.array_equal(ind.numpy(), g["embed_ind"])
+    np.testing.assert_allclose(q.detach().numpy(), g["quantize"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(oq.detach().numpy(), g["orig_quantize"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-7)
+    for k in ("embed", "embed_avg", "cluster_size"):
+        np.testing.assert_allclose(state[k].detach().numpy(), g["after._codebook." + k],
+                                   rtol=1e-5, atol=1e-6)
+    if training:
+        ((q * torch.from_numpy(g["g_quantize"])).sum() + loss.sum()).backward()
+        np.testing.assert_allclose(x.grad.numpy(), g["g_x"], rtol=1e-5, atol=1e-6)
+        if "g_embed" in g:
+            np.testing.assert_allclose(state["embed"].grad.numpy(), g["g_embed"],
+                                       rtol=1e-5, atol=1e-6)
+
+
+def test_vq_ties_lower_index_wins(golden_dir):
+    g = _load(golden_dir, "vq_ties")
+    ind = g["embed_ind"]
+    assert (ind[:40] == 2).all() and not np.isin(ind, [5, 7]).any()
+
+
+@pytest.mark.parametrize("name", sorted(ENC_CASES))
+def test_encoder_oracle_matches_reference_golden(golden_dir, name):
+    c = ENC_CASES[name]
+    g = _load(golden_dir, name)
+    enc = EncoderRef(c["in_dim"], c["hid"], nn.ReLU, c["layers"], backbone=c["backbone"],
+                     normalize=c["normalize"], dropout=0.0, moe=c.get("moe", False),
+                     num_experts=3, moe_layers="all")
+    sd = {k[len("state."):]: torch.from_numpy(v.copy()) for k, v in g.items()
+          if k.startswith("state.")}
+    assert set(sd) == set(enc.state_dict()), "state_dict keys must match the reference"
+    enc.load_state_dict(sd)
+    enc.train(not c.get("moe", False))
+    x = torch.from_numpy(g["x"].copy()).requires_grad_(True)
+    ei = torch.from_numpy(g["edge_index"])
+    xe = torch.from_numpy(g["edge_attr"]) if "edge_attr" in g else None
+    z = enc(x, ei, xe)
+    np.testing.assert_array_equal(z.detach().numpy(), g["z"])  # same ops, same order: bit-exact
+    (z * torch.from_numpy(g["g_z"])).sum().backward()
+    np.testing.assert_array_equal(x.grad.numpy(), g["g_x"])
+    for k, p in enc.named_parameters():
+        if "grad." + k in g:
+            np.testing.assert_allclose(p.grad.numpy(), g["grad." + k], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("with_xe", [False, True])
+@pytest.mark.parametrize("reduce", ["mean", "sum"])
+def test_torch_oracle_is_sequential_in_edge_order(with_xe, reduce):
+    """scatter_add_/index_add_ on CPU == add the messages of a row one by one in original edge
+    order (the C oracle): bit-for-bit, forward and backward."""
+    gen = torch.Generator().manual_seed(11)
+    n, e, f = 300, 4000, 37
+    x = torch.randn(n, f, generator=gen, requires_grad=True)
+    ei = torch.randint(0, n, (2, e), generator=gen)
+    ei[1, :600] = 3                                            # a hub row
+    xe = torch.randn(e, f, generator=gen) if with_xe else None
+    out = P.sage_propagate_ref(x, ei, xe, n, reduce)
+    ref = c_agg.aggregate_fwd(ei.numpy(), x.detach().numpy(), n, None if xe is None else xe.numpy(),
+                              act=1, reduce=int(reduce == "mean"))
+    np.testing.assert_array_equal(out.detach().numpy(), ref)
+    go = torch.randn(n, f, generator=gen)
+    out.backward(go)
+    gref = c_agg.aggregate_bwd(ei.numpy(), x.detach().numpy(), go.numpy(),
+                               None if xe is None else xe.numpy(), act=1,
+                               reduce=int(reduce == "mean"))
+    np.testing.assert_array_equal(x.grad.numpy(), gref)
+
+
+def test_gcn_oracle_vs_c():
+    gen = torch.Generator().manual_seed(12)
+    n, e, f = 200, 1500, 19
+    xw = torch.randn(n, f, generator=gen, requires_grad=True)
+    ei = torch.randint(0, n, (2, e), generator=gen)
+    out = P.gcn_propagate_ref(xw, ei, n)
+    ei2, w = P.gcn_norm_ref(ei, n)
+    ref = c_agg.aggregate_fwd(ei2.numpy(), xw.detach().numpy(), n, None, w.numpy(), act=0, reduce=0)
+    np.testing.assert_array_equal(out.detach().numpy(), ref)
+    assert np.array_equal(ei2.numpy(), graph_ref.add_remaining_self_loops_ref(ei.numpy(), n))
+
+
+def test_csr_ref_properties():
+    rng = np.random.default_rng(0)
+    n, e = 50, 400
+    ei = rng.integers(0, n, (2, e))
+    for by in (0, 1):
+        rowptr, col, perm, deg = graph_ref.csr_build_ref(ei, n, by)
+        assert rowptr[0] == 0 and rowptr[-1] == e and (np.diff(rowptr) == deg).all()
+        assert sorted(perm.tolist()) == list(range(e))
+        for i in range(n):
+            seg = perm[rowptr[i]:rowptr[i + 1]]
+            assert (ei[by][seg] == i).all() and (np.diff(seg) > 0).all()  # stable
+            assert (col[rowptr[i]:rowptr[i + 1]] == ei[1 - by][seg]).all()
