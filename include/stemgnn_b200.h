@@ -1,0 +1,161 @@
+/* stemgnn_b200.h -- C-ABI of the B200-native STEM-GNN encoder/VQ hot path.
+ *
+ * The reference (GXG-CS/STEM-GNN) is pure Python; the "FFI" it binds for this path is the
+ * ATen / torch_scatter operator layer underneath torch_geometric.  Each entry point below
+ * replaces one such operator sequence, cited as reference file:line (paths relative to
+ * /root/reference/STEM-GNN).  Conventions:
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - the caller owns all memory (outputs and workspace); kernels are stream-ordered on
+ *     `stream`, never synchronise, never allocate;
+ *   - return value 0 on success, a negative STEMGNN_E* code otherwise;
+ *     stemgnn_last_error() returns a thread-local message;
+ *   - row-major contiguous fp32 features; int64 edge_index [2,E] as the reference passes it;
+ *     the internal CSR uses int32 (E, N < 2^31).
+ */
+#ifndef STEMGNN_B200_H
+#define STEMGNN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* stemgnn_stream_t; /* cudaStream_t */
+
+#define STEMGNN_OK 0
+#define STEMGNN_EINVAL (-1)
+#define STEMGNN_ENOMEM_WS (-2)
+#define STEMGNN_ECUDA (-3)
+#define STEMGNN_EUNSUPPORTED (-4)
+
+const char* stemgnn_last_error(void);
+int stemgnn_abi_version(void);
+
+/* ------------------------------------------------------------------ K0: graph structure
+ * Replaces the implicit COO scatter order of MessagePassing.propagate (model/encoder.py:82)
+ * and scatter_mean (model/encoder.py:124) with an explicit CSR grouped by
+ * edge_index[group_row] using a STABLE sort (ties keep original edge order), which is the
+ * order scatter_add_ sums in.  Outputs: rowptr[N+1], col[E] (the other endpoint), perm[E]
+ * (original edge id per slot), cnt[N] = float(max(deg,1)) (MeanAggregation's clamped count). */
+int stemgnn_csr_build_workspace(int64_t num_edges, int64_t num_nodes, size_t* bytes_host);
+int stemgnn_csr_build(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes,
+                      int group_row, int32_t* rowptr, int32_t* col, int32_t* perm, float* cnt,
+                      void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+
+/* GCNConv.gcn_norm (torch_geometric 2.3.0, called from model/encoder.py:197): given the
+ * edge list WITH remaining self loops already appended (edge_index_sl; the host side builds
+ * it with integer mask/concat ops) and the CSR rowptr grouped by destination,
+ * deg[i] = float(in-degree incl. self loop), dis = deg^-1/2 (inf -> 0),
+ * w[e] = dis[src] * 1.0f * dis[dst] in original edge order (two separate multiplies). */
+int stemgnn_gcn_edge_weight(const int64_t* edge_index_sl, int64_t num_edges, int64_t num_nodes,
+                            const int32_t* rowptr_by_dst, float* w_out, stemgnn_stream_t stream);
+
+/* ------------------------------------------------------------------ K1/K2: aggregation
+ * Forward: replaces index_select + message + scatter_add_ + count/clamp/div
+ * (model/encoder.py:82,94-97; PyG MeanAggregation; torch_scatter.scatter_mean at :124; GCN/GIN
+ * sums at :197/:199).  For every row r of the CSR:
+ *     acc = 0;  for slots p in [rowptr[r], rowptr[r+1]) in order:
+ *         m = x[col[p]] (+ xe[perm[p]] | + table[etype[perm[p]]]);  if act==RELU m = max(m,0);
+ *         if w: m = w[perm[p]] * m (separate rounding);  acc = acc + m
+ *     out[r] = reduce==MEAN ? acc / cnt[r] : acc
+ * Backward (same entry point on the TRANSPOSED structure, mode flags below):
+ *     g_x[r] = sum_p mask(r,p) * ( g_out[col[p]] / cnt_col[col[p]] ) [* w[perm[p]]]
+ *     mask = (x[r] (+ xe[perm[p]]) > 0) when act==RELU
+ * which is autograd's index_add_ of the masked, pre-divided upstream gradient in edge order. */
+#define STEMGNN_REDUCE_SUM 0
+#define STEMGNN_REDUCE_MEAN 1
+#define STEMGNN_ACT_NONE 0
+#define STEMGNN_ACT_RELU 1
+
+typedef struct {
+    const int32_t* rowptr;   /* [n_rows+1] */
+    const int32_t* col;      /* [E] gathered-row index per slot */
+    const int32_t* perm;     /* [E] original edge id per slot (needed for xe/etype/w) or NULL */
+    int64_t n_rows;          /* rows produced */
+    int64_t n_gather_rows;   /* rows of the gathered matrix (bounds) */
+    int64_t num_edges;
+    int64_t feat;            /* F */
+    const float* gathered;   /* fwd: x [n_gather_rows,F]; bwd: g_out */
+    const float* row_cnt;    /* fwd MEAN: cnt[n_rows]; else NULL */
+    const float* gather_cnt; /* bwd MEAN: cnt over gathered rows (divide each gathered row); else NULL */
+    const float* edge_feat;  /* dense xe [E,F] in ORIGINAL edge order, or NULL */
+    const float* type_table; /* [T,F] or NULL (used with edge_type) */
+    const int32_t* edge_type;/* [E] in original edge order or NULL */
+    const float* edge_weight;/* [E] in original edge order or NULL */
+    const float* row_x;      /* bwd RELU: x [n_rows,F] whose sign (plus xe) gives the mask; else NULL */
+    int act;                 /* STEMGNN_ACT_* */
+    int backward;            /* 0 fwd, 1 bwd */
+    float* out;              /* [n_rows,F] */
+} stemgnn_aggregate_args;
+
+int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t stream);
+
+/* ------------------------------------------------------------------ K3: VQ assignment
+ * Replaces dist = -cdist / einsum, argmax, one_hot, one_hot @ embed (or the eval gather) and
+ * the MSE commitment partial (model/vq.py:472-482, 650-659, 79-80, 1007), and fuses the head
+ * rearranges 'b n (h d) -> h b n d' / 'h b n d -> b n (h d)' / 'h b n -> b n h'
+ * (model/vq.py:885-887, 971, 1034) through strides:
+ *   element (h, m, d) of x        is x       [m*x_row_stride + h*x_head_stride + d]
+ *   element (h, m, d) of quantize is quantize[m*q_row_stride + h*q_head_stride + d]
+ *   element (h, m)    of ind      is ind     [m*ind_row_stride + h*ind_head_stride]
+ * embed is [embed_heads, K, D] contiguous with embed_heads in {1, heads}.
+ * metric 0: euclidean, argmax of -sqrt(clamp((x2 + e2) + (-2 x.e), 0)), first index on ties;
+ * metric 1: dot / cosine, argmax of x.e (the caller l2-normalises, model/vq.py:891).
+ * sq_err[h] (fp64) = sum over (m,d) of (quantize - x)^2, reduced in a fixed order.
+ * path 0 = auto, 1 = exact fp32 CUDA-core scan, 2 = tcgen05 bf16 GEMM + fp32 rescoring of every
+ * candidate inside a rigorous bf16 error band (same answer as path 1 up to fp32 dot-product
+ * summation order).  stats (optional, int64[4], device): rows whose winner came from the
+ * rescoring set (>1 candidate), rows that fell back to a full fp32 scan, 0, 0. */
+typedef struct {
+    const float* x; int64_t x_row_stride, x_head_stride;
+    const float* embed;
+    int64_t heads, embed_heads, rows, codes, dim;
+    int metric, path;
+    int64_t* ind; int64_t ind_row_stride, ind_head_stride;
+    float* quantize; int64_t q_row_stride, q_head_stride;
+    double* sq_err;   /* [heads] or NULL */
+    int64_t* stats;   /* [4] or NULL */
+} stemgnn_vq_assign_args;
+
+int stemgnn_vq_assign_workspace(const stemgnn_vq_assign_args* args_host, size_t* bytes_host);
+int stemgnn_vq_assign(const stemgnn_vq_assign_args* args_host, void* workspace,
+                      size_t workspace_bytes, stemgnn_stream_t stream);
+
+/* backward of straight-through + commitment (model/vq.py:937,1007-1009), elementwise over
+ * `numel` contiguous floats: g_x = g_q + g_loss[0] * coef * (x - q), coef = 2*w/numel.
+ * g_q may be NULL (treated as 0); g_loss may be NULL (treated as 0). */
+int stemgnn_vq_backward(const float* g_q, const float* x, const float* q, const float* g_loss,
+                        float coef, int64_t numel, float* g_x, stemgnn_stream_t stream);
+
+/* ------------------------------------------------------------------ K4: EMA statistics
+ * Replaces onehot.sum(1) and einsum('h n d, h n c -> h c d') (model/vq.py:492,497 / 665,670):
+ * counts [embed_heads,K] fp32 and sums [embed_heads,K,D] fp32.  Deterministic: rows are
+ * stable-sorted by code, each code's rows are added in row order inside fixed-size chunks and
+ * the chunk partials are combined in a fixed order.  With embed_heads==1 and heads>1 all heads
+ * feed the shared codebook in (row, head) order like '1 (b h) n d'.  x / ind use the same
+ * strides as stemgnn_vq_assign.  The all-reduce of [counts|sums] (model/vq.py:494,499) sits
+ * between this call and stemgnn_vq_ema_apply. */
+typedef struct {
+    const float* x; int64_t x_row_stride, x_head_stride;
+    const int64_t* ind; int64_t ind_row_stride, ind_head_stride;
+    int64_t heads, embed_heads, rows, codes, dim;
+    float* counts; float* sums;
+} stemgnn_vq_code_stats_args;
+
+int stemgnn_vq_code_stats_workspace(const stemgnn_vq_code_stats_args* args_host, size_t* bytes_host);
+int stemgnn_vq_code_stats(const stemgnn_vq_code_stats_args* args_host, void* workspace,
+                          size_t workspace_bytes, stemgnn_stream_t stream);
+
+/* lerp_ + laplace smoothing + divide (+ double l2norm for cosine), model/vq.py:495-506 /
+ * 668-681, 40-46, 102-104.  Updates cluster_size [Hc,K], embed_avg [Hc,K,D], embed in place. */
+int stemgnn_vq_ema_apply(const float* counts, const float* sums, int64_t embed_heads,
+                         int64_t codes, int64_t dim, float decay, float eps, int cosine,
+                         float* cluster_size, float* embed_avg, float* embed,
+                         stemgnn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STEMGNN_B200_H */

@@ -1,0 +1,217 @@
+// k3_vq_simt.cu -- exact fp32 CUDA-core pieces of the VQ assignment (K3 path 1) and the
+// gather / commitment-partial / backward kernels shared with the tcgen05 path (k3_vq_tc.cu).
+//
+// Replaces model/vq.py:472-482 (Euclidean) / 650-659 (cosine): dist, argmax (first index on
+// ties, vq.py:79), quantize = embed[ind]; vq.py:1007 mse partial; vq.py:937 straight-through.
+// The N x K distance matrix and the one-hot are never materialised.
+#include "k3_vq_common.cuh"
+
+namespace stemgnn {
+
+// ---- squared row norms: out[h*rows + m] = sum_d v(h,m,d)^2, one warp per row ------------------
+__global__ void vq_sqnorm_kernel(const float* __restrict__ v, int64_t rows, int64_t heads, int D,
+                                 int64_t row_stride, int64_t head_stride, float* __restrict__ out) {
+    int64_t gw = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= rows * heads) return;
+    int64_t h = gw / rows, m = gw - h * rows;
+    const float* p = v + m * row_stride + h * head_stride;
+    float s = 0.f;
+    for (int d = lane_id(); d < D; d += 32) { float t = __ldg(p + d); s = fmaf(t, t, s); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane_id() == 0) out[gw] = s;
+}
+
+// ---- exact scan: 64 rows x all codes per CTA, 4x4 register tile per thread --------------------
+constexpr int SC_TM = 64, SC_TN = 64, SC_DK = 32;
+
+__global__ void __launch_bounds__(256)
+vq_scan_kernel(VqView q, const float* __restrict__ x2, const float* __restrict__ e2,
+               const int32_t* __restrict__ row_list, const int32_t* __restrict__ row_count,
+               int32_t* __restrict__ best_out) {
+    // row_list == NULL: CTA b handles rows [64b, 64b+64) of head blockIdx.y.
+    // row_list != NULL: entries are flat ids h*rows+m; *row_count of them are valid.
+    __shared__ float Xs[SC_DK][SC_TM + 1];
+    __shared__ float Es[SC_DK][SC_TN + 1];
+    __shared__ float red_s[SC_TM][17];
+    __shared__ int red_i[SC_TM][17];
+    __shared__ int64_t row_base[SC_TM];   // element offset of the row in x, or -1
+    __shared__ int row_flat[SC_TM];
+
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    int64_t total = row_list ? (int64_t)*row_count : q.rows;
+    int64_t r0 = (int64_t)blockIdx.x * SC_TM;
+    if (r0 >= total) return;
+    if (tid < SC_TM) {
+        int64_t r = r0 + tid;
+        int64_t flat = -1;
+        if (r < total) flat = row_list ? (int64_t)row_list[r] : (int64_t)blockIdx.y * q.rows + r;
+        row_flat[tid] = (int)flat;
+        if (flat >= 0) {
+            int64_t h = flat / q.rows, m = flat - h * q.rows;
+            row_base[tid] = m * q.x_row_stride + h * q.x_head_stride;
+        } else row_base[tid] = -1;
+    }
+    __syncthreads();
+    // all rows of one CTA share a head only when row_list == NULL; with a row list the head
+    // can differ per row, so the codebook head is resolved per row when embed_heads > 1.
+    const int D = q.D, K = q.K;
+    float best_s[4];
+    int best_i[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { best_s[i] = -INFINITY; best_i[i] = 0; }
+
+    // With a row list and per-head codebooks, process one head at a time (rare fallback path).
+    const int n_head_pass = (row_list && q.embed_heads > 1) ? (int)q.heads : 1;
+    for (int hp = 0; hp < n_head_pass; ++hp) {
+        int64_t eh;
+        if (q.embed_heads == 1) eh = 0;
+        else eh = row_list ? hp : blockIdx.y;
+        const float* E = q.embed + eh * (int64_t)K * D;
+        const float* e2h = e2 + eh * (int64_t)K;
+        for (int c0 = 0; c0 < K; c0 += SC_TN) {
+            float acc[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+            for (int d0 = 0; d0 < D; d0 += SC_DK) {
+                const int k = tid & 31, rr = tid >> 5;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    int r = rr + 8 * i;
+                    int64_t rb = row_base[r];
+                    Xs[k][r] = (rb >= 0 && d0 + k < D) ? __ldg(q.x + rb + d0 + k) : 0.f;
+                    int c = c0 + r;
+                    Es[k][r] = (c < K && d0 + k < D) ? __ldg(E + (int64_t)c * D + d0 + k) : 0.f;
+                }
+                __syncthreads();
+#pragma unroll 8
+                for (int kk = 0; kk < SC_DK; ++kk) {
+                    float a[4], b[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { a[i] = Xs[kk][ty * 4 + i]; b[i] = Es[kk][tx * 4 + i]; }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+                }
+                __syncthreads();
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                int flat = row_flat[ty * 4 + i];
+                if (flat < 0) continue;
+                if (n_head_pass > 1 && flat / q.rows != hp) continue;
+                float xx = q.metric == 0 ? x2[flat] : 0.f;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    int c = c0 + tx * 4 + j;
+                    if (c >= K) continue;
+                    float s = vq_score(q.metric, xx, e2h[c], acc[i][j]);
+                    if (s > best_s[i]) { best_s[i] = s; best_i[i] = c; }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { red_s[ty * 4 + i][tx] = best_s[i]; red_i[ty * 4 + i][tx] = best_i[i]; }
+    __syncthreads();
+    if (tid < SC_TM && row_flat[tid] >= 0) {
+        float bs = red_s[tid][0];
+        int bi = red_i[tid][0];
+#pragma unroll
+        for (int t = 1; t < 16; ++t) {
+            float s = red_s[tid][t];
+            int i2 = red_i[tid][t];
+            if (s > bs || (s == bs && i2 < bi)) { bs = s; bi = i2; }
+        }
+        best_out[row_flat[tid]] = bi;
+    }
+}
+
+// ---- gather + commitment partial: one warp per (head,row) --------------------------------------
+// quantize(h,m,:) = embed[eh, best, :]; ind(h,m) = best; partials[h*nblk + blockIdx.x] = sum (q-x)^2
+// over this CTA's rows, reduced in a fixed order (shuffle tree, then warps in index order).
+__global__ void __launch_bounds__(256)
+vq_gather_kernel(VqView q, const int32_t* __restrict__ best, double* __restrict__ partials) {
+    __shared__ double wsum[8];
+    const int w = threadIdx.x >> 5, lane = lane_id();
+    const int64_t h = blockIdx.y;
+    const int64_t m = (int64_t)blockIdx.x * 8 + w;
+    double part = 0.0;
+    if (m < q.rows) {
+        const int b = best[h * q.rows + m];
+        const int64_t eh = q.embed_heads == 1 ? 0 : h;
+        const float* e = q.embed + (eh * q.K + b) * (int64_t)q.D;
+        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
+        float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
+        float s = 0.f;
+        for (int d = lane; d < q.D; d += 32) {
+            float ev = __ldg(e + d);
+            float df = ev - __ldg(xp + d);
+            s = fmaf(df, df, s);
+            if (qp) qp[d] = ev;
+        }
+        part = (double)s;
+        if (lane == 0 && q.ind) q.ind[m * q.ind_row_stride + h * q.ind_head_stride] = (int64_t)b;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) wsum[w] = part;
+    __syncthreads();
+    if (threadIdx.x == 0 && partials) {
+        double t = 0.0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += wsum[i];
+        partials[h * gridDim.x + blockIdx.x] = t;
+    }
+}
+
+// one CTA per head: fixed-order reduction of the per-CTA partials
+__global__ void __launch_bounds__(256)
+vq_sqerr_reduce_kernel(const double* __restrict__ partials, int nblk, double* __restrict__ sq_err) {
+    __shared__ double sm[256];
+    const double* p = partials + (int64_t)blockIdx.x * nblk;
+    double t = 0.0;
+    for (int i = threadIdx.x; i < nblk; i += 256) t += p[i];
+    sm[threadIdx.x] = t;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) sm[threadIdx.x] += sm[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sq_err[blockIdx.x] = sm[0];
+}
+
+// ---- backward: g_x = g_q + g_loss*coef*(x - q) ---------------------------------------------------
+__global__ void vq_backward_kernel(const float* __restrict__ g_q, const float* __restrict__ x,
+                                   const float* __restrict__ qv, const float* __restrict__ g_loss,
+                                   float coef, int64_t n, float* __restrict__ g_x) {
+    const float gl = g_loss ? __ldg(g_loss) * coef : 0.f;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        float g = g_q ? g_q[i] : 0.f;
+        g_x[i] = fmaf(gl, x[i] - qv[i], g);
+    }
+}
+
+}  // namespace stemgnn
+
+using namespace stemgnn;
+
+extern "C" int stemgnn_vq_backward(const float* g_q, const float* x, const float* q,
+                                   const float* g_loss, float coef, int64_t numel, float* g_x,
+                                   stemgnn_stream_t stream) {
+    SG_CHECK_ARG(numel >= 0, "negative numel");
+    if (numel == 0) return STEMGNN_OK;
+    SG_CHECK_ARG(x && q && g_x, "NULL pointer");
+    int64_t blocks = (numel + 255) / 256;
+    int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    vq_backward_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(g_q, x, q, g_loss, coef,
+                                                                           numel, g_x);
+    SG_CHECK_LAUNCH();
+    return STEMGNN_OK;
+}
