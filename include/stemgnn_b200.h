@@ -151,9 +151,9 @@ int stemgnn_vq_code_stats(const stemgnn_vq_code_stats_args* args_host, void* wor
 /* lerp_ + laplace smoothing + divide (+ double l2norm for cosine), model/vq.py:495-506 /
  * 668-681, 40-46, 102-104.  Updates cluster_size [Hc,K], embed_avg [Hc,K,D], embed in place. */
 int stemgnn_vq_ema_apply(const float* counts, const float* sums, int64_t embed_heads,
-                         int64_t codes, int64_t dim, float decay, float eps, int cosine,
+                         int64_t codes, int64_t dim, double decay, double eps, int cosine,
                          float* cluster_size, float* embed_avg, float* embed,
-                         stemgnn_stream_t stream);
+                         float* totals_scratch /* [embed_heads] */, stemgnn_stream_t stream);
 
 #ifdef __cplusplus
 }

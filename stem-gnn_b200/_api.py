@@ -1,0 +1,15 @@
+"""Public surface: the drop-in modules plus the functional operators underneath them."""
+from . import _lib
+from ._lib import StemGnnError
+from .conv import GCNConv, GINConv, MixtureSageLayer, MySAGEConv
+from .encoder import Encoder, InnerProductDecoder
+from .graph import CSR, GraphStructure, clear_structure_cache, structure_of
+from .ops import (aggregate, vq_assign_raw, vq_code_stats, vq_ema_apply, vq_quantize,
+                  METRIC_DOT, METRIC_EUCLID, PATH_AUTO, PATH_EXACT, PATH_TENSOR)
+from .vq import CosineSimCodebook, EuclideanCodebook, VectorQuantize
+
+__all__ = ["StemGnnError", "GCNConv", "GINConv", "MixtureSageLayer", "MySAGEConv", "Encoder",
+           "InnerProductDecoder", "CSR", "GraphStructure", "clear_structure_cache", "structure_of",
+           "aggregate", "vq_assign_raw", "vq_code_stats", "vq_ema_apply", "vq_quantize",
+           "METRIC_DOT", "METRIC_EUCLID", "PATH_AUTO", "PATH_EXACT", "PATH_TENSOR",
+           "CosineSimCodebook", "EuclideanCodebook", "VectorQuantize"]

@@ -1,0 +1,101 @@
+"""ctypes binding of the C-ABI in include/stemgnn_b200.h (libstemgnn_b200.so, built in-tree by
+`__graft_entry__.build()`).  There is no CPU path: a missing library or a non-CUDA tensor is an
+error, never a fallback."""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libstemgnn_b200.so")
+ABI_VERSION = 1
+
+_i64, _i32, _vp, _f32, _f64 = C.c_int64, C.c_int, C.c_void_p, C.c_float, C.c_double
+
+
+class AggregateArgs(C.Structure):
+    _fields_ = [("rowptr", _vp), ("col", _vp), ("perm", _vp), ("n_rows", _i64),
+                ("n_gather_rows", _i64), ("num_edges", _i64), ("feat", _i64), ("gathered", _vp),
+                ("row_cnt", _vp), ("gather_cnt", _vp), ("edge_feat", _vp), ("type_table", _vp),
+                ("edge_type", _vp), ("edge_weight", _vp), ("row_x", _vp), ("act", _i32),
+                ("backward", _i32), ("out", _vp)]
+
+
+class VqAssignArgs(C.Structure):
+    _fields_ = [("x", _vp), ("x_row_stride", _i64), ("x_head_stride", _i64), ("embed", _vp),
+                ("heads", _i64), ("embed_heads", _i64), ("rows", _i64), ("codes", _i64),
+                ("dim", _i64), ("metric", _i32), ("path", _i32), ("ind", _vp),
+                ("ind_row_stride", _i64), ("ind_head_stride", _i64), ("quantize", _vp),
+                ("q_row_stride", _i64), ("q_head_stride", _i64), ("sq_err", _vp), ("stats", _vp)]
+
+
+class VqCodeStatsArgs(C.Structure):
+    _fields_ = [("x", _vp), ("x_row_stride", _i64), ("x_head_stride", _i64), ("ind", _vp),
+                ("ind_row_stride", _i64), ("ind_head_stride", _i64), ("heads", _i64),
+                ("embed_heads", _i64), ("rows", _i64), ("codes", _i64), ("dim", _i64),
+                ("counts", _vp), ("sums", _vp)]
+
+
+# name -> (restype, argtypes); every symbol include/stemgnn_b200.h declares
+SIGNATURES = {
+    "stemgnn_last_error": (C.c_char_p, []),
+    "stemgnn_abi_version": (_i32, []),
+    "stemgnn_csr_build_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
+    "stemgnn_csr_build": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
+    "stemgnn_aggregate": (_i32, [C.POINTER(AggregateArgs), _vp]),
+    "stemgnn_vq_assign_workspace": (_i32, [C.POINTER(VqAssignArgs), C.POINTER(C.c_size_t)]),
+    "stemgnn_vq_assign": (_i32, [C.POINTER(VqAssignArgs), _vp, C.c_size_t, _vp]),
+    "stemgnn_vq_backward": (_i32, [_vp, _vp, _vp, _vp, _f32, _i64, _vp, _vp]),
+    "stemgnn_vq_code_stats_workspace": (_i32, [C.POINTER(VqCodeStatsArgs), C.POINTER(C.c_size_t)]),
+    "stemgnn_vq_code_stats": (_i32, [C.POINTER(VqCodeStatsArgs), _vp, C.c_size_t, _vp]),
+    "stemgnn_vq_ema_apply": (_i32, [_vp, _vp, _i64, _i64, _i64, _f64, _f64, _i32, _vp, _vp, _vp,
+                                    _vp, _vp]),
+}
+
+_lib = None
+
+
+class StemGnnError(RuntimeError):
+    pass
+
+
+def lib():
+    """The loaded shared library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise StemGnnError(
+                f"{SO_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`."
+                " stemgnn_b200 has no CPU or PyTorch fallback.")
+        h = C.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(h, name)
+            fn.restype, fn.argtypes = res, args
+        if h.stemgnn_abi_version() != ABI_VERSION:
+            raise StemGnnError("libstemgnn_b200.so ABI version mismatch; rebuild")
+        _lib = h
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib().stemgnn_last_error()
+        raise StemGnnError(f"stemgnn error {rc}: {msg.decode() if msg else ''}")
+
+
+def ptr(t):
+    """Device pointer of a CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise StemGnnError("stemgnn_b200 operates on CUDA tensors only (no CPU fallback)")
+    return t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def workspace(nbytes, device):
+    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)

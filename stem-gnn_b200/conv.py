@@ -1,0 +1,164 @@
+"""Drop-in conv layers of the STEM-GNN encoder (reference model/encoder.py:17-129 and the PyG
+GCNConv / GINConv it instantiates at :197/:199), with the propagate step replaced by the fused
+sm_100a aggregation kernels.  Constructor / forward signatures and state_dict keys follow the
+reference so checkpoints and the unchanged pretrain.py / finetune.py keep working."""
+from typing import Optional, Tuple, Union
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from torch import Tensor
+
+from .graph import GraphStructure, structure_of
+from .ops import aggregate
+
+
+def _graph(edge_index, num_nodes):
+    if isinstance(edge_index, GraphStructure):
+        return edge_index
+    if not isinstance(edge_index, Tensor):
+        raise NotImplementedError("SparseTensor adjacency is not supported; pass edge_index [2,E]")
+    return structure_of(edge_index, num_nodes)
+
+
+class MySAGEConv(nn.Module):
+    """out = lin_l(mean_{j->i} relu(x_j [+ xe])) + lin_r(x_i)   (model/encoder.py:72-97)."""
+
+    def __init__(self, in_channels: Union[int, Tuple[int, int]], out_channels: int,
+                 aggr: Optional[str] = "mean", normalize: bool = False, root_weight: bool = True,
+                 project: bool = False, bias: bool = True, **kwargs):
+        super().__init__()
+        if kwargs:
+            raise NotImplementedError(f"MessagePassing options {sorted(kwargs)} are not supported")
+        if aggr not in ("mean", "sum", "add"):
+            raise NotImplementedError(f"aggr={aggr!r}: only 'mean' and 'sum'/'add' are on the hot path")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.aggr, self.normalize, self.root_weight, self.project = aggr, normalize, root_weight, project
+        if isinstance(in_channels, int):
+            in_channels = (in_channels, in_channels)
+        if in_channels[0] != in_channels[1]:
+            raise NotImplementedError("bipartite (x_src, x_dst) inputs are not supported")
+        if project:
+            self.lin = nn.Linear(in_channels[0], in_channels[0], bias=True)
+        self.lin_l = nn.Linear(in_channels[0], out_channels, bias=bias)
+        if root_weight:
+            self.lin_r = nn.Linear(in_channels[1], out_channels, bias=False)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        if self.project:
+            self.lin.reset_parameters()
+        self.lin_l.reset_parameters()
+        if self.root_weight:
+            self.lin_r.reset_parameters()
+
+    def forward(self, x: Tensor, edge_index, edge_attr: Optional[Tensor] = None, size=None) -> Tensor:
+        if isinstance(x, (tuple, list)):
+            if x[1] is not None and x[1] is not x[0]:
+                raise NotImplementedError("bipartite (x_src, x_dst) inputs are not supported")
+            x = x[0]
+        if size is not None and tuple(size) != (x.size(0), x.size(0)):
+            raise NotImplementedError("size must be None or (N, N)")
+        x_r = x
+        if self.project:
+            x = self.lin(x).relu()
+        g = _graph(edge_index, x.size(0))
+        if isinstance(edge_attr, tuple):          # (type_table [T,F], edge_type [E]) fast form
+            out = aggregate(x, g, reduce=self.aggr, act="relu", type_table=edge_attr[0],
+                            edge_type=edge_attr[1])
+        else:
+            out = aggregate(x, g, reduce=self.aggr, act="relu", edge_attr=edge_attr)
+        out = self.lin_l(out)
+        if self.root_weight:
+            out = out + self.lin_r(x_r)
+        if self.normalize:
+            out = F.normalize(out, p=2.0, dim=-1)
+        return out
+
+    def __repr__(self):
+        return f"{self.__class__.__name__}({self.in_channels}, {self.out_channels}, aggr={self.aggr})"
+
+
+class GCNConv(nn.Module):
+    """PyG GCNConv(in, out) as built at model/encoder.py:197: x W, symmetric-normalised sum over
+    the edges plus remaining self loops, + bias."""
+
+    def __init__(self, in_channels: int, out_channels: int, improved: bool = False,
+                 cached: bool = False, add_self_loops: bool = True, normalize: bool = True,
+                 bias: bool = True, **kwargs):
+        super().__init__()
+        if improved or not add_self_loops or not normalize or kwargs:
+            raise NotImplementedError("only the default GCNConv(in, out) configuration is supported")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.lin = nn.Linear(in_channels, out_channels, bias=False)
+        if bias:
+            self.bias = nn.Parameter(torch.empty(out_channels))
+        else:
+            self.register_parameter("bias", None)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        nn.init.xavier_uniform_(self.lin.weight)
+        if self.bias is not None:
+            nn.init.zeros_(self.bias)
+
+    def forward(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
+        if edge_weight is not None:
+            raise NotImplementedError("GCNConv with explicit edge_weight is not on the hot path")
+        g_sl, w = _graph(edge_index, x.size(0)).gcn()
+        out = aggregate(self.lin(x), g_sl, reduce="sum", edge_weight=w)
+        return out + self.bias if self.bias is not None else out
+
+
+class GINConv(nn.Module):
+    """PyG GINConv(nn) as built at model/encoder.py:199: nn((1 + eps) x_i + sum_j x_j)."""
+
+    def __init__(self, nn_module: nn.Module, eps: float = 0.0, train_eps: bool = False, **kwargs):
+        super().__init__()
+        if kwargs:
+            raise NotImplementedError(f"GINConv options {sorted(kwargs)} are not supported")
+        self.nn = nn_module
+        self.initial_eps = eps
+        if train_eps:
+            self.eps = nn.Parameter(torch.empty(1))
+        else:
+            self.register_buffer("eps", torch.empty(1))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        for m in self.nn.modules():
+            if m is not self.nn and hasattr(m, "reset_parameters"):
+                m.reset_parameters()
+        if hasattr(self.nn, "reset_parameters"):
+            self.nn.reset_parameters()
+        self.eps.data.fill_(self.initial_eps)
+
+    def forward(self, x: Tensor, edge_index, size=None) -> Tensor:
+        if size is not None and not isinstance(size, (tuple, list)):
+            raise NotImplementedError("GINConv takes no edge features (model/encoder.py:311 passes "
+                                      "edge_attr as `size`; use edge_attr=None with backbone='gin')")
+        out = aggregate(x, _graph(edge_index, x.size(0)), reduce="sum")
+        return self.nn(out + (1 + self.eps) * x)
+
+
+class MixtureSageLayer(nn.Module):
+    """model/encoder.py:109-129.  Aggregates x[edge_index[1]] AT edge_index[0] (the reverse of
+    MySAGEConv), no relu, no edge features."""
+
+    def __init__(self, in_dim: int, out_dim: int, num_experts: int, residual: bool = True):
+        super().__init__()
+        self.in_dim, self.out_dim, self.num_experts = in_dim, out_dim, num_experts
+        self.residual = residual and (in_dim == out_dim)
+        self.weights = nn.Parameter(torch.empty(num_experts, in_dim * 2, out_dim))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        nn.init.xavier_uniform_(self.weights)
+
+    def forward(self, x: Tensor, edge_index, edge_attr: Optional[Tensor] = None) -> Tensor:
+        agg = aggregate(x, _graph(edge_index, x.size(0)), to_row=0, reduce="mean")
+        combined = torch.cat([agg, x], dim=-1)
+        outputs = torch.einsum("nd,kdo->nko", combined, self.weights)
+        if self.residual:
+            outputs = outputs + x.unsqueeze(1)
+        return outputs

@@ -33,6 +33,7 @@ __global__ void vq_gather_kernel(VqView q, const int32_t* best, double* partials
 __global__ void vq_sqerr_reduce_kernel(const double* partials, int nblk, double* sq_err);
 
 // path 2 (k3_vq_tc.cu): returns 0 on success
+bool vq_tc_supported(const VqView& q);
 int vq_assign_tc_workspace(const VqView& q, size_t* bytes);
 int vq_assign_tc(const VqView& q, const float* x2, const float* e2, int32_t* best, int64_t* stats,
                  void* ws, size_t ws_bytes, cudaStream_t stream);

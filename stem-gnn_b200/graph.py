@@ -1,0 +1,108 @@
+"""Graph structure for the pull-based aggregation kernels (K0).
+
+The reference never builds a CSR: PyG scatters in COO order (model/encoder.py:82).  Grouping the
+edges by aggregation row with a STABLE sort keeps that per-row order, so the kernels add the
+messages of a row in exactly the order `scatter_add_` does.  Both groupings are kept: by
+edge_index[1] (forward of MySAGEConv / GCN / GIN, backward of MixtureSageLayer) and by
+edge_index[0] (the transposed structure for the other direction).
+"""
+import ctypes as C
+import weakref
+
+import torch
+
+from . import _lib
+
+
+class CSR:
+    """rowptr[N+1] int32, col[E] int32 (other endpoint), perm[E] int32 (original edge id),
+    cnt[N] fp32 = max(degree, 1)."""
+    __slots__ = ("rowptr", "col", "perm", "cnt", "n", "e")
+
+    def __init__(self, edge_index, num_nodes, group_row):
+        L = _lib.lib()
+        dev = edge_index.device
+        E, N = edge_index.size(1), int(num_nodes)
+        self.n, self.e = N, E
+        self.rowptr = torch.empty(N + 1, dtype=torch.int32, device=dev)
+        self.col = torch.empty(E, dtype=torch.int32, device=dev)
+        self.perm = torch.empty(E, dtype=torch.int32, device=dev)
+        self.cnt = torch.empty(N, dtype=torch.float32, device=dev)
+        need = C.c_size_t(0)
+        _lib.check(L.stemgnn_csr_build_workspace(E, N, C.byref(need)))
+        ws = _lib.workspace(need.value, dev)
+        _lib.check(L.stemgnn_csr_build(_lib.ptr(edge_index), E, N, group_row, _lib.ptr(self.rowptr),
+                                       _lib.ptr(self.col), _lib.ptr(self.perm), _lib.ptr(self.cnt),
+                                       _lib.ptr(ws), need.value, _lib.stream()))
+
+
+class GraphStructure:
+    """Both CSR groupings of one `edge_index` ([2,E] int64 CUDA, row 0 = source j, row 1 =
+    target i), built lazily."""
+
+    def __init__(self, edge_index, num_nodes):
+        if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.size(0) != 2:
+            raise ValueError("edge_index must be an int64 tensor of shape [2, E]")
+        if not edge_index.is_cuda:
+            raise _lib.StemGnnError("edge_index must be a CUDA tensor (no CPU fallback)")
+        self.edge_index = edge_index.contiguous()
+        self.num_nodes = int(num_nodes)
+        self._csr = {}
+        self._gcn = None
+
+    def grouped_by(self, row):
+        if row not in self._csr:
+            self._csr[row] = CSR(self.edge_index, self.num_nodes, row)
+        return self._csr[row]
+
+    @property
+    def by_dst(self):
+        return self.grouped_by(1)
+
+    @property
+    def by_src(self):
+        return self.grouped_by(0)
+
+    def gcn(self):
+        """(structure over the edge list with remaining self loops, w[E'] fp32) as
+        GCNConv.gcn_norm produces them (PyG 2.3.0, called at model/encoder.py:197).  The
+        self-loop list is integer mask/concat work on the device; weights come from K0."""
+        if self._gcn is None:
+            ei, N = self.edge_index, self.num_nodes
+            keep = ei[0] != ei[1]
+            loops = torch.arange(N, dtype=ei.dtype, device=ei.device)
+            ei_sl = torch.cat([ei[:, keep], torch.stack([loops, loops])], dim=1).contiguous()
+            g = GraphStructure(ei_sl, N)
+            w = torch.empty(ei_sl.size(1), dtype=torch.float32, device=ei.device)
+            _lib.check(_lib.lib().stemgnn_gcn_edge_weight(
+                _lib.ptr(ei_sl), ei_sl.size(1), N, _lib.ptr(g.by_dst.rowptr), _lib.ptr(w),
+                _lib.stream()))
+            self._gcn = (g, w)
+        return self._gcn
+
+
+_CACHE = {}
+_CACHE_MAX = 8
+
+
+def structure_of(edge_index, num_nodes):
+    """Cached GraphStructure for this edge_index tensor.  The key is (storage pointer, shape,
+    in-place version counter, N); entries die with the tensor.  An Encoder calls every layer
+    with the same edge_index, so the two sorts run once per step."""
+    key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, int(num_nodes),
+           edge_index.device.index)
+    hit = _CACHE.get(key)
+    if hit is not None and hit[0]() is edge_index:
+        return hit[1]
+    g = GraphStructure(edge_index, num_nodes)
+    if len(_CACHE) >= _CACHE_MAX:
+        _CACHE.pop(next(iter(_CACHE)))
+    try:
+        _CACHE[key] = (weakref.ref(edge_index), g)
+    except TypeError:
+        pass
+    return g
+
+
+def clear_structure_cache():
+    _CACHE.clear()

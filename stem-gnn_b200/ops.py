@@ -1,0 +1,226 @@
+"""Autograd operators over the C-ABI: aggregation (K1 forward / K2 backward) and the VQ
+assignment / statistics / EMA calls (K3, K4)."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .graph import GraphStructure
+
+REDUCE_SUM, REDUCE_MEAN = 0, 1
+ACT_NONE, ACT_RELU = 0, 1
+
+
+def _f32c(t, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise _lib.StemGnnError(f"{name} must be a CUDA tensor (no CPU fallback)")
+    if t.dtype != torch.float32:
+        raise TypeError(f"{name} must be float32 (got {t.dtype})")
+    return t.contiguous()
+
+
+def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_cnt=None,
+                    edge_feat=None, type_table=None, edge_type=None, edge_weight=None, row_x=None,
+                    act=ACT_NONE, backward=False):
+    per_edge = edge_feat is not None or edge_type is not None or edge_weight is not None
+    a = _lib.AggregateArgs(
+        rowptr=_lib.ptr(csr.rowptr), col=_lib.ptr(csr.col),
+        perm=_lib.ptr(csr.perm) if per_edge else None,
+        n_rows=csr.n, n_gather_rows=n_gather_rows, num_edges=csr.e, feat=gathered.size(1),
+        gathered=_lib.ptr(gathered), row_cnt=_lib.ptr(row_cnt), gather_cnt=_lib.ptr(gather_cnt),
+        edge_feat=_lib.ptr(edge_feat), type_table=_lib.ptr(type_table),
+        edge_type=_lib.ptr(edge_type), edge_weight=_lib.ptr(edge_weight), row_x=_lib.ptr(row_x),
+        act=act, backward=int(backward), out=_lib.ptr(out))
+    _lib.check(_lib.lib().stemgnn_aggregate(C.byref(a), _lib.stream()))
+
+
+class _Aggregate(torch.autograd.Function):
+    """out[i] = reduce_{e: to(e)=i} act(x[from(e)] + xe[e]) [* w[e]]  and its exact autograd.
+    `to_row` is the edge_index row aggregated AT (1 for PyG source_to_target)."""
+
+    @staticmethod
+    def forward(ctx, x, graph, to_row, reduce, act, edge_feat, type_table, edge_type, edge_weight):
+        x = _f32c(x, "x")
+        if x.dim() != 2 or x.size(0) != graph.num_nodes:
+            raise ValueError("x must be [num_nodes, F]")
+        fwd = graph.grouped_by(to_row)
+        out = torch.empty_like(x)
+        _aggregate_call(fwd, x.size(0), x, out,
+                        row_cnt=fwd.cnt if reduce == REDUCE_MEAN else None,
+                        edge_feat=edge_feat, type_table=type_table, edge_type=edge_type,
+                        edge_weight=edge_weight, act=act)
+        ctx.graph, ctx.to_row, ctx.reduce, ctx.act = graph, to_row, reduce, act
+        ctx.save_for_backward(x, edge_feat, type_table, edge_type, edge_weight)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        x, edge_feat, type_table, edge_type, edge_weight = ctx.saved_tensors
+        g_out = _f32c(g_out, "grad")
+        graph = ctx.graph
+        bwd = graph.grouped_by(1 - ctx.to_row)
+        g_x = torch.empty_like(x)
+        _aggregate_call(bwd, x.size(0), g_out, g_x,
+                        gather_cnt=graph.grouped_by(ctx.to_row).cnt if ctx.reduce == REDUCE_MEAN else None,
+                        edge_feat=edge_feat, type_table=type_table, edge_type=edge_type,
+                        edge_weight=edge_weight, row_x=x if ctx.act == ACT_RELU else None,
+                        act=ctx.act, backward=True)
+        return g_x, None, None, None, None, None, None, None, None
+
+
+def aggregate(x, graph, *, to_row=1, reduce="mean", act="none", edge_attr=None, edge_type=None,
+              type_table=None, edge_weight=None):
+    """Fused gather -> message -> reduce over a GraphStructure.
+
+    edge_attr: dense [E, F] per-edge features in original edge order (what the reference passes,
+    model/encoder.py:94-97), or (type_table [T,F], edge_type [E] int32/int64) for the table form.
+    Gradients flow to `x` only: edge features / weights are data on this path."""
+    if not isinstance(graph, GraphStructure):
+        raise TypeError("graph must be a GraphStructure")
+    for t, n in ((edge_attr, "edge_attr"), (type_table, "type_table"), (edge_weight, "edge_weight")):
+        if t is not None and t.requires_grad:
+            raise NotImplementedError(f"gradient w.r.t. {n} is not part of the hot path")
+    E = graph.edge_index.size(1)
+    edge_attr = _f32c(edge_attr, "edge_attr")
+    type_table = _f32c(type_table, "type_table")
+    edge_weight = _f32c(edge_weight, "edge_weight")
+    if edge_attr is not None and tuple(edge_attr.shape) != (E, x.size(1)):
+        raise ValueError(f"edge_attr must be [E, F] = [{E}, {x.size(1)}], got {tuple(edge_attr.shape)}")
+    if edge_type is not None:
+        if type_table is None or type_table.size(1) != x.size(1) or edge_type.numel() != E:
+            raise ValueError("edge_type needs a [T, F] type_table and one id per edge")
+        edge_type = edge_type.to(torch.int32).contiguous()
+    if edge_weight is not None and edge_weight.numel() != E:
+        raise ValueError("edge_weight must have one entry per edge")
+    r = {"mean": REDUCE_MEAN, "sum": REDUCE_SUM, "add": REDUCE_SUM}[reduce]
+    a = {"none": ACT_NONE, "relu": ACT_RELU}[act]
+    return _Aggregate.apply(x, graph, to_row, r, a, edge_attr, type_table, edge_type, edge_weight)
+
+
+# ------------------------------------------------------------------------------- VQ (K3 / K4)
+METRIC_EUCLID, METRIC_DOT = 0, 1
+PATH_AUTO, PATH_EXACT, PATH_TENSOR = 0, 1, 2
+
+
+def _head_layout(x, heads, embed):
+    """x [M, heads*D] row-major; embed [Hc, K, D].  A codebook shared by several heads sees the
+    heads as extra rows ('b n (h d) -> 1 (b h) n d', model/vq.py:885-887), i.e. x viewed as
+    [M*heads, D] with one head."""
+    Hc, K, D = embed.shape
+    M = x.size(0)
+    if x.size(1) != heads * D:
+        raise ValueError(f"x has {x.size(1)} columns, expected heads*codebook_dim = {heads * D}")
+    if Hc == heads:
+        return dict(heads=heads, embed_heads=Hc, rows=M, codes=K, dim=D, row_stride=heads * D,
+                    head_stride=D, ind_row_stride=heads, ind_head_stride=1)
+    if Hc != 1:
+        raise ValueError("embed must have 1 or `heads` codebooks")
+    return dict(heads=1, embed_heads=1, rows=M * heads, codes=K, dim=D, row_stride=D,
+                head_stride=0, ind_row_stride=1, ind_head_stride=0)
+
+
+def vq_assign_raw(x, embed, heads, metric, path=PATH_AUTO, want_sq_err=True, want_stats=False):
+    """One stemgnn_vq_assign call.  Returns (ind [M, heads] int64, quantize [M, heads*D] fp32,
+    sq_err [heads'] fp64 or None, stats int64[4] or None)."""
+    x, embed = _f32c(x, "x"), _f32c(embed, "embed")
+    lay = _head_layout(x, heads, embed)
+    dev = x.device
+    ind = torch.empty((x.size(0), heads), dtype=torch.int64, device=dev)
+    q = torch.empty_like(x)
+    sq = torch.empty(lay["heads"], dtype=torch.float64, device=dev) if want_sq_err else None
+    stats = torch.zeros(4, dtype=torch.int64, device=dev) if want_stats else None
+    a = _lib.VqAssignArgs(
+        x=_lib.ptr(x), x_row_stride=lay["row_stride"], x_head_stride=lay["head_stride"],
+        embed=_lib.ptr(embed), heads=lay["heads"], embed_heads=lay["embed_heads"],
+        rows=lay["rows"], codes=lay["codes"], dim=lay["dim"], metric=metric, path=path,
+        ind=_lib.ptr(ind), ind_row_stride=lay["ind_row_stride"],
+        ind_head_stride=lay["ind_head_stride"], quantize=_lib.ptr(q),
+        q_row_stride=lay["row_stride"], q_head_stride=lay["head_stride"],
+        sq_err=_lib.ptr(sq), stats=_lib.ptr(stats))
+    L = _lib.lib()
+    need = C.c_size_t(0)
+    _lib.check(L.stemgnn_vq_assign_workspace(C.byref(a), C.byref(need)))
+    ws = _lib.workspace(need.value, dev)
+    _lib.check(L.stemgnn_vq_assign(C.byref(a), _lib.ptr(ws), need.value, _lib.stream()))
+    return ind, q, sq, stats
+
+
+def vq_code_stats(x, ind, embed_shape, heads):
+    """counts [Hc, K], sums [Hc, K, D] of the rows assigned to every code (model/vq.py:492,497)."""
+    x = _f32c(x, "x")
+    Hc, K, D = embed_shape
+    lay = _head_layout(x, heads, torch.empty(embed_shape, device="meta"))
+    dev = x.device
+    ind = ind.contiguous()
+    # one flat buffer [counts | sums] so a multi-rank caller all-reduces it in a single call
+    flat = torch.empty(Hc * K * (1 + D), dtype=torch.float32, device=dev)
+    counts, sums = flat[:Hc * K].view(Hc, K), flat[Hc * K:].view(Hc, K, D)
+    a = _lib.VqCodeStatsArgs(
+        x=_lib.ptr(x), x_row_stride=lay["row_stride"], x_head_stride=lay["head_stride"],
+        ind=_lib.ptr(ind), ind_row_stride=lay["ind_row_stride"],
+        ind_head_stride=lay["ind_head_stride"], heads=lay["heads"],
+        embed_heads=lay["embed_heads"], rows=lay["rows"], codes=K, dim=D,
+        counts=_lib.ptr(counts), sums=_lib.ptr(sums))
+    L = _lib.lib()
+    need = C.c_size_t(0)
+    _lib.check(L.stemgnn_vq_code_stats_workspace(C.byref(a), C.byref(need)))
+    ws = _lib.workspace(need.value, dev)
+    _lib.check(L.stemgnn_vq_code_stats(C.byref(a), _lib.ptr(ws), need.value, _lib.stream()))
+    return counts, sums, flat
+
+
+def vq_ema_apply(counts, sums, cluster_size, embed_avg, embed, decay, eps, cosine):
+    """In-place lerp_ + laplace smoothing + divide (+ double l2norm), model/vq.py:495-506."""
+    Hc, K, D = embed.shape
+    for t in (cluster_size, embed_avg, embed):
+        if not t.is_contiguous() or t.dtype != torch.float32:
+            raise ValueError("codebook buffers must be contiguous float32")
+    scratch = torch.empty(Hc, dtype=torch.float32, device=embed.device)
+    _lib.check(_lib.lib().stemgnn_vq_ema_apply(
+        _lib.ptr(counts), _lib.ptr(sums), Hc, K, D, float(decay), float(eps), int(cosine),
+        _lib.ptr(cluster_size), _lib.ptr(embed_avg), _lib.ptr(embed), _lib.ptr(scratch),
+        _lib.stream()))
+
+
+class _VqQuantize(torch.autograd.Function):
+    """(quantize, ind, mse) = nearest code + straight-through + mean((quantize - x)^2).
+
+    backward (model/vq.py:937,1007-1009): g_x = g_quantize + g_mse * 2 (x - q) / numel.  When the
+    codebook is learnable the commitment term also reaches embed (commit_quantize is not
+    detached, vq.py:931-933): g_embed[k] = g_mse * 2/numel * (count_k * embed_k - sum_{n->k} x_n),
+    obtained from the K4 statistics instead of an N x K one-hot GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, embed, heads, metric, path, straight_through, embed_grad):
+        ind, q, sq, _ = vq_assign_raw(x, embed, heads, metric, path)
+        numel = x.numel()
+        mse = (sq.sum() / max(numel, 1)).to(torch.float32)
+        ctx.heads, ctx.st, ctx.embed_grad, ctx.numel = heads, straight_through, embed_grad, numel
+        ctx.save_for_backward(x, q, ind, embed)
+        ctx.mark_non_differentiable(ind)
+        return q, ind, mse
+
+    @staticmethod
+    def backward(ctx, g_q, _g_ind, g_mse):
+        x, q, ind, embed = ctx.saved_tensors
+        g_x = g_embed = None
+        if ctx.needs_input_grad[0]:
+            gq = _f32c(g_q, "grad") if (g_q is not None and ctx.st) else None
+            gl = None
+            if g_mse is not None:
+                gl = g_mse.reshape(1).to(torch.float32).contiguous()
+            g_x = torch.empty_like(x)
+            _lib.check(_lib.lib().stemgnn_vq_backward(
+                _lib.ptr(gq), _lib.ptr(x), _lib.ptr(q), _lib.ptr(gl), 2.0 / max(ctx.numel, 1),
+                x.numel(), _lib.ptr(g_x), _lib.stream()))
+        if ctx.embed_grad and ctx.needs_input_grad[1] and g_mse is not None:
+            counts, sums, _ = vq_code_stats(x, ind, tuple(embed.shape), ctx.heads)
+            g_embed = (counts.unsqueeze(-1) * embed - sums) * (g_mse * (2.0 / max(ctx.numel, 1)))
+        return g_x, g_embed, None, None, None, None, None
+
+
+def vq_quantize(x, embed, heads=1, metric=METRIC_EUCLID, path=PATH_AUTO, straight_through=True,
+                embed_grad=False):
+    return _VqQuantize.apply(x, embed, heads, metric, path, straight_through, embed_grad)

@@ -1,0 +1,78 @@
+"""CPU: the C-ABI library loads and exports every symbol include/stemgnn_b200.h declares; the
+host-side modules keep the reference's state_dict layout.  No compute calls (no GPU here)."""
+import os
+import re
+
+import pytest
+import torch
+
+import stemgnn_b200 as S
+from stemgnn_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "stemgnn_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(stemgnn_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    names = _declared_symbols()
+    assert len(names) >= 12
+    assert set(names) == set(_lib.SIGNATURES), "ctypes table and header disagree"
+    h = _lib.lib()
+    for n in names:
+        assert hasattr(h, n), n
+    assert h.stemgnn_abi_version() == _lib.ABI_VERSION
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    import ctypes as C
+    h = _lib.lib()
+    need = C.c_size_t(0)
+    assert h.stemgnn_csr_build_workspace(-1, 4, C.byref(need)) == -1
+    assert b"negative" in h.stemgnn_last_error()
+    assert h.stemgnn_csr_build_workspace(1000, 10, C.byref(need)) == 0 and need.value > 0
+
+
+def test_no_cpu_fallback():
+    x = torch.randn(4, 8)
+    ei = torch.zeros(2, 3, dtype=torch.int64)
+    with pytest.raises(S.StemGnnError):
+        S.GraphStructure(ei, 4)
+    vq = S.VectorQuantize(dim=8, codebook_size=4)
+    with pytest.raises(S.StemGnnError):
+        vq(x)
+
+
+def test_state_dict_layout_matches_reference():
+    vq = S.VectorQuantize(dim=768, codebook_size=128, codebook_dim=768, heads=4,
+                          separate_codebook_per_head=True, use_cosine_sim=True,
+                          orthogonal_reg_weight=1, orthogonal_reg_max_codes=32, ema_update=False,
+                          commitment_weight=10, kmeans_init=False)
+    sd = {k: tuple(v.shape) for k, v in vq.state_dict().items()}
+    assert sd["_codebook.embed"] == (4, 128, 768) and sd["_codebook.embed_avg"] == (4, 128, 768)
+    assert sd["_codebook.cluster_size"] == (4, 128) and sd["_codebook.initted"] == (1,)
+    assert sd["project_in.weight"] == (3072, 768) and sd["project_out.weight"] == (768, 3072)
+    assert isinstance(vq._codebook.embed, torch.nn.Parameter) and vq.codebook.shape == (4, 128, 768)
+    vq1 = S.VectorQuantize(dim=16, codebook_size=8)
+    assert vq1.codebook.shape == (8, 16) and not isinstance(vq1._codebook.embed, torch.nn.Parameter)
+    enc = S.Encoder(20, 24, torch.nn.ReLU, 2, backbone="sage", normalize="batch", moe=True,
+                    moe_layers="last")
+    keys = set(enc.state_dict())
+    assert {"layers.0.lin_l.weight", "layers.0.lin_l.bias", "layers.0.lin_r.weight",
+            "layers.1.weights", "env_encoders.0.weight", "norms.1.running_mean"} <= keys
+    assert enc.moe_layer_flags == [False, True]
+    import copy
+    copy.deepcopy(enc)
+
+
+def test_unsupported_options_raise():
+    with pytest.raises(NotImplementedError):
+        S.VectorQuantize(dim=8, codebook_size=4, affine_param=True)
+    with pytest.raises(NotImplementedError):
+        S.VectorQuantize(dim=8, codebook_size=4, stochastic_sample_codes=True)
+    with pytest.raises(NotImplementedError):
+        S.Encoder(8, 8, torch.nn.ReLU, 1, backbone="gat")

@@ -1,0 +1,153 @@
+"""GPU: K0 (CSR build) and K1/K2 (aggregation fwd/bwd) through the C-ABI against the oracle.
+Integer outputs bit-exact; fp32 aggregation bit-exact too, because the kernels add a row's
+messages one by one in stable edge order like scatter_add_ (north_star bound: 1e-5 relative)."""
+import numpy as np
+import pytest
+import torch
+
+import stemgnn_b200 as S
+from oracle import graph_ref
+from oracle import propagate_ref as P
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _graph(n, e, seed, hub=0):
+    g = torch.Generator().manual_seed(seed)
+    ei = torch.randint(0, n, (2, e), generator=g)
+    if hub:
+        ei[1, :hub] = n // 3
+        ei[0, hub:2 * hub] = n // 2
+    return ei
+
+
+@pytest.mark.parametrize("n,e,hub", [(1, 0, 0), (7, 0, 0), (50, 400, 0), (2708, 10556, 0),
+                                     (5000, 70000, 9000), (169343, 1166243, 0)])
+def test_csr_build_bit_exact(n, e, hub):
+    ei = _graph(n, e, 1, hub)
+    g = S.GraphStructure(ei.to(DEV), n)
+    for by in (0, 1):
+        rowptr, col, perm, deg = graph_ref.csr_build_ref(ei.numpy(), n, by)
+        c = g.grouped_by(by)
+        assert np.array_equal(c.rowptr.cpu().numpy(), rowptr)
+        assert np.array_equal(c.col.cpu().numpy(), col)
+        assert np.array_equal(c.perm.cpu().numpy(), perm)
+        assert np.array_equal(c.cnt.cpu().numpy(), np.maximum(deg, 1).astype(np.float32))
+
+
+def _check(x, ei, n, *, reduce, act, xe=None, table=None, etype=None, exact=True):
+    xc = x.clone().requires_grad_(True)
+    xe_full = xe if xe is not None else (table[etype] if table is not None else None)
+    if act == "relu":
+        ref = P.sage_propagate_ref(xc, ei, xe_full, n, reduce)
+    else:
+        assert xe_full is None
+        xj = xc.index_select(0, ei[0])
+        ref = P.scatter_mean_ref(xj, ei[1], n) if reduce == "mean" else P._scatter_sum(xj, ei[1], n)
+    go = torch.randn(ref.shape, generator=torch.Generator().manual_seed(5))
+    ref.backward(go)
+    xg = x.to(DEV).requires_grad_(True)
+    g = S.GraphStructure(ei.to(DEV), n)
+    kw = {}
+    if xe is not None:
+        kw["edge_attr"] = xe.to(DEV)
+    if table is not None:
+        kw.update(type_table=table.to(DEV), edge_type=etype.to(DEV))
+    out = S.aggregate(xg, g, reduce=reduce, act=act, **kw)
+    out.backward(go.to(DEV))
+    cmp = np.testing.assert_array_equal if exact else \
+        (lambda a, b: np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6))
+    cmp(out.detach().cpu().numpy(), ref.detach().numpy())
+    cmp(xg.grad.cpu().numpy(), xc.grad.numpy())
+
+
+@pytest.mark.parametrize("f", [1, 3, 20, 32, 37, 64, 100, 128, 256, 260, 768, 1433])
+@pytest.mark.parametrize("reduce,act", [("mean", "relu"), ("sum", "none"), ("mean", "none")])
+def test_aggregate_shapes(f, reduce, act):
+    n, e = 300, 3000
+    ei = _graph(n, e, 2, hub=400)
+    ei[1][ei[1] == 5] = 6       # isolated destination -> 0 / clamp(count, 1)
+    x = torch.randn(n, f, generator=torch.Generator().manual_seed(3))
+    _check(x, ei, n, reduce=reduce, act=act)
+
+
+@pytest.mark.parametrize("f", [24, 100, 768])
+def test_aggregate_edge_features_dense_and_table(f):
+    n, e = 200, 2500
+    g = torch.Generator().manual_seed(4)
+    ei = _graph(n, e, 4, hub=300)
+    x = torch.randn(n, f, generator=g)
+    table = torch.randn(5, f, generator=g)
+    etype = torch.randint(0, 5, (e,), generator=g)
+    _check(x, ei, n, reduce="mean", act="relu", xe=table[etype])
+    _check(x, ei, n, reduce="mean", act="relu", table=table, etype=etype)
+
+
+def test_aggregate_empty_graph_and_empty_features():
+    n = 10
+    ei = torch.zeros(2, 0, dtype=torch.int64)
+    x = torch.randn(n, 8)
+    _check(x, ei, n, reduce="mean", act="relu")
+
+
+@pytest.mark.parametrize("f", [19, 64])
+def test_gcn_weighted_sum(f):
+    n, e = 400, 3000
+    g = torch.Generator().manual_seed(6)
+    ei = _graph(n, e, 6, hub=200)
+    ei[1, 500:540] = ei[0, 500:540]   # explicit self loops
+    xw = torch.randn(n, f, generator=g)
+    xc = xw.clone().requires_grad_(True)
+    ref = P.gcn_propagate_ref(xc, ei, n)
+    go = torch.randn(n, f, generator=g)
+    ref.backward(go)
+    gs = S.GraphStructure(ei.to(DEV), n)
+    g_sl, w = gs.gcn()
+    ei_ref, w_ref = P.gcn_norm_ref(ei, n)
+    assert torch.equal(g_sl.edge_index.cpu(), ei_ref)
+    np.testing.assert_array_equal(w.cpu().numpy(), w_ref.numpy())
+    xg = xw.to(DEV).requires_grad_(True)
+    out = S.aggregate(xg, g_sl, reduce="sum", edge_weight=w)
+    out.backward(go.to(DEV))
+    np.testing.assert_array_equal(out.detach().cpu().numpy(), ref.detach().numpy())
+    np.testing.assert_array_equal(xg.grad.cpu().numpy(), xc.grad.numpy())
+
+
+def test_reverse_direction_mixture_aggregate():
+    n, e, f = 300, 2000, 48
+    ei = _graph(n, e, 7, hub=100)
+    x = torch.randn(n, f, generator=torch.Generator().manual_seed(7))
+    xc = x.clone().requires_grad_(True)
+    ref = P.mixture_aggregate_ref(xc, ei)
+    go = torch.randn(n, f, generator=torch.Generator().manual_seed(8))
+    ref.backward(go)
+    xg = x.to(DEV).requires_grad_(True)
+    out = S.aggregate(xg, S.GraphStructure(ei.to(DEV), n), to_row=0, reduce="mean")
+    out.backward(go.to(DEV))
+    np.testing.assert_array_equal(out.detach().cpu().numpy(), ref.detach().numpy())
+    np.testing.assert_array_equal(xg.grad.cpu().numpy(), xc.grad.numpy())
+
+
+def test_arxiv_shaped_full_size_bit_exact():
+    n, e, f = 169343, 1166243, 128
+    ei = _graph(n, e, 9)
+    x = torch.randn(n, f, generator=torch.Generator().manual_seed(9))
+    _check(x, ei, n, reduce="mean", act="relu")
+
+
+def test_linearity_property_large():
+    """Size-independent property at a products-like degree: sum aggregation without activation
+    is linear, agg(a x + y) == a agg(x) + agg(y) up to fp32 rounding."""
+    n, e, f = 200000, 5000000, 100
+    g = torch.Generator(device=DEV).manual_seed(10)
+    ei = torch.randint(0, n, (2, e), generator=g, device=DEV)
+    gs = S.GraphStructure(ei, n)
+    x = torch.randn(n, f, generator=g, device=DEV)
+    y = torch.randn(n, f, generator=g, device=DEV)
+    lhs = S.aggregate(2.0 * x + y, gs, reduce="sum")
+    rhs = 2.0 * S.aggregate(x, gs, reduce="sum") + S.aggregate(y, gs, reduce="sum")
+    torch.testing.assert_close(lhs, rhs, rtol=1e-4, atol=1e-4)
+    deg = torch.bincount(ei[1], minlength=n).float()
+    ones = S.aggregate(torch.ones(n, 4, device=DEV), gs, reduce="sum")
+    assert torch.equal(ones[:, 0], deg)
