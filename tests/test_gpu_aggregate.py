@@ -126,7 +126,9 @@ def test_reverse_direction_mixture_aggregate():
     out = S.aggregate(xg, S.GraphStructure(ei.to(DEV), n), to_row=0, reduce="mean")
     out.backward(go.to(DEV))
     np.testing.assert_array_equal(out.detach().cpu().numpy(), ref.detach().numpy())
-    np.testing.assert_array_equal(xg.grad.cpu().numpy(), xc.grad.numpy())
+    # the reference gathers with advanced indexing x[col] (encoder.py:124); its CPU backward is
+    # index_put_(accumulate=True), whose summation order is not the edge order -> 1e-5 bound
+    np.testing.assert_allclose(xg.grad.cpu().numpy(), xc.grad.numpy(), rtol=1e-5, atol=1e-6)
 
 
 def test_arxiv_shaped_full_size_bit_exact():

@@ -68,8 +68,7 @@ def test_vq_matches_reference_golden(golden_dir, name):
                                    g["after._codebook." + k], rtol=1e-5, atol=2e-6)
     if training:
         ((q * torch.from_numpy(g["g_quantize"]).to(DEV)).sum() + loss.sum()).backward()
-        if not cfg.get("orthogonal_reg_weight"):
-            np.testing.assert_allclose(x.grad.cpu().numpy(), g["g_x"], rtol=1e-5, atol=2e-6)
+        np.testing.assert_allclose(x.grad.cpu().numpy(), g["g_x"], rtol=1e-5, atol=2e-6)
         if "g_embed" in g and not cfg.get("orthogonal_reg_weight"):
             np.testing.assert_allclose(vq._codebook.embed.grad.cpu().numpy(), g["g_embed"],
                                        rtol=1e-5, atol=2e-6)
