@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py -- the driver-facing benchmark of the STEM-GNN encoder/VQ hot path on B200.
+
+One "step" = one pretrain-style pass of the hot path over one synthetic graph of the
+BASELINE.json configs[1] shape (ogbn-arxiv-shaped: 169,343 nodes, 1,166,243 edges, 128 feats;
+2-layer SAGE encoder 128->256->256 with BatchNorm + dropout 0.15; VectorQuantize 512 x 256,
+Euclidean, EMA decay 0.8): K0 CSR/CSC build of the fresh edge_index, encoder forward,
+VQ forward (argmin, gather, commitment loss, EMA update), backward, AdamW step.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (CUDA kernels, C-ABI)
+    python bench.py --impl reference --steps K --warmup W     # the CPU restatement, host cores
+
+* `value`  : edges/s = layers * E * n_gpus / step time, inputs resident in HBM, L2 flushed
+             between timed steps, CUDA events, max over ranks.
+* `e2e`    : same metric through the public module API with HOST (pinned) inputs: H2D of x and
+             edge_index and D2H of the loss inside the timed region.
+* `roofline`: the dominant kernel family of this library in the timed region, timed live with
+             CUDA events around each C-ABI call (stemgnn_b200._lib.traced).
+* N > 1    : one process per GPU (torchrun); every rank runs the step on its own graph (weak
+             scaling, the reference's mini-batch replicas); EMA statistics (model/vq.py:494,499)
+             and dense gradients are all-reduced over NCCL.
+The oracle (oracle/) is executed only for `cpu_baseline` and `--impl reference`.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.nn as nn  # noqa: E402
+
+WORKLOADS = {
+    # name: N, E, F_in, hidden, layers, K, D
+    "arxiv": dict(n=169343, e=1166243, f=128, hid=256, layers=2, codes=512,
+                  desc="ogbn-arxiv-shaped synthetic (169,343 nodes, 1,166,243 edges, 128 feats) "
+                       "2-layer SAGE encoder 128-256-256 + VQ 512x256 Euclid/EMA pretrain step"),
+    "cora": dict(n=2708, e=10556, f=1433, hid=768, layers=2, codes=128,
+                 desc="Cora-shaped synthetic (2,708 nodes, 10,556 edges, 1,433 feats)"),
+    "products": dict(n=2449029, e=61859140, f=100, hid=256, layers=3, codes=512,
+                     desc="ogbn-products-shaped synthetic (2,449,029 nodes, 61,859,140 edges, 100 feats)"),
+}
+METRIC = "edges/sec encoder fwd+bwd & VQ nodes/sec"
+L2_FLUSH_BYTES = 256 << 20
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tc=d["bf16_tflops"], tc_sus=d.get("bf16_tflops_sustained"),
+                    src="measured")
+    return dict(hbm=6650.0, tc=1590.0, tc_sus=1400.0, src="fallback")
+
+
+def synth_graph(w, seed, device="cpu"):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    ei = torch.randint(0, w["n"], (2, w["e"]), generator=g)
+    x = torch.randn(w["n"], w["f"], generator=g)
+    return x.to(device), ei.to(device)
+
+
+# --------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for ln in self.lines:
+            c = [t.strip() for t in ln.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx = float(c[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        # samples under load: the upper half (idle gaps between steps pull the clock down)
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------- our arm
+def build_models(w, device, S):
+    torch.manual_seed(0)
+    enc = S.Encoder(w["f"], w["hid"], nn.ReLU, w["layers"], backbone="sage", normalize="batch",
+                    dropout=0.15).to(device).train()
+    vq = S.VectorQuantize(dim=w["hid"], codebook_size=w["codes"], decay=0.8,
+                          commitment_weight=1.0).to(device).train()
+    opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
+    return enc, vq, opt
+
+
+def make_step(enc, vq, opt, S, world):
+    import torch.distributed as dist
+    params = [p for p in enc.parameters()]
+
+    def step(x, ei):
+        S.clear_structure_cache()          # pretraining sees a fresh edge_index every batch
+        opt.zero_grad(set_to_none=True)
+        z = enc(x, ei)
+        q, ind, vq_loss, _ = vq(z)
+        loss = q.square().mean() + vq_loss.sum()
+        loss.backward()
+        if world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat)
+            flat /= world
+            o = 0
+            for p in params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
+        opt.step()
+        return loss
+    return step
+
+
+def summarize_trace(trace, steps, pk, n_feat_bytes_l2):
+    fam = {}
+    for name, nbytes, flops, launches, e0, e1 in trace:
+        ms = e0.elapsed_time(e1)
+        key = "aggregate" if name.startswith("aggregate") else name
+        d = fam.setdefault(key, dict(ms=0.0, calls=0, bytes_min=0, bytes_gather=0, flops=0))
+        d["ms"] += ms; d["calls"] += 1; d["flops"] += flops
+        if isinstance(nbytes, tuple):
+            d["bytes_min"] += nbytes[0]; d["bytes_gather"] += nbytes[1]
+        else:
+            d["bytes_min"] += nbytes; d["bytes_gather"] += nbytes
+    out = {}
+    for k, d in fam.items():
+        sec = d["ms"] / 1e3
+        o = dict(ms_per_step=d["ms"] / steps, calls_per_step=d["calls"] / steps)
+        if sec > 0:
+            o["gbps_alg_min"] = d["bytes_min"] / sec / 1e9
+            o["gbps_alg_gather"] = d["bytes_gather"] / sec / 1e9
+            if d["flops"]:
+                o["tflops"] = d["flops"] / sec / 1e12
+        out[k] = o
+    return out
+
+
+def roofline_of(kern, name, pk, x_fits_l2):
+    k = kern[name]
+    if name == "vq_assign" and k.get("tflops") is not None:
+        # K >= ~508 with fp32 inputs sits right of the ridge: tensor-bound
+        return dict(kernel=name, bound="tensor", achieved=k["tflops"], peak=pk["tc_sus"] or pk["tc"],
+                    unit="TFLOP/s", frac=k["tflops"] / (pk["tc_sus"] or pk["tc"]), traffic=None,
+                    peak_source=pk["src"] + " (sustained: kernel timed inside a long step)")
+    a = k["gbps_alg_min"] if x_fits_l2 else k["gbps_alg_gather"]
+    return dict(kernel=name, bound="hbm", achieved=a, peak=pk["hbm"], unit="GB/s", frac=a / pk["hbm"],
+                traffic=None, peak_source=pk["src"],
+                bytes_model="compulsory (X fits L2)" if x_fits_l2 else "one source row per edge")
+
+
+def cpu_baseline_step_fn(w, threads):
+    """The oracle's restatement of the same step (CPU, fp32, all host threads)."""
+    from oracle.encoder_ref import EncoderRef
+    from oracle.vq_ref import vq_forward_ref
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    enc = EncoderRef(w["f"], w["hid"], nn.ReLU, w["layers"], backbone="sage", normalize="batch",
+                     dropout=0.15).train()
+    opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
+    K, D = w["codes"], w["hid"]
+    embed = torch.empty(1, K, D)
+    nn.init.kaiming_uniform_(embed)
+    state = dict(embed=embed, embed_avg=embed.clone(), cluster_size=torch.zeros(1, K))
+
+    def step(x, ei):
+        opt.zero_grad(set_to_none=True)
+        z = enc(x, ei)
+        q, ind, vq_loss, _ = vq_forward_ref(z, state, training=True, ema_update=True, decay=0.8,
+                                            commitment_weight=1.0)
+        loss = q.square().mean() + vq_loss.sum()
+        loss.backward()
+        opt.step()
+        return float(loss.detach())
+    return step
+
+
+def cpu_sample(w, frac):
+    """Bounded sample of the workload for the CPU arm: the same shape scaled by `frac`."""
+    if frac >= 1.0:
+        return dict(w), "full workload"
+    s = dict(w)
+    s["n"], s["e"] = max(int(w["n"] * frac), 1), max(int(w["e"] * frac), 1)
+    return s, f"{frac:g} of the nodes and edges (same widths), scaled by edges"
+
+
+def run_reference(args, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    ws, sample = cpu_sample(w, args.cpu_frac)
+    step = cpu_baseline_step_fn(ws, threads)
+    x, ei = synth_graph(ws, 1)
+    for _ in range(args.warmup):
+        step(x, ei)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step(x, ei)
+    dt = time.perf_counter() - t0
+    val = ws["layers"] * ws["e"] * args.steps / dt
+    nodes = ws["n"] * args.steps / dt
+    line = dict(metric=METRIC, value=val, unit="edges/s", impl="reference", n_gpus=args.gpus,
+                steps=args.steps, warmup=args.warmup, ms_per_step=dt / args.steps * 1e3,
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+                data="synthetic", vq_nodes_per_s=nodes,
+                config=dict(workload=w["desc"], layers=w["layers"], nodes=w["n"], edges=w["e"], sample=sample),
+                cpu_baseline=dict(value=val, unit="edges/s", cores=threads, kind="port",
+                                  sample=sample + "; oracle/ restatement of the reference step "
+                                  "(PyG/torch_scatter are not installable here)"),
+                e2e=dict(value=val, unit="edges/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                gpu_launches=0)
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, w):
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; stemgnn_b200 has no CPU path "
+                         "(use --impl reference for the CPU restatement)")
+    import __graft_entry__ as G
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    if rank == 0:
+        G.build()
+    if world > 1:
+        dist.barrier()
+    import stemgnn_b200 as S
+    from stemgnn_b200 import _lib
+    _lib.lib()
+
+    enc, vq, opt = build_models(w, dev, S)
+    step = make_step(enc, vq, opt, S, world)
+    x_h, ei_h = synth_graph(w, 1 + rank)
+    x_h, ei_h = x_h.pin_memory(), ei_h.pin_memory()
+    x_d, ei_d = x_h.to(dev), ei_h.to(dev)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    pk = peaks()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---------------- resident-input timing (value)
+    for _ in range(max(args.warmup, 3)):
+        step(x_d, ei_d)
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _lib.TRACE = []
+    l0 = _lib.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    for a, b in ev:
+        flush.fill_(1)                      # L2 flush between timed steps (256 MB > 126 MB L2)
+        a.record()
+        step(x_d, ei_d)
+        b.record()
+    sync_all()
+    launches = (_lib.launch_count() - l0) / args.steps
+    trace, _lib.TRACE = _lib.TRACE, None
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+
+    # ---------------- end-to-end timing (host buffers in, loss out)
+    x_s, ei_s = torch.empty_like(x_d), torch.empty_like(ei_d)
+    loss_h = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        x_s.copy_(x_h, non_blocking=True)
+        ei_s.copy_(ei_h, non_blocking=True)
+        loss = step(x_s, ei_s)
+        loss_h.copy_(loss.detach().reshape(1), non_blocking=True)
+
+    for _ in range(2):
+        e2e_step()
+    sync_all()
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    for a, b in ev2:
+        flush.fill_(1)
+        a.record()
+        e2e_step()
+        b.record()
+    sync_all()
+    ms_e2e = sum(a.elapsed_time(b) for a, b in ev2)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    units = w["layers"] * w["e"] * world
+    value = units * args.steps / (ms / 1e3)
+    e2e_v = units * args.steps / (ms_e2e / 1e3)
+    x_fits_l2 = w["n"] * max(w["f"], w["hid"]) * 4 <= 126e6
+    kern = summarize_trace(trace, args.steps, pk, x_fits_l2)
+    mine = {k: v for k, v in kern.items()}
+    top = max(mine, key=lambda k: mine[k]["ms_per_step"])
+    roof = roofline_of(kern, top, pk, x_fits_l2)
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        roof["traffic"] = json.load(open(traffic_file)).get(top)
+    line = dict(metric=METRIC, value=value, unit="edges/s", n_gpus=world, steps=args.steps,
+                warmup=max(args.warmup, 3), ms_per_step=ms / args.steps, higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                vq_nodes_per_s=w["n"] * world * args.steps / (ms / 1e3),
+                config=dict(workload=w["desc"], layers=w["layers"], nodes=w["n"], edges=w["e"],
+                            l2="flushed between timed steps (256 MB write)",
+                            parallelism=f"replicas x{world}: EMA statistics + dense grads all-reduced"
+                            if world > 1 else "single GPU"),
+                e2e=dict(value=e2e_v, unit="edges/s", ms_per_step=ms_e2e / args.steps,
+                         h2d_bytes_per_step=x_h.numel() * 4 + ei_h.numel() * 8, d2h_bytes_per_step=4),
+                gpu_launches=launches, roofline=roof, kernels=kern, clocks=clocks)
+    if world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        ws, sample = cpu_sample(w, args.cpu_frac)
+        cstep = cpu_baseline_step_fn(ws, threads)
+        xc, eic = synth_graph(ws, 1)
+        cstep(xc, eic)
+        t0, n = time.perf_counter(), 0
+        while n < 3 or (time.perf_counter() - t0 < 10 and n < 50):
+            cstep(xc, eic); n += 1
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = dict(value=ws["layers"] * ws["e"] * n / dt, unit="edges/s",
+                                    cores=threads, kind="port",
+                                    sample=f"{n} steps of {sample}; oracle/ restatement, torch CPU fp32")
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="arxiv", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-frac", type=float, default=1.0,
+                    help="fraction of the graph the CPU arm runs per step (bounded sample)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    w = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, w)
+    else:
+        run_ours(args, w)
+
+
+if __name__ == "__main__":
+    main()

@@ -32,6 +32,8 @@ typedef void* stemgnn_stream_t; /* cudaStream_t */
 
 const char* stemgnn_last_error(void);
 int stemgnn_abi_version(void);
+/* number of CUDA kernels this library has launched in this process (all entry points) */
+uint64_t stemgnn_launch_count(void);
 
 /* ------------------------------------------------------------------ K0: graph structure
  * Replaces the implicit COO scatter order of MessagePassing.propagate (model/encoder.py:82)

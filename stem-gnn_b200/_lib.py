@@ -40,6 +40,7 @@ class VqCodeStatsArgs(C.Structure):
 SIGNATURES = {
     "stemgnn_last_error": (C.c_char_p, []),
     "stemgnn_abi_version": (_i32, []),
+    "stemgnn_launch_count": (C.c_uint64, []),
     "stemgnn_csr_build_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
     "stemgnn_csr_build": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
     "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
@@ -99,3 +100,36 @@ def stream():
 
 def workspace(nbytes, device):
     return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+
+
+# ------------------------------------------------------------------ per-call device timing
+# Optional CUDA-event trace of every C-ABI call (used by bench.py for the roofline of the
+# dominant kernel "live over the timed region").  Off by default: zero overhead.
+TRACE = None
+
+
+class traced:
+    """with traced("name", algorithmic_bytes, flops): <C-ABI call(s)>"""
+    __slots__ = ("rec",)
+
+    def __init__(self, name, nbytes=0, flops=0, launches=0):
+        self.rec = None
+        if TRACE is not None:
+            self.rec = [name, nbytes, flops, launches, torch.cuda.Event(enable_timing=True),
+                        torch.cuda.Event(enable_timing=True)]
+
+    def __enter__(self):
+        if self.rec is not None:
+            self.rec[4].record()
+        return self
+
+    def __exit__(self, *exc):
+        if self.rec is not None:
+            self.rec[5].record()
+            TRACE.append(self.rec)
+        return False
+
+
+def launch_count():
+    """Kernels launched by this library in this process so far (counted at the launch sites)."""
+    return int(lib().stemgnn_launch_count())

@@ -1,12 +1,17 @@
 // common.cu -- error string, ABI version, device attribute cache.
 #include <stdarg.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "common.cuh"
 
 namespace stemgnn {
 static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+uint64_t launches() { return g_launches.load(std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -30,3 +35,4 @@ int sm_count() {
 
 extern "C" const char* stemgnn_last_error(void) { return stemgnn::g_err; }
 extern "C" int stemgnn_abi_version(void) { return 1; }
+extern "C" uint64_t stemgnn_launch_count(void) { return stemgnn::launches(); }

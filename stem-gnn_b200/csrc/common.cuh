@@ -11,6 +11,10 @@ namespace stemgnn {
 
 void set_error(const char* fmt, ...);
 int sm_count();  // cached per process (device of first use)
+void count_launch();  // process-wide launch counter behind stemgnn_launch_count()
+
+// every kernel launch of the library goes through this so the count is a measurement
+#define SG_LAUNCH(...) (stemgnn::count_launch(), __VA_ARGS__)
 
 #define SG_CHECK_ARG(cond, msg)                                   \
     do {                                                          \

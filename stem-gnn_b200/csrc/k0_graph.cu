@@ -226,10 +226,10 @@ const int32_t* radix_sort_pairs(const int64_t* k64, const int32_t* k32, int64_t 
         int32_t* kout = kbuf[p & 1];
         int32_t* vout = ((P - 1 - p) & 1) ? vws : vals_out;   // last pass writes vals_out
         const int64_t* kk64 = p == 0 ? k64 : nullptr;
-        radix_hist_kernel<<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, n, 8 * p, nblk, block_hist);
-        radix_scan_kernel<<<RS_BINS, RS_THREADS, 0, stream>>>(block_hist, nblk, digit_total);
-        radix_scatter_kernel<<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, vin, n, 8 * p, nblk,
-                                                              block_hist, digit_total, kout, vout);
+        SG_LAUNCH(radix_hist_kernel<<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, n, 8 * p, nblk, block_hist));
+        SG_LAUNCH(radix_scan_kernel<<<RS_BINS, RS_THREADS, 0, stream>>>(block_hist, nblk, digit_total));
+        SG_LAUNCH(radix_scatter_kernel<<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, vin, n, 8 * p, nblk,
+                                                              block_hist, digit_total, kout, vout));
         kin = kout;
         vin = vout;
     }
@@ -238,8 +238,8 @@ const int32_t* radix_sort_pairs(const int64_t* k64, const int32_t* k32, int64_t 
 
 void launch_lower_bound(const int32_t* sorted_keys, int64_t n, int64_t n_bins, int32_t* offsets,
                         cudaStream_t stream) {
-    csr_rowptr_kernel<<<(unsigned)((n_bins + 1 + 255) / 256), 256, 0, stream>>>(sorted_keys, n,
-                                                                                 n_bins, offsets);
+    SG_LAUNCH(csr_rowptr_kernel<<<(unsigned)((n_bins + 1 + 255) / 256), 256, 0, stream>>>(sorted_keys, n,
+                                                                                 n_bins, offsets));
 }
 
 }  // namespace stemgnn
@@ -272,7 +272,7 @@ extern "C" int stemgnn_csr_build(const int64_t* edge_index, int64_t E, int64_t N
     const int T = 256;
     if (E == 0) {
         cudaMemsetAsync(rowptr, 0, (size_t)(N + 1) * 4, stream);
-        if (cnt && N > 0) csr_cnt_kernel<<<(unsigned)((N + T - 1) / T), T, 0, stream>>>(rowptr, N, cnt);
+        if (cnt && N > 0) SG_LAUNCH(csr_cnt_kernel<<<(unsigned)((N + T - 1) / T), T, 0, stream>>>(rowptr, N, cnt));
         SG_CHECK_LAUNCH();
         return STEMGNN_OK;
     }
@@ -280,9 +280,9 @@ extern "C" int stemgnn_csr_build(const int64_t* edge_index, int64_t E, int64_t N
     const int64_t* key_row = edge_index + (int64_t)group_row * E;
     const int64_t* other_row = edge_index + (int64_t)(1 - group_row) * E;
     const int32_t* kin = radix_sort_pairs(key_row, nullptr, E, N, perm, ws, stream);
-    csr_rowptr_kernel<<<(unsigned)((N + 1 + T - 1) / T), T, 0, stream>>>(kin, E, N, rowptr);
-    if (cnt && N > 0) csr_cnt_kernel<<<(unsigned)((N + T - 1) / T), T, 0, stream>>>(rowptr, N, cnt);
-    csr_col_kernel<<<(unsigned)((E + T - 1) / T), T, 0, stream>>>(other_row, perm, E, col);
+    SG_LAUNCH(csr_rowptr_kernel<<<(unsigned)((N + 1 + T - 1) / T), T, 0, stream>>>(kin, E, N, rowptr));
+    if (cnt && N > 0) SG_LAUNCH(csr_cnt_kernel<<<(unsigned)((N + T - 1) / T), T, 0, stream>>>(rowptr, N, cnt));
+    SG_LAUNCH(csr_col_kernel<<<(unsigned)((E + T - 1) / T), T, 0, stream>>>(other_row, perm, E, col));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }
@@ -293,8 +293,8 @@ extern "C" int stemgnn_gcn_edge_weight(const int64_t* edge_index_sl, int64_t E, 
     SG_CHECK_ARG(E >= 0 && N >= 0, "negative size");
     if (E == 0) return STEMGNN_OK;
     SG_CHECK_ARG(edge_index_sl && rowptr_by_dst && w_out, "NULL pointer");
-    gcn_weight_kernel<<<(unsigned)((E + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        edge_index_sl, E, rowptr_by_dst, w_out);
+    SG_LAUNCH(gcn_weight_kernel<<<(unsigned)((E + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        edge_index_sl, E, rowptr_by_dst, w_out));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

@@ -157,7 +157,7 @@ template <int VEC, int LANES, int CH, int MODE, bool BWD>
 static void launch(const AggParams& p, cudaStream_t s) {
     constexpr int ROWS_PER_BLOCK = 8 * (32 / LANES);
     unsigned grid = (unsigned)((p.n_rows + ROWS_PER_BLOCK - 1) / ROWS_PER_BLOCK);
-    aggregate_kernel<VEC, LANES, CH, MODE, BWD><<<grid, 256, 0, s>>>(p);
+    SG_LAUNCH(aggregate_kernel<VEC, LANES, CH, MODE, BWD><<<grid, 256, 0, s>>>(p));
 }
 
 template <int MODE, bool BWD>

@@ -91,22 +91,22 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
     double* partials = ws.take<double>((size_t)q.heads * p.nblk);
 
     const int64_t ek = q.embed_heads * (int64_t)q.K;
-    vq_sqnorm_kernel<<<(unsigned)((ek * 32 + 255) / 256), 256, 0, stream>>>(
-        q.embed, ek, 1, q.D, q.D, 0, e2);
+    SG_LAUNCH(vq_sqnorm_kernel<<<(unsigned)((ek * 32 + 255) / 256), 256, 0, stream>>>(
+        q.embed, ek, 1, q.D, q.D, 0, e2));
     if (q.metric == 0)
-        vq_sqnorm_kernel<<<(unsigned)((p.items * 32 + 255) / 256), 256, 0, stream>>>(
-            q.x, q.rows, q.heads, q.D, q.x_row_stride, q.x_head_stride, x2);
+        SG_LAUNCH(vq_sqnorm_kernel<<<(unsigned)((p.items * 32 + 255) / 256), 256, 0, stream>>>(
+            q.x, q.rows, q.heads, q.D, q.x_row_stride, q.x_head_stride, x2));
     if (p.path == 1) {
         dim3 grid((unsigned)((q.rows + 63) / 64), (unsigned)q.heads);
-        vq_scan_kernel<<<grid, 256, 0, stream>>>(q, x2, e2, nullptr, nullptr, best);
+        SG_LAUNCH(vq_scan_kernel<<<grid, 256, 0, stream>>>(q, x2, e2, nullptr, nullptr, best));
     } else {
         rc = vq_assign_tc(q, x2, e2, best, a->stats, ws.base + ws.off, workspace_bytes - ws.off, stream);
         if (rc) return rc;
     }
     dim3 ggrid((unsigned)p.nblk, (unsigned)q.heads);
-    vq_gather_kernel<<<ggrid, 256, 0, stream>>>(q, best, a->sq_err ? partials : nullptr);
+    SG_LAUNCH(vq_gather_kernel<<<ggrid, 256, 0, stream>>>(q, best, a->sq_err ? partials : nullptr));
     if (a->sq_err)
-        vq_sqerr_reduce_kernel<<<(unsigned)q.heads, 256, 0, stream>>>(partials, (int)p.nblk, a->sq_err);
+        SG_LAUNCH(vq_sqerr_reduce_kernel<<<(unsigned)q.heads, 256, 0, stream>>>(partials, (int)p.nblk, a->sq_err));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

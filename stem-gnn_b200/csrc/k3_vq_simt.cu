@@ -210,8 +210,8 @@ extern "C" int stemgnn_vq_backward(const float* g_q, const float* x, const float
     int64_t blocks = (numel + 255) / 256;
     int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-    vq_backward_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(g_q, x, q, g_loss, coef,
-                                                                           numel, g_x);
+    SG_LAUNCH(vq_backward_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(g_q, x, q, g_loss, coef,
+                                                                           numel, g_x));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

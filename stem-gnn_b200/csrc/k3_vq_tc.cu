@@ -1,6 +1,5 @@
-// k3_vq_tc.cu -- K3 path 2: tcgen05 bf16 distance GEMM with TMEM accumulators + exact fp32
-// rescoring of near-ties.  (Placeholder until the kernel lands: reports "unsupported" so the
-// auto path uses the exact fp32 scan; nothing falls back silently.)
+// k3_vq_tc.cu -- K3 path 2 placeholder while the tcgen05 kernel is brought up: reports the
+// tensor-core path as unsupported so path 0 (auto) resolves to the exact fp32 scan.
 #include "k3_vq_common.cuh"
 
 namespace stemgnn {

@@ -244,7 +244,7 @@ void launch_chunks(const StatsView& v, const StatsPlan& p, const int32_t* skeys,
                    const int32_t* off, float* sums, float* hp, cudaStream_t s) {
     const int groups = 256 / p.G;
     unsigned grid = (unsigned)((p.nchunks + groups - 1) / groups);
-    stats_chunk_kernel<VEC, NCOL><<<grid, 256, 0, s>>>(v, p.T, p.chunk, p.G, skeys, sitems, off, sums, hp);
+    SG_LAUNCH(stats_chunk_kernel<VEC, NCOL><<<grid, 256, 0, s>>>(v, p.T, p.chunk, p.G, skeys, sitems, off, sums, hp));
 }
 }  // namespace
 
@@ -295,10 +295,10 @@ extern "C" int stemgnn_vq_code_stats(const stemgnn_vq_code_stats_args* a, void* 
     v.ind = a->ind; v.ind_row_stride = a->ind_row_stride; v.ind_head_stride = a->ind_head_stride;
     v.heads = a->heads; v.embed_heads = a->embed_heads; v.rows = a->rows;
     v.K = (int)a->codes; v.D = (int)a->dim;
-    stats_keys_kernel<<<(unsigned)((p.T + 255) / 256), 256, 0, stream>>>(v, p.T, keys);
+    SG_LAUNCH(stats_keys_kernel<<<(unsigned)((p.T + 255) / 256), 256, 0, stream>>>(v, p.T, keys));
     const int32_t* skeys = radix_sort_pairs(nullptr, keys, p.T, p.KK, sitems, ws, stream);
     launch_lower_bound(skeys, p.T, p.KK, off, stream);
-    stats_counts_kernel<<<(unsigned)((p.KK + 255) / 256), 256, 0, stream>>>(off, p.KK, a->counts);
+    SG_LAUNCH(stats_counts_kernel<<<(unsigned)((p.KK + 255) / 256), 256, 0, stream>>>(off, p.KK, a->counts));
 #define SG_STATS_CASE(V, N) \
     if (p.vec == V && p.ncol == N) launch_chunks<V, N>(v, p, skeys, sitems, off, a->sums, hp, stream)
     SG_STATS_CASE(4, 1); SG_STATS_CASE(4, 2); SG_STATS_CASE(4, 4); SG_STATS_CASE(4, 8);
@@ -306,8 +306,8 @@ extern "C" int stemgnn_vq_code_stats(const stemgnn_vq_code_stats_args* a, void* 
     SG_STATS_CASE(1, 16); SG_STATS_CASE(1, 32);
 #undef SG_STATS_CASE
     int64_t tot = p.KK * a->dim;
-    stats_combine_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(off, p.KK, (int)a->dim,
-                                                                            p.chunk, hp, a->sums);
+    SG_LAUNCH(stats_combine_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(off, p.KK, (int)a->dim,
+                                                                            p.chunk, hp, a->sums));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }
@@ -320,12 +320,12 @@ extern "C" int stemgnn_vq_ema_apply(const float* counts, const float* sums, int6
     SG_CHECK_ARG(embed_heads >= 1 && codes >= 1 && dim >= 1, "bad sizes");
     SG_CHECK_ARG(counts && sums && cluster_size && embed_avg && embed && totals_scratch, "NULL pointer");
     const float w = (float)(1.0 - decay);   // python double 1-decay, rounded to fp32 by lerp_
-    ema_cluster_kernel<<<(unsigned)embed_heads, 256, 0, stream>>>(counts, (int)codes, w, cluster_size,
-                                                                  totals_scratch);
+    SG_LAUNCH(ema_cluster_kernel<<<(unsigned)embed_heads, 256, 0, stream>>>(counts, (int)codes, w, cluster_size,
+                                                                  totals_scratch));
     const int64_t KK = embed_heads * codes;
-    ema_embed_kernel<<<(unsigned)((KK * 32 + 255) / 256), 256, 0, stream>>>(
+    SG_LAUNCH(ema_embed_kernel<<<(unsigned)((KK * 32 + 255) / 256), 256, 0, stream>>>(
         sums, cluster_size, totals_scratch, KK, (int)codes, (int)dim, w, (float)eps,
-        (float)((double)codes * eps), cosine, embed_avg, embed);
+        (float)((double)codes * eps), cosine, embed_avg, embed));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

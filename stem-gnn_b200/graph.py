@@ -31,9 +31,10 @@ class CSR:
         need = C.c_size_t(0)
         _lib.check(L.stemgnn_csr_build_workspace(E, N, C.byref(need)))
         ws = _lib.workspace(need.value, dev)
-        _lib.check(L.stemgnn_csr_build(_lib.ptr(edge_index), E, N, group_row, _lib.ptr(self.rowptr),
-                                       _lib.ptr(self.col), _lib.ptr(self.perm), _lib.ptr(self.cnt),
-                                       _lib.ptr(ws), need.value, _lib.stream()))
+        with _lib.traced("csr_build", E * (16 + 12) + (2 * N + 1) * 4, 0):
+            _lib.check(L.stemgnn_csr_build(_lib.ptr(edge_index), E, N, group_row, _lib.ptr(self.rowptr),
+                                           _lib.ptr(self.col), _lib.ptr(self.perm), _lib.ptr(self.cnt),
+                                           _lib.ptr(ws), need.value, _lib.stream()))
 
 
 class GraphStructure:

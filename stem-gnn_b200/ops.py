@@ -33,7 +33,17 @@ def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_c
         edge_feat=_lib.ptr(edge_feat), type_table=_lib.ptr(type_table),
         edge_type=_lib.ptr(edge_type), edge_weight=_lib.ptr(edge_weight), row_x=_lib.ptr(row_x),
         act=act, backward=int(backward), out=_lib.ptr(out))
-    _lib.check(_lib.lib().stemgnn_aggregate(C.byref(a), _lib.stream()))
+    # algorithmic bytes: every row read once (X fits the 126 MB L2) or one source
+    # row per edge (it does not); index, count and per-edge streams once
+    n_g, F, E = n_gather_rows, gathered.size(1), csr.e
+    idx = E * 4 + (csr.n + 1) * 4 + (csr.n * 4 if (row_cnt is not None or gather_cnt is not None) else 0)
+    if per_edge:
+        idx += E * 4 + (E * F * 4 if edge_feat is not None else 0) + (E * 4 if edge_type is not None or edge_weight is not None else 0)
+    rows = csr.n * F * 4 * (2 if row_x is not None else 1)
+    b_min, b_gather = n_g * F * 4 + rows + idx, E * F * 4 + rows + idx
+    name = "aggregate_bwd" if backward else "aggregate_fwd"
+    with _lib.traced(name, (b_min, b_gather), 0, 1):
+        _lib.check(_lib.lib().stemgnn_aggregate(C.byref(a), _lib.stream()))
 
 
 class _Aggregate(torch.autograd.Function):
@@ -143,7 +153,10 @@ def vq_assign_raw(x, embed, heads, metric, path=PATH_AUTO, want_sq_err=True, wan
     need = C.c_size_t(0)
     _lib.check(L.stemgnn_vq_assign_workspace(C.byref(a), C.byref(need)))
     ws = _lib.workspace(need.value, dev)
-    _lib.check(L.stemgnn_vq_assign(C.byref(a), _lib.ptr(ws), need.value, _lib.stream()))
+    M, K, D, H = lay["rows"], lay["codes"], lay["dim"], lay["heads"]
+    nbytes = H * M * D * 4 * 2 + H * M * 8 + embed.numel() * 4
+    with _lib.traced("vq_assign", nbytes, 2 * H * M * K * D):
+        _lib.check(L.stemgnn_vq_assign(C.byref(a), _lib.ptr(ws), need.value, _lib.stream()))
     return ind, q, sq, stats
 
 
@@ -167,7 +180,9 @@ def vq_code_stats(x, ind, embed_shape, heads):
     need = C.c_size_t(0)
     _lib.check(L.stemgnn_vq_code_stats_workspace(C.byref(a), C.byref(need)))
     ws = _lib.workspace(need.value, dev)
-    _lib.check(L.stemgnn_vq_code_stats(C.byref(a), _lib.ptr(ws), need.value, _lib.stream()))
+    T = lay["heads"] * lay["rows"]
+    with _lib.traced("vq_code_stats", T * D * 4 + T * 8 + 2 * Hc * K * (D + 1) * 4, 0):
+        _lib.check(L.stemgnn_vq_code_stats(C.byref(a), _lib.ptr(ws), need.value, _lib.stream()))
     return counts, sums, flat
 
 
@@ -178,10 +193,11 @@ def vq_ema_apply(counts, sums, cluster_size, embed_avg, embed, decay, eps, cosin
         if not t.is_contiguous() or t.dtype != torch.float32:
             raise ValueError("codebook buffers must be contiguous float32")
     scratch = torch.empty(Hc, dtype=torch.float32, device=embed.device)
-    _lib.check(_lib.lib().stemgnn_vq_ema_apply(
-        _lib.ptr(counts), _lib.ptr(sums), Hc, K, D, float(decay), float(eps), int(cosine),
-        _lib.ptr(cluster_size), _lib.ptr(embed_avg), _lib.ptr(embed), _lib.ptr(scratch),
-        _lib.stream()))
+    with _lib.traced("vq_ema_apply", 4 * Hc * K * (D + 1) * 4, 0, 2):
+        _lib.check(_lib.lib().stemgnn_vq_ema_apply(
+            _lib.ptr(counts), _lib.ptr(sums), Hc, K, D, float(decay), float(eps), int(cosine),
+            _lib.ptr(cluster_size), _lib.ptr(embed_avg), _lib.ptr(embed), _lib.ptr(scratch),
+            _lib.stream()))
 
 
 class _VqQuantize(torch.autograd.Function):
@@ -212,9 +228,10 @@ class _VqQuantize(torch.autograd.Function):
             if g_mse is not None:
                 gl = g_mse.reshape(1).to(torch.float32).contiguous()
             g_x = torch.empty_like(x)
-            _lib.check(_lib.lib().stemgnn_vq_backward(
-                _lib.ptr(gq), _lib.ptr(x), _lib.ptr(q), _lib.ptr(gl), 2.0 / max(ctx.numel, 1),
-                x.numel(), _lib.ptr(g_x), _lib.stream()))
+            with _lib.traced("vq_backward", x.numel() * 4 * (4 if gq is not None else 3), 0, 1):
+                _lib.check(_lib.lib().stemgnn_vq_backward(
+                    _lib.ptr(gq), _lib.ptr(x), _lib.ptr(q), _lib.ptr(gl), 2.0 / max(ctx.numel, 1),
+                    x.numel(), _lib.ptr(g_x), _lib.stream()))
         if ctx.embed_grad and ctx.needs_input_grad[1] and g_mse is not None:
             counts, sums, _ = vq_code_stats(x, ind, tuple(embed.shape), ctx.heads)
             g_embed = (counts.unsqueeze(-1) * embed - sums) * (g_mse * (2.0 / max(ctx.numel, 1)))
