@@ -1,13 +1,654 @@
-// k3_vq_tc.cu -- K3 path 2 placeholder while the tcgen05 kernel is brought up: reports the
-// tensor-core path as unsupported so path 0 (auto) resolves to the exact fp32 scan.
+// k3_vq_tc.cu -- K3 path 2: the codebook search as a tcgen05 / TMEM GEMM fused with the row
+// argmax, for sm_100a.
+//
+// Replaces dist = einsum('h n d, h c d -> h n c') / -cdist and argmax (reference
+// STEM-GNN/model/vq.py:650,652 cosine; :472,474 Euclidean; gumbel_sample :79) without ever
+// materialising the N x K score matrix.
+//
+//   scores~ = bf16(X) . bf16(E)^T  [-  e2/2 for the Euclidean metric]      (tensor cores)
+//
+// A persistent CTA owns a 128-row tile of X.  Four producer warps read the fp32 rows with
+// 128-bit loads, round to bf16 and store them K-major / 128B-swizzled in shared memory (the
+// canonical UMMA operand layout) -- X is read from HBM exactly once, as fp32.  The codebook is
+// pre-converted once per call into the same swizzled tile image in global memory, so one
+// elected thread streams it with 1-D bulk async copies (cp.async.bulk -> mbarrier complete_tx)
+// through a ring of 32 KB stages.  One elected thread issues tcgen05.mma (M=128, N<=256, K=16,
+// bf16 -> fp32) into a double-buffered 2 x 256-column TMEM accumulator; four epilogue warps read
+// the accumulator with tcgen05.ld (one row per thread), add -e2/2 and keep the running best
+// score plus every code within a rigorous error band of it.
+//
+// Parity: bf16 rounding perturbs a dot product by at most 2^-8 |x||e| (plus fp32 accumulation
+// slop), so the exact fp32 winner is always inside the band.  Rows whose band holds a single
+// code are final; the others (typically a few codes) are re-scored by vq_rescore_kernel with
+// the *same* fp32 formula and summation order as the exact scan (k3_vq_simt.cu), first index
+// winning ties -- the result is identical to path 1.  A row whose candidate list overflows is
+// re-scanned exactly.  FLOPs: 2*N*K*D on the tensor pipe; HBM: N*D*4 B (x) + N*4 B (best).
+#include <cuda_bf16.h>
+
 #include "k3_vq_common.cuh"
 
 namespace stemgnn {
-bool vq_tc_supported(const VqView&) { return false; }
-int vq_assign_tc_workspace(const VqView&, size_t* bytes) { *bytes = 0; return STEMGNN_EUNSUPPORTED; }
-int vq_assign_tc(const VqView&, const float*, const float*, int32_t*, int64_t*, void*, size_t,
-                 cudaStream_t) {
-    set_error("vq_assign_tc: tcgen05 path not built");
-    return STEMGNN_EUNSUPPORTED;
+namespace tc {
+
+constexpr int BM = 128;                    // rows per tile = UMMA M
+constexpr int BN = 256;                    // codes per accumulator tile = max UMMA N
+constexpr int BK = 64;                     // bf16 columns per smem chunk (one 128 B swizzle row)
+constexpr int A_CHUNK_BYTES = BM * 128;    // 16 KB
+constexpr int B_STAGE_BYTES = BN * 128;    // 32 KB
+constexpr int CAP = 8;                     // candidates kept per row
+constexpr int NUM_THREADS = 320;           // warps 0-3 epilogue, 4-7 producers, 8 loader, 9 MMA
+constexpr int PROD_WARP0 = 4, LOAD_WARP = 8, MMA_WARP = 9;
+constexpr int MAX_KC = 16;                 // a_full barriers (resident: D <= 1024; ring: stages)
+constexpr int MAX_SB = 6;
+constexpr int SMEM_EXTRA = 4 * BN * 4 + 4 * BM * 4 + 64 * 8 + 16;   // ne2 slices, x2 ring, barriers
+constexpr int SMEM_MAX = 232448;           // 227 KB opt-in limit per CTA
+
+// ---------------------------------------------------------------------------------- PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
 }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar),
+                 "r"(bytes)
+                 : "memory");
+}
+// Bounded wait: a protocol bug traps (launch failure) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (!done && spin > (1u << 24)) __trap();
+    }
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_smem() {   // generic-proxy smem writes -> async proxy
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {   // arrives when prior MMAs retire
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, fp32 accumulate, M x N x 16
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                          uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row atoms 1024 B apart.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
+    return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, N at [17,23), M at [24,29)
+__device__ __forceinline__ uint32_t make_idesc(int m, int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t addr, float* v) {
+    uint32_t* r = reinterpret_cast<uint32_t*>(v);
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+          "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
+          "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
+          "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(addr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ---------------------------------------------------------------------------------- params
+struct TcParams {
+    const float* x; int64_t x_row_stride, x_head_stride;
+    int64_t heads, embed_heads, rows;
+    int K, D;
+    int n_tiles, kcn;                // code tiles of 256, 64-column chunks
+    int sb;                          // B ring stages
+    int sa;                          // A ring stages (ring mode only)
+    const __nv_bfloat16* img;        // [embed_heads][n_tiles][kcn][256 x 64] swizzled tile images
+    const float* ne2;                // [embed_heads][n_tiles*256]: -e2/2 | 0, padded with -inf
+    const uint32_t* emax2_bits;      // [embed_heads] max e2 as float bits
+    float c1, c2;                    // band = c1*|x|*emax + c2*(x2 + e2max)
+    int32_t* best;                   // [heads*rows]
+    int32_t* cand;                   // [heads*rows][CAP]
+    int32_t* multi_list; int32_t* fb_list; int32_t* counters;   // [0]=multi, [1]=fallback
+};
+
+__device__ __forceinline__ int tile_codes32(const TcParams& p, int n) {
+    int rem = p.K - n * BN;
+    rem = rem > BN ? BN : rem;
+    return (rem + 31) & ~31;
+}
+
+// ---------------------------------------------------------------------------------- kernel
+template <bool RESIDENT>
+__global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // dynamic smem base is 1024-aligned by the attribute on sm_100; keep an explicit round-up
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int a_slots = RESIDENT ? p.kcn : p.sa;
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + (size_t)a_slots * A_CHUNK_BYTES;
+    float* s_ne2 = reinterpret_cast<float*>(sB + (size_t)p.sb * B_STAGE_BYTES);   // [4][256]
+    float* s_x2 = s_ne2 + 4 * BN;                                                  // [4][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_x2 + 4 * BM);
+    uint64_t* a_full = bars;                 // [MAX_KC]
+    uint64_t* a_empty = bars + MAX_KC;       // [MAX_KC] (resident mode uses [0])
+    uint64_t* b_full = bars + 2 * MAX_KC;    // [MAX_SB]
+    uint64_t* b_empty = b_full + MAX_SB;     // [MAX_SB]
+    uint64_t* t_full = b_empty + MAX_SB;     // [2]
+    uint64_t* t_empty = t_full + 2;          // [2]
+    uint64_t* x2_full = t_empty + 2;         // [4]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x2_full + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t row_tiles = (p.rows + BM - 1) / BM;
+    const int64_t n_items = row_tiles * p.heads;
+
+    if (warp == LOAD_WARP && lane == 0) {
+        for (int i = 0; i < MAX_KC; ++i) { mbar_init(smem_u32(a_full + i), BM); mbar_init(smem_u32(a_empty + i), 1); }
+        for (int i = 0; i < MAX_SB; ++i) { mbar_init(smem_u32(b_full + i), 1); mbar_init(smem_u32(b_empty + i), 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), BM); }
+        for (int i = 0; i < 4; ++i) mbar_init(smem_u32(x2_full + i), BM);
+        fence_barrier_init();
+    }
+    if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_slot), 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == LOAD_WARP) {
+        // ================= codebook loader: bulk async copies into the B ring =================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int64_t h = item / row_tiles;
+                const int64_t eh = p.embed_heads == 1 ? 0 : h;
+                for (int n = 0; n < p.n_tiles; ++n) {
+                    const uint32_t bytes = (uint32_t)tile_codes32(p, n) * 128u;
+                    const uint8_t* src = reinterpret_cast<const uint8_t*>(p.img) +
+                                         ((eh * p.n_tiles + n) * (int64_t)p.kcn) * B_STAGE_BYTES;
+                    for (int kc = 0; kc < p.kcn; ++kc, ++it) {
+                        const uint32_t s = it % (uint32_t)p.sb, ph = (it / (uint32_t)p.sb) & 1u;
+                        mbar_wait(smem_u32(b_empty + s), ph ^ 1u);
+                        mbar_expect_tx(smem_u32(b_full + s), bytes);
+                        bulk_g2s(smem_u32(sB + (size_t)s * B_STAGE_BYTES), src + (size_t)kc * B_STAGE_BYTES,
+                                 bytes, smem_u32(b_full + s));
+                    }
+                }
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        // ================= MMA issuer: one thread drives the tensor core =================
+        if (lane == 0) {
+            uint32_t it_b = 0, it_a = 0, acc_it = 0, tile_it = 0;
+            const int last_ksteps = ((p.D - (p.kcn - 1) * BK) + 15) / 16;
+            for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
+                for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
+                    const uint32_t idesc = make_idesc(BM, tile_codes32(p, n));
+                    const uint32_t st = acc_it & 1u;
+                    mbar_wait(smem_u32(t_empty + st), ((acc_it >> 1) & 1u) ^ 1u);
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + st * BN;
+                    for (int kc = 0; kc < p.kcn; ++kc, ++it_b) {
+                        const uint32_t sb = it_b % (uint32_t)p.sb;
+                        uint32_t a_addr;
+                        if (RESIDENT) {
+                            if (n == 0) mbar_wait(smem_u32(a_full + kc), tile_it & 1u);
+                            a_addr = smem_u32(sA + (size_t)kc * A_CHUNK_BYTES);
+                        } else {
+                            const uint32_t sa = it_a % (uint32_t)p.sa;
+                            mbar_wait(smem_u32(a_full + sa), (it_a / (uint32_t)p.sa) & 1u);
+                            a_addr = smem_u32(sA + (size_t)sa * A_CHUNK_BYTES);
+                        }
+                        mbar_wait(smem_u32(b_full + sb), (it_b / (uint32_t)p.sb) & 1u);
+                        tc_fence_after();
+                        const uint64_t a_desc = smem_desc_sw128(a_addr);
+                        const uint64_t b_desc = smem_desc_sw128(smem_u32(sB + (size_t)sb * B_STAGE_BYTES));
+                        const int ksteps = kc == p.kcn - 1 ? last_ksteps : BK / 16;
+                        for (int k = 0; k < ksteps; ++k)   // +32 B along K inside the swizzle row
+                            umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                      (uint32_t)((kc | k) != 0));
+                        umma_commit(smem_u32(b_empty + sb));
+                        if (!RESIDENT) { umma_commit(smem_u32(a_empty + it_a % (uint32_t)p.sa)); ++it_a; }
+                    }
+                    umma_commit(smem_u32(t_full + st));
+                }
+                if (RESIDENT) umma_commit(smem_u32(a_empty));
+            }
+        }
+    } else if (warp >= PROD_WARP0) {
+        // ================= producers: fp32 rows -> bf16, swizzled K-major A chunks =================
+        const int pt = threadIdx.x - PROD_WARP0 * 32;       // 0..127
+        const int q = pt & 15, rg = pt >> 4;                // float4 slot in the chunk, row in the atom
+        const uint32_t soff = (uint32_t)(rg * 128 + (((q >> 1) ^ rg) << 4) + (q & 1) * 8);
+        uint32_t it_a = 0, tile_it = 0;
+        for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
+            const int64_t h = item / row_tiles, mt = item - h * row_tiles;
+            const int64_t row0 = mt * BM;
+            const float* xb = p.x + h * p.x_head_stride;
+            float sq[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) sq[i] = 0.f;
+            if (RESIDENT) mbar_wait(smem_u32(a_empty), (tile_it & 1u) ^ 1u);
+            const int n_pass = RESIDENT ? 1 : p.n_tiles;
+            for (int n = 0; n < n_pass; ++n) {
+                for (int kc = 0; kc < p.kcn; ++kc) {
+                    uint32_t slot = kc;
+                    if (!RESIDENT) {
+                        slot = it_a % (uint32_t)p.sa;
+                        mbar_wait(smem_u32(a_empty + slot), ((it_a / (uint32_t)p.sa) & 1u) ^ 1u);
+                        ++it_a;
+                    }
+                    const int col = kc * BK + q * 4;
+                    const bool col_ok = col < p.D;
+                    float4 v[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const int64_t r = row0 + rg + 8 * i;
+                        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (col_ok && r < p.rows)
+                            v[i] = __ldg(reinterpret_cast<const float4*>(xb + r * p.x_row_stride + col));
+                    }
+                    uint8_t* dst = sA + (size_t)slot * A_CHUNK_BYTES + soff;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(v[i].x, v[i].y);
+                        __nv_bfloat162 hi = __floats2bfloat162_rn(v[i].z, v[i].w);
+                        uint2 pk;
+                        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+                        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                        *reinterpret_cast<uint2*>(dst + i * 1024) = pk;
+                        if (n == 0) {
+                            sq[i] = fmaf(v[i].x, v[i].x, sq[i]); sq[i] = fmaf(v[i].y, v[i].y, sq[i]);
+                            sq[i] = fmaf(v[i].z, v[i].z, sq[i]); sq[i] = fmaf(v[i].w, v[i].w, sq[i]);
+                        }
+                    }
+                    fence_async_smem();
+                    mbar_arrive(smem_u32(a_full + slot));
+                    if (n == 0 && kc == p.kcn - 1) {
+                        // squared row norms for the error band -> x2 ring (4 deep, see epilogue)
+                        float* x2d = s_x2 + (tile_it & 3u) * BM;
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            float s = sq[i];
+                            s += __shfl_xor_sync(0xffffffffu, s, 1);
+                            s += __shfl_xor_sync(0xffffffffu, s, 2);
+                            s += __shfl_xor_sync(0xffffffffu, s, 4);
+                            s += __shfl_xor_sync(0xffffffffu, s, 8);
+                            if (q == 0) x2d[rg + 8 * i] = s;
+                        }
+                        mbar_arrive(smem_u32(x2_full + (tile_it & 3u)));
+                    }
+                }
+            }
+        }
+    } else {
+        // ================= epilogue: TMEM -> registers, running best + candidate band =================
+        const int row_in_tile = warp * 32 + lane;
+        float* ne2s = s_ne2 + warp * BN;
+        uint32_t acc_it = 0, tile_it = 0;
+        for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
+            const int64_t h = item / row_tiles, mt = item - h * row_tiles;
+            const int64_t eh = p.embed_heads == 1 ? 0 : h;
+            const int64_t m = mt * BM + row_in_tile;
+            const float* ne2g = p.ne2 + eh * (int64_t)p.n_tiles * BN;
+            float rb = -INFINITY, thr = -INFINITY, band = 0.f;
+            float cv[CAP];
+            int ci[CAP];
+            int nc = 0;
+            bool overflow = false;
+            for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
+                const int ncols = tile_codes32(p, n);
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < BN / 32; ++j) ne2s[j * 32 + lane] = __ldg(ne2g + n * BN + j * 32 + lane);
+                __syncwarp();
+                const uint32_t st = acc_it & 1u;
+                mbar_wait(smem_u32(t_full + st), (acc_it >> 1) & 1u);
+                tc_fence_after();
+                if (n == 0) {
+                    mbar_wait(smem_u32(x2_full + (tile_it & 3u)), (tile_it >> 2) & 1u);
+                    const float xx = s_x2[(tile_it & 3u) * BM + row_in_tile];
+                    const float e2m = __uint_as_float(__ldg(p.emax2_bits + eh));
+                    band = p.c1 * sqrtf(xx) * sqrtf(e2m) + p.c2 * (xx + e2m);
+                }
+                const uint32_t t_addr = tmem_base + ((uint32_t)(warp * 32) << 16) + st * BN;
+                for (int c0 = 0; c0 < ncols; c0 += 32) {
+                    float v[32];
+                    tmem_ld32(t_addr + (uint32_t)c0, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        float mx = -INFINITY;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            v[g * 8 + i] += ne2s[c0 + g * 8 + i];
+                            mx = fmaxf(mx, v[g * 8 + i]);
+                        }
+                        if (mx >= thr) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                const float s = v[g * 8 + i];
+                                if (s >= thr) {
+                                    if (s > rb) { rb = s; thr = rb - band; }
+                                    if (nc == CAP) {       // compact against the current threshold
+                                        int keep = 0;
+                                        for (int j = 0; j < CAP; ++j)
+                                            if (cv[j] >= thr) { cv[keep] = cv[j]; ci[keep] = ci[j]; ++keep; }
+                                        nc = keep;
+                                        if (nc == CAP) { overflow = true; nc = 0; }
+                                    }
+                                    cv[nc] = s;
+                                    ci[nc] = n * BN + c0 + g * 8 + i;
+                                    ++nc;
+                                }
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(smem_u32(t_empty + st));
+            }
+            if (m < p.rows) {
+                const int64_t flat = h * p.rows + m;
+                int keep = 0, only = -1;
+                for (int j = 0; j < nc; ++j)
+                    if (cv[j] >= thr) { only = ci[j]; p.cand[flat * CAP + keep] = ci[j]; ++keep; }
+                if (overflow || keep == 0) {
+                    p.best[flat] = -1;
+                    p.fb_list[atomicAdd(p.counters + 1, 1)] = (int32_t)flat;
+                } else if (keep == 1) {
+                    p.best[flat] = only;
+                } else {
+                    for (int j = keep; j < CAP; ++j) p.cand[flat * CAP + j] = -1;
+                    p.best[flat] = -1;
+                    p.multi_list[atomicAdd(p.counters + 0, 1)] = (int32_t)flat;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == MMA_WARP) tmem_dealloc(tmem_base, 512);
+}
+
+// -------------------------------------------------------------------------- codebook image
+// One thread per 16-byte chunk (8 bf16) of the swizzled tile image; padding is zero.
+__global__ void vq_tc_image_kernel(const float* __restrict__ embed, int64_t embed_heads, int K, int D,
+                                   int n_tiles, int kcn, __nv_bfloat16* __restrict__ img) {
+    const int64_t total = embed_heads * n_tiles * (int64_t)kcn * BN * 8;
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    const int j = (int)(t & 7);                 // logical 16-byte chunk in the 128 B row
+    const int r = (int)((t >> 3) % BN);         // row (code) in the tile
+    int64_t tile = (t >> 3) / BN;               // (eh, n, kc) flattened
+    const int kc = (int)(tile % kcn);
+    const int n = (int)((tile / kcn) % n_tiles);
+    const int64_t eh = tile / kcn / n_tiles;
+    const int code = n * BN + r, col = kc * BK + j * 8;
+    float f[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        f[i] = (code < K && col + i < D) ? __ldg(embed + (eh * K + code) * (int64_t)D + col + i) : 0.f;
+    uint4 pk;
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
+    pk.x = *reinterpret_cast<uint32_t*>(&b0); pk.y = *reinterpret_cast<uint32_t*>(&b1);
+    pk.z = *reinterpret_cast<uint32_t*>(&b2); pk.w = *reinterpret_cast<uint32_t*>(&b3);
+    const int64_t off = tile * B_STAGE_BYTES + (int64_t)(r >> 3) * 1024 + (r & 7) * 128 + ((j ^ (r & 7)) << 4);
+    *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(img) + off) = pk;
+}
+
+// ne2[eh][c] = -e2/2 (Euclid) | 0 (dot) for c < K, -inf for padding; emax2 = max_c e2
+__global__ void vq_tc_ne2_kernel(const float* __restrict__ e2, int64_t embed_heads, int K, int n_tiles,
+                                 int metric, float* __restrict__ ne2, uint32_t* __restrict__ emax2_bits) {
+    const int64_t kp = (int64_t)n_tiles * BN;
+    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= embed_heads * kp) return;
+    const int64_t eh = t / kp;
+    const int c = (int)(t - eh * kp);
+    float v = -INFINITY;
+    if (c < K) {
+        const float e = e2[eh * K + c];
+        v = metric == 0 ? -0.5f * e : 0.f;
+        atomicMax(emax2_bits + eh, __float_as_uint(e));   // e2 >= 0: uint order == float order
+    }
+    ne2[t] = v;
+}
+
+// ---------------------------------------------------------------------------- rescoring
+// One warp per row with more than one candidate: the same fp32 formula and summation order as
+// the exact scan (vq_sqnorm_kernel for x2, a sequential fmaf chain over d for the dot), first
+// index wins ties.  Lane j scores candidate j.
+__global__ void __launch_bounds__(256)
+vq_rescore_kernel(VqView q, const float* __restrict__ e2, const int32_t* __restrict__ multi_list,
+                  const int32_t* __restrict__ counters, const int32_t* __restrict__ cand,
+                  int32_t* __restrict__ best) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int total = counters[0];
+    for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < total; w += nwarps) {
+        const int64_t flat = multi_list[w];
+        const int64_t h = flat / q.rows, m = flat - h * q.rows;
+        const int64_t eh = q.embed_heads == 1 ? 0 : h;
+        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
+        float x2 = 0.f;
+        if (q.metric == 0) {
+            for (int d = lane; d < q.D; d += 32) { float t = __ldg(xp + d); x2 = fmaf(t, t, x2); }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x2 += __shfl_xor_sync(0xffffffffu, x2, o);
+        }
+        const int c = lane < CAP ? cand[flat * CAP + lane] : -1;
+        float s = -INFINITY;
+        if (c >= 0) {
+            const float* ep = q.embed + (eh * q.K + c) * (int64_t)q.D;
+            float acc = 0.f;
+            for (int d = 0; d < q.D; ++d) acc = fmaf(__ldg(xp + d), __ldg(ep + d), acc);
+            s = vq_score(q.metric, x2, e2[eh * q.K + c], acc);
+        }
+        int bi = c >= 0 ? c : 0x7fffffff;
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {       // candidates live in lanes 0..7
+            float s2 = __shfl_xor_sync(0xffffffffu, s, o);
+            int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (s2 > s || (s2 == s && i2 < bi)) { s = s2; bi = i2; }
+        }
+        if (lane == 0) best[flat] = bi;
+    }
+}
+
+// x2 of the listed rows only (same summation order as vq_sqnorm_kernel)
+__global__ void vq_sqnorm_list_kernel(VqView q, const int32_t* __restrict__ list,
+                                      const int32_t* __restrict__ count, float* __restrict__ x2) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int total = *count;
+    for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < total; w += nwarps) {
+        const int64_t flat = list[w];
+        const int64_t h = flat / q.rows, m = flat - h * q.rows;
+        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
+        float s = 0.f;
+        for (int d = lane; d < q.D; d += 32) { float t = __ldg(xp + d); s = fmaf(t, t, s); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) x2[flat] = s;
+    }
+}
+
+__global__ void vq_tc_stats_kernel(const int32_t* __restrict__ counters, int64_t* __restrict__ stats) {
+    stats[0] = counters[0];
+    stats[1] = counters[1];
+}
+
+struct Plan {
+    int n_tiles, kcn, sb, sa;
+    bool resident;
+    size_t smem, img_bytes, ne2_bytes;
+};
+
+static bool make_plan(const VqView& q, Plan& pl) {
+    pl.n_tiles = (q.K + BN - 1) / BN;
+    pl.kcn = (q.D + BK - 1) / BK;
+    const size_t avail = SMEM_MAX - SMEM_EXTRA - 1024;
+    const size_t a_res = (size_t)pl.kcn * A_CHUNK_BYTES;
+    pl.resident = pl.kcn <= MAX_KC && a_res + 2 * (size_t)B_STAGE_BYTES <= avail;
+    if (pl.resident) {
+        pl.sa = 0;
+        size_t sb = (avail - a_res) / B_STAGE_BYTES;
+        pl.sb = (int)(sb > 4 ? 4 : sb);
+    } else {
+        pl.sa = 4;
+        pl.sb = 4;
+    }
+    const size_t a_bytes = pl.resident ? a_res : (size_t)pl.sa * A_CHUNK_BYTES;
+    pl.smem = a_bytes + (size_t)pl.sb * B_STAGE_BYTES + SMEM_EXTRA + 1024;
+    pl.img_bytes = (size_t)q.embed_heads * pl.n_tiles * pl.kcn * B_STAGE_BYTES;
+    pl.ne2_bytes = (size_t)q.embed_heads * pl.n_tiles * BN * 4;
+    return pl.smem <= SMEM_MAX;
+}
+
+}  // namespace tc
+
+bool vq_tc_supported(const VqView& q) {
+    tc::Plan pl;
+    const bool aligned = q.D % 4 == 0 && q.x_row_stride % 4 == 0 && q.x_head_stride % 4 == 0 &&
+                         (reinterpret_cast<uintptr_t>(q.x) & 15) == 0;
+    return aligned && q.D >= 16 && q.K >= 1 && tc::make_plan(q, pl);
+}
+
+int vq_assign_tc_workspace(const VqView& q, size_t* bytes) {
+    tc::Plan pl;
+    if (!tc::make_plan(q, pl)) return STEMGNN_EUNSUPPORTED;
+    const size_t items = (size_t)(q.heads * q.rows);
+    size_t b = 0;
+    b += align_up(pl.img_bytes, 1024);
+    b += align_up(pl.ne2_bytes, 256);
+    b += align_up((size_t)q.embed_heads * 4 + 16, 256);      // emax2 bits + counters
+    b += align_up(items * tc::CAP * 4, 256);                 // candidates
+    b += 2 * align_up(items * 4, 256);                       // multi list, fallback list
+    *bytes = b + 1024;
+    return STEMGNN_OK;
+}
+
+int vq_assign_tc(const VqView& q, const float* x2, const float* e2, int32_t* best, int64_t* stats,
+                 void* ws_ptr, size_t ws_bytes, cudaStream_t stream) {
+    using namespace tc;
+    Plan pl;
+    if (!make_plan(q, pl)) {
+        set_error("vq_assign_tc: shape does not fit the tcgen05 plan");
+        return STEMGNN_EUNSUPPORTED;
+    }
+    size_t need = 0;
+    vq_assign_tc_workspace(q, &need);
+    if (ws_ptr == nullptr || ws_bytes < need) {
+        set_error("vq_assign_tc: workspace too small (%zu < %zu)", ws_bytes, need);
+        return STEMGNN_ENOMEM_WS;
+    }
+    // 1024-byte alignment for the bulk-copy source images
+    char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws_ptr) + 1023) & ~(uintptr_t)1023);
+    Workspace ws(base, ws_bytes - (size_t)(base - reinterpret_cast<char*>(ws_ptr)));
+    const size_t items = (size_t)(q.heads * q.rows);
+    __nv_bfloat16* img = reinterpret_cast<__nv_bfloat16*>(ws.take<char>(align_up(pl.img_bytes, 1024)));
+    float* ne2 = ws.take<float>(pl.ne2_bytes / 4);
+    uint32_t* small = ws.take<uint32_t>((size_t)q.embed_heads + 4);
+    int32_t* cand = ws.take<int32_t>(items * CAP);
+    int32_t* multi_list = ws.take<int32_t>(items);
+    int32_t* fb_list = ws.take<int32_t>(items);
+    uint32_t* emax2 = small + 4;
+    int32_t* counters = reinterpret_cast<int32_t*>(small);
+    cudaMemsetAsync(small, 0, ((size_t)q.embed_heads + 4) * 4, stream);
+
+    const int64_t img_threads = (int64_t)q.embed_heads * pl.n_tiles * pl.kcn * BN * 8;
+    SG_LAUNCH(vq_tc_image_kernel<<<(unsigned)((img_threads + 255) / 256), 256, 0, stream>>>(
+        q.embed, q.embed_heads, q.K, q.D, pl.n_tiles, pl.kcn, img));
+    const int64_t ne2_threads = (int64_t)q.embed_heads * pl.n_tiles * BN;
+    SG_LAUNCH(vq_tc_ne2_kernel<<<(unsigned)((ne2_threads + 255) / 256), 256, 0, stream>>>(
+        e2, q.embed_heads, q.K, pl.n_tiles, q.metric, ne2, emax2));
+
+    TcParams p;
+    p.x = q.x; p.x_row_stride = q.x_row_stride; p.x_head_stride = q.x_head_stride;
+    p.heads = q.heads; p.embed_heads = q.embed_heads; p.rows = q.rows;
+    p.K = q.K; p.D = q.D; p.n_tiles = pl.n_tiles; p.kcn = pl.kcn; p.sb = pl.sb; p.sa = pl.sa;
+    p.img = img; p.ne2 = ne2; p.emax2_bits = emax2;
+    // |bf16 dot - fp32 chain dot| <= (2^-8 + D 2^-23) |x||e| (5% margin); the Euclidean score adds
+    // fp32 roundings of x2 + e2 - 2 dot, a few ulps of (x2 + e2): 2^-21 (x2 + e2max) covers them
+    p.c1 = 1.05f * (0.00390625f + (float)q.D * 1.1920929e-7f);
+    p.c2 = q.metric == 0 ? 4.76837158e-7f : 0.f;
+    p.best = best; p.cand = cand; p.multi_list = multi_list; p.fb_list = fb_list; p.counters = counters;
+
+    const int64_t n_items = ((q.rows + BM - 1) / BM) * q.heads;
+    const int grid = (int)(n_items < sm_count() ? n_items : sm_count());
+    cudaError_t e;
+    if (pl.resident) {
+        e = cudaFuncSetAttribute(vq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+        if (e == cudaSuccess) SG_LAUNCH(vq_tc_kernel<true><<<grid, NUM_THREADS, pl.smem, stream>>>(p));
+    } else {
+        e = cudaFuncSetAttribute(vq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem);
+        if (e == cudaSuccess) SG_LAUNCH(vq_tc_kernel<false><<<grid, NUM_THREADS, pl.smem, stream>>>(p));
+    }
+    if (e != cudaSuccess) {
+        set_error("vq_assign_tc: cudaFuncSetAttribute(%zu B smem): %s", pl.smem, cudaGetErrorString(e));
+        return STEMGNN_ECUDA;
+    }
+    const int rgrid = sm_count() * 8;
+    SG_LAUNCH(vq_rescore_kernel<<<rgrid, 256, 0, stream>>>(q, e2, multi_list, counters, cand, best));
+    // exact re-scan of rows whose candidate list overflowed (normally none)
+    SG_LAUNCH(vq_sqnorm_list_kernel<<<sm_count() * 4, 256, 0, stream>>>(q, fb_list, counters + 1,
+                                                                        const_cast<float*>(x2)));
+    dim3 fgrid((unsigned)(sm_count() * 2), 1);
+    SG_LAUNCH(vq_scan_kernel<<<fgrid, 256, 0, stream>>>(q, x2, e2, fb_list, counters + 1, best));
+    if (stats) SG_LAUNCH(vq_tc_stats_kernel<<<1, 1, 0, stream>>>(counters, stats));
+    cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) {
+        set_error("vq_assign_tc: CUDA error %s", cudaGetErrorString(le));
+        return STEMGNN_ECUDA;
+    }
+    return STEMGNN_OK;
+}
+
 }  // namespace stemgnn
