@@ -106,10 +106,12 @@ int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t 
  * metric 0: euclidean, argmax of -sqrt(clamp((x2 + e2) + (-2 x.e), 0)), first index on ties;
  * metric 1: dot / cosine, argmax of x.e (the caller l2-normalises, model/vq.py:891).
  * sq_err[h] (fp64) = sum over (m,d) of (quantize - x)^2, reduced in a fixed order.
- * path 0 = auto, 1 = exact fp32 CUDA-core scan, 2 = tcgen05 bf16 GEMM + fp32 rescoring of every
- * candidate inside a rigorous bf16 error band (same answer as path 1 up to fp32 dot-product
- * summation order).  stats (optional, int64[4], device): rows whose winner came from the
- * rescoring set (>1 candidate), rows that fell back to a full fp32 scan, 0, 0. */
+ * path 0 = auto, 1 = exact fp32 CUDA-core scan, 2 = tcgen05 fp16 GEMM with a rigorous
+ * per-row error band: rows whose band holds one code are final, the others are re-scored in
+ * fp32 over the codes inside the band (same formula, first index on ties), so path 2 returns
+ * the fp32 answer up to the summation order of the dot product.  stats (optional, int64[4],
+ * device): [0] rows decided by fp32 re-scoring of a candidate list, [1] rows that needed an
+ * exact scan over all codes (candidate overflow / |x| outside the fp16 range), [2..3] = 0. */
 typedef struct {
     const float* x; int64_t x_row_stride, x_head_stride;
     const float* embed;

@@ -29,13 +29,15 @@ __global__ void vq_sqnorm_kernel(const float* v, int64_t rows, int64_t heads, in
                                  int64_t row_stride, int64_t head_stride, float* out);
 __global__ void vq_scan_kernel(VqView q, const float* x2, const float* e2, const int32_t* row_list,
                                const int32_t* row_count, int32_t* best_out);
-__global__ void vq_gather_kernel(VqView q, const int32_t* best, double* partials);
+__global__ void vq_gather_kernel(VqView q, const int32_t* best, const int32_t* cand, const float* e2,
+                                 double* partials, unsigned long long* stats);
+constexpr int VQ_CAND_CAP = 8;   // candidate slots per row written by the tcgen05 path
 __global__ void vq_sqerr_reduce_kernel(const double* partials, int nblk, double* sq_err);
 
 // path 2 (k3_vq_tc.cu): returns 0 on success
 bool vq_tc_supported(const VqView& q);
 int vq_assign_tc_workspace(const VqView& q, size_t* bytes);
-int vq_assign_tc(const VqView& q, const float* x2, const float* e2, int32_t* best, int64_t* stats,
-                 void* ws, size_t ws_bytes, cudaStream_t stream);
+int vq_assign_tc(const VqView& q, const float* e2, int32_t* best, int32_t** cand_out, void* ws,
+                 size_t ws_bytes, cudaStream_t stream);
 
 }  // namespace stemgnn

@@ -32,7 +32,7 @@ int make_view(const stemgnn_vq_assign_args* a, VqView& q, VqPlan& p) {
     p.path = a->path;
     if (p.path == 0) p.path = vq_tc_supported(q) ? 2 : 1;
     if (p.path == 2 && !vq_tc_supported(q)) {
-        set_error("stemgnn_vq_assign: path 2 (tcgen05) needs dim %% 16 == 0, dim <= 1024 and 16-byte aligned rows");
+        set_error("stemgnn_vq_assign: path 2 (tcgen05) needs dim %% 4 == 0, dim >= 16 and 16-byte aligned rows");
         return STEMGNN_EUNSUPPORTED;
     }
     return STEMGNN_OK;
@@ -93,18 +93,21 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
     const int64_t ek = q.embed_heads * (int64_t)q.K;
     SG_LAUNCH(vq_sqnorm_kernel<<<(unsigned)((ek * 32 + 255) / 256), 256, 0, stream>>>(
         q.embed, ek, 1, q.D, q.D, 0, e2));
-    if (q.metric == 0)
-        SG_LAUNCH(vq_sqnorm_kernel<<<(unsigned)((p.items * 32 + 255) / 256), 256, 0, stream>>>(
-            q.x, q.rows, q.heads, q.D, q.x_row_stride, q.x_head_stride, x2));
+    int32_t* cand = nullptr;
     if (p.path == 1) {
+        if (q.metric == 0)
+            SG_LAUNCH(vq_sqnorm_kernel<<<(unsigned)((p.items * 32 + 255) / 256), 256, 0, stream>>>(
+                q.x, q.rows, q.heads, q.D, q.x_row_stride, q.x_head_stride, x2));
         dim3 grid((unsigned)((q.rows + 63) / 64), (unsigned)q.heads);
         SG_LAUNCH(vq_scan_kernel<<<grid, 256, 0, stream>>>(q, x2, e2, nullptr, nullptr, best));
     } else {
-        rc = vq_assign_tc(q, x2, e2, best, a->stats, ws.base + ws.off, workspace_bytes - ws.off, stream);
+        rc = vq_assign_tc(q, e2, best, &cand, ws.base + ws.off, workspace_bytes - ws.off, stream);
         if (rc) return rc;
     }
     dim3 ggrid((unsigned)p.nblk, (unsigned)q.heads);
-    SG_LAUNCH(vq_gather_kernel<<<ggrid, 256, 0, stream>>>(q, best, a->sq_err ? partials : nullptr));
+    SG_LAUNCH(vq_gather_kernel<<<ggrid, 256, 0, stream>>>(
+        q, best, cand, e2, a->sq_err ? partials : nullptr,
+        reinterpret_cast<unsigned long long*>(a->stats)));
     if (a->sq_err)
         SG_LAUNCH(vq_sqerr_reduce_kernel<<<(unsigned)q.heads, 256, 0, stream>>>(partials, (int)p.nblk, a->sq_err));
     SG_CHECK_LAUNCH();

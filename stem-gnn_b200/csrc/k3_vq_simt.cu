@@ -133,18 +133,64 @@ vq_scan_kernel(VqView q, const float* __restrict__ x2, const float* __restrict__
 // ---- gather + commitment partial: one warp per (head,row) --------------------------------------
 // quantize(h,m,:) = embed[eh, best, :]; ind(h,m) = best; partials[h*nblk + blockIdx.x] = sum (q-x)^2
 // over this CTA's rows, reduced in a fixed order (shuffle tree, then warps in index order).
+// Rows the tcgen05 path left open are settled here first, while the warp holds the row anyway:
+// best == -1: re-score the row's candidate list (cand[flat][0..CAP), -1 padded) with the
+// reference's fp32 formula; best == -2: exact scan over all K codes.  First index wins ties.
+__device__ __forceinline__ float warp_dot(const float* __restrict__ a, const float* __restrict__ b,
+                                          int D, bool vec4, int lane) {
+    float s = 0.f;
+    if (vec4) {
+        for (int d = lane * 4; d < D; d += 128) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(a + d));
+            const float4 w = __ldg(reinterpret_cast<const float4*>(b + d));
+            s = fmaf(u.x, w.x, s); s = fmaf(u.y, w.y, s); s = fmaf(u.z, w.z, s); s = fmaf(u.w, w.w, s);
+        }
+    } else {
+        for (int d = lane; d < D; d += 32) s = fmaf(__ldg(a + d), __ldg(b + d), s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    return s;
+}
+
 __global__ void __launch_bounds__(256)
-vq_gather_kernel(VqView q, const int32_t* __restrict__ best, double* __restrict__ partials) {
+vq_gather_kernel(VqView q, const int32_t* __restrict__ best, const int32_t* __restrict__ cand,
+                 const float* __restrict__ e2, double* __restrict__ partials,
+                 unsigned long long* __restrict__ stats) {
     __shared__ double wsum[8];
     const int w = threadIdx.x >> 5, lane = lane_id();
     const int64_t h = blockIdx.y;
     const int64_t m = (int64_t)blockIdx.x * 8 + w;
     double part = 0.0;
     if (m < q.rows) {
-        const int b = best[h * q.rows + m];
+        const int64_t flat = h * q.rows + m;
+        int b = best[flat];
         const int64_t eh = q.embed_heads == 1 ? 0 : h;
-        const float* e = q.embed + (eh * q.K + b) * (int64_t)q.D;
         const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
+        if (b < 0) {
+            const float* E = q.embed + eh * (int64_t)q.K * q.D;
+            const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
+            const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
+            float bs = -INFINITY;
+            int bi = 0x7fffffff;
+            if (b == -1) {
+                for (int j = 0; j < VQ_CAND_CAP; ++j) {
+                    const int c = cand[flat * VQ_CAND_CAP + j];
+                    if (c < 0) break;
+                    const float s = vq_score(q.metric, x2, e2[eh * q.K + c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
+                    if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
+                }
+                if (lane == 0 && stats) atomicAdd(stats + 0, 1ull);
+            } else {
+                for (int c = 0; c < q.K; ++c) {
+                    const float s = vq_score(q.metric, x2, e2[eh * q.K + c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
+                    if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
+                }
+                if (lane == 0 && stats) atomicAdd(stats + 1, 1ull);
+            }
+            b = bi < q.K ? bi : 0;     // all-NaN rows: argmax of NaNs is index 0
+        }
+        const float* e = q.embed + (eh * q.K + b) * (int64_t)q.D;
         float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
         float s = 0.f;
         for (int d = lane; d < q.D; d += 32) {

@@ -5,25 +5,31 @@
 // STEM-GNN/model/vq.py:650,652 cosine; :472,474 Euclidean; gumbel_sample :79) without ever
 // materialising the N x K score matrix.
 //
-//   scores~ = bf16(X) . bf16(E)^T  [-  e2/2 for the Euclidean metric]      (tensor cores)
+//   scores~ = S * fp16(X) . fp16(E / S)^T  [-  e2/2 for the Euclidean metric]   (tensor cores)
+//
+// fp16 operands (11-bit significand, same kind::f16 rate as bf16) keep the error band 8x
+// tighter than bf16 would; S is a per-codebook power of two that maps max|e| to [2^13, 2^14).
 //
 // A persistent CTA owns a 128-row tile of X.  Four producer warps read the fp32 rows with
-// 128-bit loads, round to bf16 and store them K-major / 128B-swizzled in shared memory (the
+// 128-bit loads, round to fp16 and store them K-major / 128B-swizzled in shared memory (the
 // canonical UMMA operand layout) -- X is read from HBM exactly once, as fp32.  The codebook is
 // pre-converted once per call into the same swizzled tile image in global memory, so one
 // elected thread streams it with 1-D bulk async copies (cp.async.bulk -> mbarrier complete_tx)
 // through a ring of 32 KB stages.  One elected thread issues tcgen05.mma (M=128, N<=256, K=16,
-// bf16 -> fp32) into a double-buffered 2 x 256-column TMEM accumulator; four epilogue warps read
+// f16 -> fp32) into a double-buffered 2 x 256-column TMEM accumulator; four epilogue warps read
 // the accumulator with tcgen05.ld (one row per thread), add -e2/2 and keep the running best
 // score plus every code within a rigorous error band of it.
 //
-// Parity: bf16 rounding perturbs a dot product by at most 2^-8 |x||e| (plus fp32 accumulation
-// slop), so the exact fp32 winner is always inside the band.  Rows whose band holds a single
-// code are final; the others (typically a few codes) are re-scored by vq_rescore_kernel with
-// the *same* fp32 formula and summation order as the exact scan (k3_vq_simt.cu), first index
-// winning ties -- the result is identical to path 1.  A row whose candidate list overflows is
-// re-scanned exactly.  FLOPs: 2*N*K*D on the tensor pipe; HBM: N*D*4 B (x) + N*4 B (best).
-#include <cuda_bf16.h>
+// Parity: with x~ = fp16(x), e~ = S fp16(e/S) the tensor-core dot differs from the exact one by
+// at most |x - x~||e| + |x~||e - e~| (+ fp32 accumulation slop); both residual norms are
+// MEASURED (producers / prep kernel), not bounded a priori, so the band is rigorous and tight
+// (~2^-10 |x||e|).  The fp32 winner is always inside [best~ - band, best~].  Rows whose band
+// holds a single code are final; the others get best = -1 and their candidate list, and the
+// gather kernel (k3_vq_simt.cu) re-scores those few codes with the reference's fp32 formula,
+// first index winning ties.  A row whose list overflows (or with |x| >= 2^15, outside the fp16
+// range) gets best = -2 and is re-scanned exactly there.
+// FLOPs: 2*N*K*D on the tensor pipe; HBM: N*D*4 B (x) + N*4 B (best).
+#include <cuda_fp16.h>
 
 #include "k3_vq_common.cuh"
 
@@ -35,12 +41,12 @@ constexpr int BN = 256;                    // codes per accumulator tile = max U
 constexpr int BK = 64;                     // bf16 columns per smem chunk (one 128 B swizzle row)
 constexpr int A_CHUNK_BYTES = BM * 128;    // 16 KB
 constexpr int B_STAGE_BYTES = BN * 128;    // 32 KB
-constexpr int CAP = 8;                     // candidates kept per row
+constexpr int CAP = VQ_CAND_CAP;           // candidates kept per row
 constexpr int NUM_THREADS = 320;           // warps 0-3 epilogue, 4-7 producers, 8 loader, 9 MMA
 constexpr int PROD_WARP0 = 4, LOAD_WARP = 8, MMA_WARP = 9;
 constexpr int MAX_KC = 16;                 // a_full barriers (resident: D <= 1024; ring: stages)
 constexpr int MAX_SB = 6;
-constexpr int SMEM_EXTRA = 4 * BN * 4 + 4 * BM * 4 + 64 * 8 + 16;   // ne2 slices, x2 ring, barriers
+constexpr int SMEM_EXTRA = 4 * BN * 4 + 4 * BM * 4 + 64 * 8 + 16;   // ne2 slices, band ring, barriers
 constexpr int SMEM_MAX = 232448;           // 227 KB opt-in limit per CTA
 
 // ---------------------------------------------------------------------------------- PTX
@@ -104,8 +110,8 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {   // arrives when pr
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                  : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, fp32 accumulate, M x N x 16
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+// D[tmem] (+)= A[smem] * B[smem]^T, 16-bit inputs, fp32 accumulate, M x N x 16
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
                                           uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -117,9 +123,10 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr) {
     return (uint64_t)((addr >> 4) & 0x3FFFu) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
-// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, N at [17,23), M at [24,29)
+// kind::f16 instruction descriptor: D fp32 (bit 4), A/B fp16 (format 0), both K-major,
+// N>>3 at [17,23), M>>4 at [24,29)
 __device__ __forceinline__ uint32_t make_idesc(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t addr, float* v) {
     uint32_t* r = reinterpret_cast<uint32_t*>(v);
@@ -147,13 +154,12 @@ struct TcParams {
     int n_tiles, kcn;                // code tiles of 256, 64-column chunks
     int sb;                          // B ring stages
     int sa;                          // A ring stages (ring mode only)
-    const __nv_bfloat16* img;        // [embed_heads][n_tiles][kcn][256 x 64] swizzled tile images
+    const __half* img;               // [embed_heads][n_tiles][kcn][256 x 64] swizzled tile images
     const float* ne2;                // [embed_heads][n_tiles*256]: -e2/2 | 0, padded with -inf
-    const uint32_t* emax2_bits;      // [embed_heads] max e2 as float bits
-    float c1, c2;                    // band = c1*|x|*emax + c2*(x2 + e2max)
-    int32_t* best;                   // [heads*rows]
-    int32_t* cand;                   // [heads*rows][CAP]
-    int32_t* multi_list; int32_t* fb_list; int32_t* counters;   // [0]=multi, [1]=fallback
+    const uint32_t* head_stats;      // [embed_heads][4] float bits: max|e|, max e2, max |e - e~|^2, S
+    float c_acc, c2;                 // band = 2(rx*emax + 1.001|x|*remax + c_acc*|x|*emax) + c2*(x2+e2max)
+    int32_t* best;                   // [heads*rows]: code, -1 (see cand) or -2 (exact re-scan)
+    int32_t* cand;                   // [heads*rows][CAP], -1 padded
 };
 
 __device__ __forceinline__ int tile_codes32(const TcParams& p, int n) {
@@ -172,16 +178,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     uint8_t* sA = smem;
     uint8_t* sB = sA + (size_t)a_slots * A_CHUNK_BYTES;
     float* s_ne2 = reinterpret_cast<float*>(sB + (size_t)p.sb * B_STAGE_BYTES);   // [4][256]
-    float* s_x2 = s_ne2 + 4 * BN;                                                  // [4][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_x2 + 4 * BM);
+    float* s_band = s_ne2 + 4 * BN;                                                // [4][128]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_band + 4 * BM);
     uint64_t* a_full = bars;                 // [MAX_KC]
     uint64_t* a_empty = bars + MAX_KC;       // [MAX_KC] (resident mode uses [0])
     uint64_t* b_full = bars + 2 * MAX_KC;    // [MAX_SB]
     uint64_t* b_empty = b_full + MAX_SB;     // [MAX_SB]
     uint64_t* t_full = b_empty + MAX_SB;     // [2]
     uint64_t* t_empty = t_full + 2;          // [2]
-    uint64_t* x2_full = t_empty + 2;         // [4]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x2_full + 4);
+    uint64_t* band_full = t_empty + 2;         // [4]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(band_full + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row_tiles = (p.rows + BM - 1) / BM;
@@ -191,7 +197,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
         for (int i = 0; i < MAX_KC; ++i) { mbar_init(smem_u32(a_full + i), BM); mbar_init(smem_u32(a_empty + i), 1); }
         for (int i = 0; i < MAX_SB; ++i) { mbar_init(smem_u32(b_full + i), 1); mbar_init(smem_u32(b_empty + i), 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), BM); }
-        for (int i = 0; i < 4; ++i) mbar_init(smem_u32(x2_full + i), BM);
+        for (int i = 0; i < 4; ++i) mbar_init(smem_u32(band_full + i), BM);
         fence_barrier_init();
     }
     if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -250,7 +256,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                         const uint64_t b_desc = smem_desc_sw128(smem_u32(sB + (size_t)sb * B_STAGE_BYTES));
                         const int ksteps = kc == p.kcn - 1 ? last_ksteps : BK / 16;
                         for (int k = 0; k < ksteps; ++k)   // +32 B along K inside the swizzle row
-                            umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                            umma_f16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
                                       (uint32_t)((kc | k) != 0));
                         umma_commit(smem_u32(b_empty + sb));
                         if (!RESIDENT) { umma_commit(smem_u32(a_empty + it_a % (uint32_t)p.sa)); ++it_a; }
@@ -261,18 +267,19 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
             }
         }
     } else if (warp >= PROD_WARP0) {
-        // ================= producers: fp32 rows -> bf16, swizzled K-major A chunks =================
+        // ================= producers: fp32 rows -> fp16, swizzled K-major A chunks =================
         const int pt = threadIdx.x - PROD_WARP0 * 32;       // 0..127
         const int q = pt & 15, rg = pt >> 4;                // float4 slot in the chunk, row in the atom
         const uint32_t soff = (uint32_t)(rg * 128 + (((q >> 1) ^ rg) << 4) + (q & 1) * 8);
         uint32_t it_a = 0, tile_it = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int64_t h = item / row_tiles, mt = item - h * row_tiles;
+            const int64_t eh = p.embed_heads == 1 ? 0 : h;
             const int64_t row0 = mt * BM;
             const float* xb = p.x + h * p.x_head_stride;
-            float sq[16];
+            float sq[16], rq[16];       // |x|^2 and |x - fp16(x)|^2 of this thread's slice of 16 rows
 #pragma unroll
-            for (int i = 0; i < 16; ++i) sq[i] = 0.f;
+            for (int i = 0; i < 16; ++i) { sq[i] = 0.f; rq[i] = 0.f; }
             if (RESIDENT) mbar_wait(smem_u32(a_empty), (tile_it & 1u) ^ 1u);
             const int n_pass = RESIDENT ? 1 : p.n_tiles;
             for (int n = 0; n < n_pass; ++n) {
@@ -296,32 +303,49 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                     uint8_t* dst = sA + (size_t)slot * A_CHUNK_BYTES + soff;
 #pragma unroll
                     for (int i = 0; i < 16; ++i) {
-                        __nv_bfloat162 lo = __floats2bfloat162_rn(v[i].x, v[i].y);
-                        __nv_bfloat162 hi = __floats2bfloat162_rn(v[i].z, v[i].w);
+                        const __half2 lo = __floats2half2_rn(v[i].x, v[i].y);
+                        const __half2 hi = __floats2half2_rn(v[i].z, v[i].w);
                         uint2 pk;
-                        pk.x = *reinterpret_cast<uint32_t*>(&lo);
-                        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+                        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
                         *reinterpret_cast<uint2*>(dst + i * 1024) = pk;
                         if (n == 0) {
-                            sq[i] = fmaf(v[i].x, v[i].x, sq[i]); sq[i] = fmaf(v[i].y, v[i].y, sq[i]);
-                            sq[i] = fmaf(v[i].z, v[i].z, sq[i]); sq[i] = fmaf(v[i].w, v[i].w, sq[i]);
+                            const float2 fl = __half22float2(lo), fh = __half22float2(hi);
+                            float d;
+                            sq[i] = fmaf(v[i].x, v[i].x, sq[i]); d = v[i].x - fl.x; rq[i] = fmaf(d, d, rq[i]);
+                            sq[i] = fmaf(v[i].y, v[i].y, sq[i]); d = v[i].y - fl.y; rq[i] = fmaf(d, d, rq[i]);
+                            sq[i] = fmaf(v[i].z, v[i].z, sq[i]); d = v[i].z - fh.x; rq[i] = fmaf(d, d, rq[i]);
+                            sq[i] = fmaf(v[i].w, v[i].w, sq[i]); d = v[i].w - fh.y; rq[i] = fmaf(d, d, rq[i]);
                         }
                     }
                     fence_async_smem();
                     mbar_arrive(smem_u32(a_full + slot));
                     if (n == 0 && kc == p.kcn - 1) {
-                        // squared row norms for the error band -> x2 ring (4 deep, see epilogue)
-                        float* x2d = s_x2 + (tile_it & 3u) * BM;
+                        // per-row error band -> band ring (4 deep: the epilogue of tile t-4 has
+                        // finished before the producers of tile t can run)
+                        const float emax = sqrtf(__uint_as_float(__ldg(p.head_stats + eh * 4 + 1)));
+                        const float e2max = __uint_as_float(__ldg(p.head_stats + eh * 4 + 1));
+                        const float remax = sqrtf(__uint_as_float(__ldg(p.head_stats + eh * 4 + 2)));
+                        float* bd = s_band + (tile_it & 3u) * BM;
 #pragma unroll
                         for (int i = 0; i < 16; ++i) {
-                            float s = sq[i];
-                            s += __shfl_xor_sync(0xffffffffu, s, 1);
-                            s += __shfl_xor_sync(0xffffffffu, s, 2);
-                            s += __shfl_xor_sync(0xffffffffu, s, 4);
-                            s += __shfl_xor_sync(0xffffffffu, s, 8);
-                            if (q == 0) x2d[rg + 8 * i] = s;
+                            float s = sq[i], r = rq[i];
+#pragma unroll
+                            for (int o = 1; o < 16; o <<= 1) {
+                                s += __shfl_xor_sync(0xffffffffu, s, o);
+                                r += __shfl_xor_sync(0xffffffffu, r, o);
+                            }
+                            if (q == 0) {
+                                const float xn = sqrtf(s);
+                                float b = 2.f * (1.001f * sqrtf(r) * emax + 1.001f * xn * remax + p.c_acc * xn * emax) +
+                                          p.c2 * (s + e2max);
+                                // |x| >= 2^15 could overflow fp16: an infinite band sends the row
+                                // to the exact re-scan (NaN/Inf rows end there as well)
+                                if (!(s < 1073741824.f)) b = INFINITY;
+                                bd[rg + 8 * i] = b;
+                            }
                         }
-                        mbar_arrive(smem_u32(x2_full + (tile_it & 3u)));
+                        mbar_arrive(smem_u32(band_full + (tile_it & 3u)));
                     }
                 }
             }
@@ -336,6 +360,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
             const int64_t eh = p.embed_heads == 1 ? 0 : h;
             const int64_t m = mt * BM + row_in_tile;
             const float* ne2g = p.ne2 + eh * (int64_t)p.n_tiles * BN;
+            const float scale = __uint_as_float(__ldg(p.head_stats + eh * 4 + 3));
             float rb = -INFINITY, thr = -INFINITY, band = 0.f;
             float cv[CAP];
             int ci[CAP];
@@ -348,14 +373,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                 for (int j = 0; j < BN / 32; ++j) ne2s[j * 32 + lane] = __ldg(ne2g + n * BN + j * 32 + lane);
                 __syncwarp();
                 const uint32_t st = acc_it & 1u;
+                if (n == 0) {
+                    mbar_wait(smem_u32(band_full + (tile_it & 3u)), (tile_it >> 2) & 1u);
+                    band = s_band[(tile_it & 3u) * BM + row_in_tile];
+                }
                 mbar_wait(smem_u32(t_full + st), (acc_it >> 1) & 1u);
                 tc_fence_after();
-                if (n == 0) {
-                    mbar_wait(smem_u32(x2_full + (tile_it & 3u)), (tile_it >> 2) & 1u);
-                    const float xx = s_x2[(tile_it & 3u) * BM + row_in_tile];
-                    const float e2m = __uint_as_float(__ldg(p.emax2_bits + eh));
-                    band = p.c1 * sqrtf(xx) * sqrtf(e2m) + p.c2 * (xx + e2m);
-                }
                 const uint32_t t_addr = tmem_base + ((uint32_t)(warp * 32) << 16) + st * BN;
                 for (int c0 = 0; c0 < ncols; c0 += 32) {
                     float v[32];
@@ -366,14 +389,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                         float mx = -INFINITY;
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
-                            v[g * 8 + i] += ne2s[c0 + g * 8 + i];
+                            v[g * 8 + i] = fmaf(v[g * 8 + i], scale, ne2s[c0 + g * 8 + i]);
                             mx = fmaxf(mx, v[g * 8 + i]);
                         }
                         if (mx >= thr) {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 const float s = v[g * 8 + i];
-                                if (s >= thr) {
+                                if (s >= thr && !overflow) {
                                     if (s > rb) { rb = s; thr = rb - band; }
                                     if (nc == CAP) {       // compact against the current threshold
                                         int keep = 0;
@@ -399,14 +422,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                 for (int j = 0; j < nc; ++j)
                     if (cv[j] >= thr) { only = ci[j]; p.cand[flat * CAP + keep] = ci[j]; ++keep; }
                 if (overflow || keep == 0) {
-                    p.best[flat] = -1;
-                    p.fb_list[atomicAdd(p.counters + 1, 1)] = (int32_t)flat;
+                    p.best[flat] = -2;
                 } else if (keep == 1) {
                     p.best[flat] = only;
                 } else {
                     for (int j = keep; j < CAP; ++j) p.cand[flat * CAP + j] = -1;
                     p.best[flat] = -1;
-                    p.multi_list[atomicAdd(p.counters + 0, 1)] = (int32_t)flat;
                 }
             }
         }
@@ -417,10 +438,34 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     if (warp == MMA_WARP) tmem_dealloc(tmem_base, 512);
 }
 
-// -------------------------------------------------------------------------- codebook image
-// One thread per 16-byte chunk (8 bf16) of the swizzled tile image; padding is zero.
+// -------------------------------------------------------------------------- codebook prep
+// head_stats[eh] = {max|e|, max e2, max |e - e~|^2, S} as float bits (all >= 0: uint order ==
+// float order, so atomicMax works).  S = 2^(floor(log2 max|e|) - 13) puts max|e|/S in
+// [2^13, 2^14): no fp16 overflow, and elements down to 2^-28 max|e| stay normal.
+__global__ void vq_tc_maxabs_kernel(const float* __restrict__ embed, int64_t embed_heads, int K, int D,
+                                    uint32_t* __restrict__ head_stats) {
+    const int64_t gw = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= embed_heads * K) return;
+    const float* e = embed + gw * D;
+    float m = 0.f;
+    for (int d = lane_id(); d < D; d += 32) m = fmaxf(m, fabsf(__ldg(e + d)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane_id() == 0) atomicMax(head_stats + (gw / K) * 4 + 0, __float_as_uint(m));
+}
+
+__device__ __forceinline__ float head_scale(const uint32_t* head_stats, int64_t eh) {
+    const float m = __uint_as_float(head_stats[eh * 4 + 0]);
+    if (!(m > 0.f) || !(m < INFINITY)) return 1.f;
+    int ex = ilogbf(m) - 13;
+    ex = ex < -100 ? -100 : (ex > 100 ? 100 : ex);
+    return ldexpf(1.f, ex);
+}
+
+// One thread per 16-byte chunk (8 fp16) of the swizzled tile image; padding is zero.
 __global__ void vq_tc_image_kernel(const float* __restrict__ embed, int64_t embed_heads, int K, int D,
-                                   int n_tiles, int kcn, __nv_bfloat16* __restrict__ img) {
+                                   int n_tiles, int kcn, const uint32_t* __restrict__ head_stats,
+                                   __half* __restrict__ img) {
     const int64_t total = embed_heads * n_tiles * (int64_t)kcn * BN * 8;
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= total) return;
@@ -430,99 +475,52 @@ __global__ void vq_tc_image_kernel(const float* __restrict__ embed, int64_t embe
     const int kc = (int)(tile % kcn);
     const int n = (int)((tile / kcn) % n_tiles);
     const int64_t eh = tile / kcn / n_tiles;
+    const float inv = 1.f / head_scale(head_stats, eh);     // power of two: exact
     const int code = n * BN + r, col = kc * BK + j * 8;
     float f[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
-        f[i] = (code < K && col + i < D) ? __ldg(embed + (eh * K + code) * (int64_t)D + col + i) : 0.f;
+        f[i] = (code < K && col + i < D) ? __ldg(embed + (eh * K + code) * (int64_t)D + col + i) * inv : 0.f;
     uint4 pk;
-    __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
-    __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
-    pk.x = *reinterpret_cast<uint32_t*>(&b0); pk.y = *reinterpret_cast<uint32_t*>(&b1);
-    pk.z = *reinterpret_cast<uint32_t*>(&b2); pk.w = *reinterpret_cast<uint32_t*>(&b3);
+    const __half2 b0 = __floats2half2_rn(f[0], f[1]), b1 = __floats2half2_rn(f[2], f[3]);
+    const __half2 b2 = __floats2half2_rn(f[4], f[5]), b3 = __floats2half2_rn(f[6], f[7]);
+    pk.x = *reinterpret_cast<const uint32_t*>(&b0); pk.y = *reinterpret_cast<const uint32_t*>(&b1);
+    pk.z = *reinterpret_cast<const uint32_t*>(&b2); pk.w = *reinterpret_cast<const uint32_t*>(&b3);
     const int64_t off = tile * B_STAGE_BYTES + (int64_t)(r >> 3) * 1024 + (r & 7) * 128 + ((j ^ (r & 7)) << 4);
     *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(img) + off) = pk;
 }
 
-// ne2[eh][c] = -e2/2 (Euclid) | 0 (dot) for c < K, -inf for padding; emax2 = max_c e2
-__global__ void vq_tc_ne2_kernel(const float* __restrict__ e2, int64_t embed_heads, int K, int n_tiles,
-                                 int metric, float* __restrict__ ne2, uint32_t* __restrict__ emax2_bits) {
+// One warp per (padded) code: ne2 = -e2/2 (Euclid) | 0 (dot), -inf for padding; max e2 and the
+// max squared fp16 residual |e - S fp16(e/S)|^2 go to head_stats; head_stats[3] = S.
+__global__ void vq_tc_ne2_kernel(const float* __restrict__ embed, const float* __restrict__ e2,
+                                 int64_t embed_heads, int K, int D, int n_tiles, int metric,
+                                 float* __restrict__ ne2, uint32_t* __restrict__ head_stats) {
     const int64_t kp = (int64_t)n_tiles * BN;
-    int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= embed_heads * kp) return;
-    const int64_t eh = t / kp;
-    const int c = (int)(t - eh * kp);
-    float v = -INFINITY;
-    if (c < K) {
-        const float e = e2[eh * K + c];
-        v = metric == 0 ? -0.5f * e : 0.f;
-        atomicMax(emax2_bits + eh, __float_as_uint(e));   // e2 >= 0: uint order == float order
+    const int64_t gw = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (gw >= embed_heads * kp) return;
+    const int64_t eh = gw / kp;
+    const int c = (int)(gw - eh * kp);
+    if (c >= K) {
+        if (lane_id() == 0) ne2[gw] = -INFINITY;
+        return;
     }
-    ne2[t] = v;
-}
-
-// ---------------------------------------------------------------------------- rescoring
-// One warp per row with more than one candidate: the same fp32 formula and summation order as
-// the exact scan (vq_sqnorm_kernel for x2, a sequential fmaf chain over d for the dot), first
-// index wins ties.  Lane j scores candidate j.
-__global__ void __launch_bounds__(256)
-vq_rescore_kernel(VqView q, const float* __restrict__ e2, const int32_t* __restrict__ multi_list,
-                  const int32_t* __restrict__ counters, const int32_t* __restrict__ cand,
-                  int32_t* __restrict__ best) {
-    const int lane = threadIdx.x & 31;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int total = counters[0];
-    for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < total; w += nwarps) {
-        const int64_t flat = multi_list[w];
-        const int64_t h = flat / q.rows, m = flat - h * q.rows;
-        const int64_t eh = q.embed_heads == 1 ? 0 : h;
-        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
-        float x2 = 0.f;
-        if (q.metric == 0) {
-            for (int d = lane; d < q.D; d += 32) { float t = __ldg(xp + d); x2 = fmaf(t, t, x2); }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) x2 += __shfl_xor_sync(0xffffffffu, x2, o);
-        }
-        const int c = lane < CAP ? cand[flat * CAP + lane] : -1;
-        float s = -INFINITY;
-        if (c >= 0) {
-            const float* ep = q.embed + (eh * q.K + c) * (int64_t)q.D;
-            float acc = 0.f;
-            for (int d = 0; d < q.D; ++d) acc = fmaf(__ldg(xp + d), __ldg(ep + d), acc);
-            s = vq_score(q.metric, x2, e2[eh * q.K + c], acc);
-        }
-        int bi = c >= 0 ? c : 0x7fffffff;
-#pragma unroll
-        for (int o = 4; o > 0; o >>= 1) {       // candidates live in lanes 0..7
-            float s2 = __shfl_xor_sync(0xffffffffu, s, o);
-            int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (s2 > s || (s2 == s && i2 < bi)) { s = s2; bi = i2; }
-        }
-        if (lane == 0) best[flat] = bi;
+    const float S = head_scale(head_stats, eh), inv = 1.f / S;
+    const float* e = embed + (eh * K + c) * (int64_t)D;
+    float r = 0.f;
+    for (int d = lane_id(); d < D; d += 32) {
+        const float v = __ldg(e + d);
+        const float df = v - __half2float(__float2half_rn(v * inv)) * S;
+        r = fmaf(df, df, r);
     }
-}
-
-// x2 of the listed rows only (same summation order as vq_sqnorm_kernel)
-__global__ void vq_sqnorm_list_kernel(VqView q, const int32_t* __restrict__ list,
-                                      const int32_t* __restrict__ count, float* __restrict__ x2) {
-    const int lane = threadIdx.x & 31;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int total = *count;
-    for (int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < total; w += nwarps) {
-        const int64_t flat = list[w];
-        const int64_t h = flat / q.rows, m = flat - h * q.rows;
-        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
-        float s = 0.f;
-        for (int d = lane; d < q.D; d += 32) { float t = __ldg(xp + d); s = fmaf(t, t, s); }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) x2[flat] = s;
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    if (lane_id() == 0) {
+        const float ee = e2[eh * K + c];
+        ne2[gw] = metric == 0 ? -0.5f * ee : 0.f;
+        atomicMax(head_stats + eh * 4 + 1, __float_as_uint(ee));
+        atomicMax(head_stats + eh * 4 + 2, __float_as_uint(r * 1.0001f));
+        if (c == 0) head_stats[eh * 4 + 3] = __float_as_uint(S);
     }
-}
-
-__global__ void vq_tc_stats_kernel(const int32_t* __restrict__ counters, int64_t* __restrict__ stats) {
-    stats[0] = counters[0];
-    stats[1] = counters[1];
 }
 
 struct Plan {
@@ -547,6 +545,8 @@ static bool make_plan(const VqView& q, Plan& pl) {
     }
     const size_t a_bytes = pl.resident ? a_res : (size_t)pl.sa * A_CHUNK_BYTES;
     pl.smem = a_bytes + (size_t)pl.sb * B_STAGE_BYTES + SMEM_EXTRA + 1024;
+    // at least half of the SM's shared memory: one CTA per SM (it owns all 512 TMEM columns)
+    if (pl.smem < 120 * 1024) pl.smem = 120 * 1024;
     pl.img_bytes = (size_t)q.embed_heads * pl.n_tiles * pl.kcn * B_STAGE_BYTES;
     pl.ne2_bytes = (size_t)q.embed_heads * pl.n_tiles * BN * 4;
     return pl.smem <= SMEM_MAX;
@@ -568,15 +568,14 @@ int vq_assign_tc_workspace(const VqView& q, size_t* bytes) {
     size_t b = 0;
     b += align_up(pl.img_bytes, 1024);
     b += align_up(pl.ne2_bytes, 256);
-    b += align_up((size_t)q.embed_heads * 4 + 16, 256);      // emax2 bits + counters
+    b += align_up((size_t)q.embed_heads * 16, 256);          // head_stats
     b += align_up(items * tc::CAP * 4, 256);                 // candidates
-    b += 2 * align_up(items * 4, 256);                       // multi list, fallback list
     *bytes = b + 1024;
     return STEMGNN_OK;
 }
 
-int vq_assign_tc(const VqView& q, const float* x2, const float* e2, int32_t* best, int64_t* stats,
-                 void* ws_ptr, size_t ws_bytes, cudaStream_t stream) {
+int vq_assign_tc(const VqView& q, const float* e2, int32_t* best, int32_t** cand_out, void* ws_ptr,
+                 size_t ws_bytes, cudaStream_t stream) {
     using namespace tc;
     Plan pl;
     if (!make_plan(q, pl)) {
@@ -593,33 +592,34 @@ int vq_assign_tc(const VqView& q, const float* x2, const float* e2, int32_t* bes
     char* base = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws_ptr) + 1023) & ~(uintptr_t)1023);
     Workspace ws(base, ws_bytes - (size_t)(base - reinterpret_cast<char*>(ws_ptr)));
     const size_t items = (size_t)(q.heads * q.rows);
-    __nv_bfloat16* img = reinterpret_cast<__nv_bfloat16*>(ws.take<char>(align_up(pl.img_bytes, 1024)));
+    __half* img = reinterpret_cast<__half*>(ws.take<char>(align_up(pl.img_bytes, 1024)));
     float* ne2 = ws.take<float>(pl.ne2_bytes / 4);
-    uint32_t* small = ws.take<uint32_t>((size_t)q.embed_heads + 4);
+    uint32_t* head_stats = ws.take<uint32_t>((size_t)q.embed_heads * 4);
     int32_t* cand = ws.take<int32_t>(items * CAP);
-    int32_t* multi_list = ws.take<int32_t>(items);
-    int32_t* fb_list = ws.take<int32_t>(items);
-    uint32_t* emax2 = small + 4;
-    int32_t* counters = reinterpret_cast<int32_t*>(small);
-    cudaMemsetAsync(small, 0, ((size_t)q.embed_heads + 4) * 4, stream);
+    *cand_out = cand;
+    cudaMemsetAsync(head_stats, 0, (size_t)q.embed_heads * 16, stream);
 
+    const int64_t ek = q.embed_heads * (int64_t)q.K;
+    SG_LAUNCH(vq_tc_maxabs_kernel<<<(unsigned)((ek * 32 + 255) / 256), 256, 0, stream>>>(
+        q.embed, q.embed_heads, q.K, q.D, head_stats));
     const int64_t img_threads = (int64_t)q.embed_heads * pl.n_tiles * pl.kcn * BN * 8;
     SG_LAUNCH(vq_tc_image_kernel<<<(unsigned)((img_threads + 255) / 256), 256, 0, stream>>>(
-        q.embed, q.embed_heads, q.K, q.D, pl.n_tiles, pl.kcn, img));
-    const int64_t ne2_threads = (int64_t)q.embed_heads * pl.n_tiles * BN;
-    SG_LAUNCH(vq_tc_ne2_kernel<<<(unsigned)((ne2_threads + 255) / 256), 256, 0, stream>>>(
-        e2, q.embed_heads, q.K, pl.n_tiles, q.metric, ne2, emax2));
+        q.embed, q.embed_heads, q.K, q.D, pl.n_tiles, pl.kcn, head_stats, img));
+    const int64_t ne2_warps = (int64_t)q.embed_heads * pl.n_tiles * BN;
+    SG_LAUNCH(vq_tc_ne2_kernel<<<(unsigned)((ne2_warps * 32 + 255) / 256), 256, 0, stream>>>(
+        q.embed, e2, q.embed_heads, q.K, q.D, pl.n_tiles, q.metric, ne2, head_stats));
 
     TcParams p;
     p.x = q.x; p.x_row_stride = q.x_row_stride; p.x_head_stride = q.x_head_stride;
     p.heads = q.heads; p.embed_heads = q.embed_heads; p.rows = q.rows;
     p.K = q.K; p.D = q.D; p.n_tiles = pl.n_tiles; p.kcn = pl.kcn; p.sb = pl.sb; p.sa = pl.sa;
-    p.img = img; p.ne2 = ne2; p.emax2_bits = emax2;
-    // |bf16 dot - fp32 chain dot| <= (2^-8 + D 2^-23) |x||e| (5% margin); the Euclidean score adds
-    // fp32 roundings of x2 + e2 - 2 dot, a few ulps of (x2 + e2): 2^-21 (x2 + e2max) covers them
-    p.c1 = 1.05f * (0.00390625f + (float)q.D * 1.1920929e-7f);
-    p.c2 = q.metric == 0 ? 4.76837158e-7f : 0.f;
-    p.best = best; p.cand = cand; p.multi_list = multi_list; p.fb_list = fb_list; p.counters = counters;
+    p.img = img; p.ne2 = ne2; p.head_stats = head_stats;
+    // fp32 accumulation of D exact fp16 x fp16 products (tensor core) and of the fp32 re-score
+    // chain: <= D 2^-22 |x||e| together.  The Euclidean score adds the fp32 roundings of
+    // x2 + e2 - 2 dot and of acc*S - e2/2: a few ulps of (x2 + e2), covered by 2^-20 (x2 + e2max).
+    p.c_acc = (float)q.D * 2.3841858e-7f;
+    p.c2 = q.metric == 0 ? 9.5367432e-7f : 0.f;
+    p.best = best; p.cand = cand;
 
     const int64_t n_items = ((q.rows + BM - 1) / BM) * q.heads;
     const int grid = (int)(n_items < sm_count() ? n_items : sm_count());
@@ -635,14 +635,6 @@ int vq_assign_tc(const VqView& q, const float* x2, const float* e2, int32_t* bes
         set_error("vq_assign_tc: cudaFuncSetAttribute(%zu B smem): %s", pl.smem, cudaGetErrorString(e));
         return STEMGNN_ECUDA;
     }
-    const int rgrid = sm_count() * 8;
-    SG_LAUNCH(vq_rescore_kernel<<<rgrid, 256, 0, stream>>>(q, e2, multi_list, counters, cand, best));
-    // exact re-scan of rows whose candidate list overflowed (normally none)
-    SG_LAUNCH(vq_sqnorm_list_kernel<<<sm_count() * 4, 256, 0, stream>>>(q, fb_list, counters + 1,
-                                                                        const_cast<float*>(x2)));
-    dim3 fgrid((unsigned)(sm_count() * 2), 1);
-    SG_LAUNCH(vq_scan_kernel<<<fgrid, 256, 0, stream>>>(q, x2, e2, fb_list, counters + 1, best));
-    if (stats) SG_LAUNCH(vq_tc_stats_kernel<<<1, 1, 0, stream>>>(counters, stats));
     cudaError_t le = cudaGetLastError();
     if (le != cudaSuccess) {
         set_error("vq_assign_tc: CUDA error %s", cudaGetErrorString(le));

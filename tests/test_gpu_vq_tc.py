@@ -1,0 +1,159 @@
+"""GPU: K3 path 2 (tcgen05 fp16 GEMM + error band + fp32 re-scoring) against path 1 (exact fp32
+scan) and against the oracle's formula, through the C-ABI.  north_star bound: code indices
+identical except on ties with a score gap below 1e-6 (relative); every mismatch is checked
+against that bound in fp64."""
+import numpy as np
+import pytest
+import torch
+
+import stemgnn_b200 as S
+from oracle.vq_ref import cdist_ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _scores64(x, embed, metric):
+    """fp64 scores (H, M, K) of x (H, M, D) against embed (H, K, D)."""
+    x, e = x.double(), embed.double()
+    dot = torch.einsum("hmd,hkd->hmk", x, e)
+    if metric == S.METRIC_DOT:
+        return dot
+    d2 = (x ** 2).sum(-1, keepdim=True) + (e ** 2).sum(-1).unsqueeze(1) - 2 * dot
+    return -d2.clamp(min=0).sqrt()
+
+
+def _check_pair(x, embed, heads, metric, expect_equal=False, max_mismatch=None):
+    """path 2 == path 1 except near-ties; returns stats of path 2."""
+    i1, q1, sq1, _ = S.vq_assign_raw(x, embed, heads, metric, S.PATH_EXACT)
+    i2, q2, sq2, st = S.vq_assign_raw(x, embed, heads, metric, S.PATH_TENSOR, want_stats=True)
+    torch.cuda.synchronize()
+    Hc, K, D = embed.shape
+    M = x.size(0)
+    if Hc == heads:
+        xs = x.view(M, heads, D).permute(1, 0, 2)
+        a, b = i1.t(), i2.t()                                    # (H, M)
+    else:
+        xs = x.reshape(1, M * heads, D)
+        a, b = i1.reshape(1, -1), i2.reshape(1, -1)
+    diff = (a != b).nonzero()
+    if expect_equal:
+        assert diff.numel() == 0
+    if diff.numel():
+        limit = max(2, a.numel() // 2000) if max_mismatch is None else max_mismatch
+        assert diff.size(0) <= limit, f"{diff.size(0)} mismatches of {a.numel()}"
+        for h, m in diff.tolist():
+            s = _scores64(xs[h:h + 1, m:m + 1], embed[h:h + 1], metric)[0, 0]
+            s1, s2 = s[a[h, m]].item(), s[b[h, m]].item()
+            assert abs(s1 - s2) <= 1e-6 * max(1.0, abs(s1)), (h, m, s1, s2)
+    same = (i1 == i2).all(dim=-1) if i1.dim() > 1 else (i1 == i2)
+    assert torch.equal(q1[same], q2[same])
+    torch.testing.assert_close(sq1, sq2, rtol=1e-6, atol=0)
+    return st.cpu().tolist(), i2
+
+
+@pytest.mark.parametrize("metric", [S.METRIC_EUCLID, S.METRIC_DOT])
+@pytest.mark.parametrize("rows,K,D", [
+    (1, 1, 16), (1, 7, 32), (127, 37, 32), (128, 100, 64), (129, 256, 64), (1000, 257, 128),
+    (1000, 512, 256), (777, 100, 20), (500, 300, 72), (3000, 1000, 128), (2000, 4096, 128),
+    (600, 700, 512), (600, 300, 576), (400, 260, 640), (300, 520, 1024), (5000, 128, 768),
+])
+def test_tensor_path_matches_exact_scan(rows, K, D, metric):
+    g = torch.Generator(device=DEV).manual_seed(rows * 31 + K * 7 + D)
+    x = torch.randn(rows, D, generator=g, device=DEV)
+    embed = torch.randn(1, K, D, generator=g, device=DEV) * 0.3
+    if metric == S.METRIC_DOT:
+        x = torch.nn.functional.normalize(x, dim=-1)
+        embed = torch.nn.functional.normalize(embed, dim=-1)
+    st, ind = _check_pair(x, embed, 1, metric)
+    assert st[1] == 0, "no row should need the exact re-scan on random data"
+    ref = _scores64(x.unsqueeze(0), embed, metric)[0].argmax(-1)
+    bad = (ref != ind.view(-1)).nonzero().view(-1)
+    assert bad.numel() <= max(1, rows // 2000)
+
+
+@pytest.mark.parametrize("heads,sep", [(4, True), (4, False), (2, True)])
+@pytest.mark.parametrize("metric", [S.METRIC_EUCLID, S.METRIC_DOT])
+def test_tensor_path_heads(heads, sep, metric):
+    rows, K, D = 1500, 128, 96
+    g = torch.Generator(device=DEV).manual_seed(heads * 3 + int(sep))
+    x = torch.randn(rows, heads * D, generator=g, device=DEV)
+    embed = torch.randn(heads if sep else 1, K, D, generator=g, device=DEV)
+    if metric == S.METRIC_DOT:
+        x = torch.nn.functional.normalize(x.view(rows, heads, D), dim=-1).view(rows, heads * D)
+        embed = torch.nn.functional.normalize(embed, dim=-1)
+    _check_pair(x, embed, heads, metric)
+
+
+def test_exact_ties_pick_first_index_and_overflow_rescans():
+    rows, K, D = 700, 64, 64
+    g = torch.Generator(device=DEV).manual_seed(11)
+    x = torch.randn(rows, D, generator=g, device=DEV)
+    embed = torch.randn(1, K, D, generator=g, device=DEV)
+    embed[0, 40] = embed[0, 3]                     # duplicated code: the lower index must win
+    embed[0, 20:32] = embed[0, 9]                  # 13 identical codes: candidate list overflows
+    x[:50] = embed[0, 9] + 1e-3 * torch.randn(50, D, generator=g, device=DEV)
+    x[50:80] = embed[0, 3]                         # exact hits: clamp(0).sqrt() ties
+    for metric in (S.METRIC_EUCLID, S.METRIC_DOT):
+        st, ind = _check_pair(x, embed, 1, metric, expect_equal=True)
+        assert not ((ind >= 20) & (ind < 32)).any() and not (ind == 40).any()
+        if metric == S.METRIC_EUCLID:
+            assert (ind[:50] == 9).all() and (ind[50:80] == 3).all()
+            assert st[1] >= 50
+
+
+def test_rows_outside_fp16_range_fall_back_to_the_exact_scan():
+    rows, K, D = 300, 200, 64
+    g = torch.Generator(device=DEV).manual_seed(12)
+    x = torch.randn(rows, D, generator=g, device=DEV)
+    x[:40] *= 1e6
+    x[40:60] *= 1e-9
+    embed = torch.randn(1, K, D, generator=g, device=DEV)
+    # |x| ~ 1e7: ulp(x2 + e2) swamps e2 and the dot, so fp32 itself ties many codes; the
+    # re-scan's dot order differs from the tiled scan's -> mismatches allowed inside the 1e-6 gap
+    st, _ = _check_pair(x, embed, 1, S.METRIC_EUCLID, max_mismatch=40)
+    assert st[1] >= 40
+    tiny = torch.randn(1, K, D, generator=g, device=DEV) * 1e-12      # scale S handles tiny codebooks
+    _check_pair(torch.randn(rows, D, generator=g, device=DEV), tiny, 1, S.METRIC_DOT)
+    huge = torch.randn(1, K, D, generator=g, device=DEV) * 1e12
+    _check_pair(torch.randn(rows, D, generator=g, device=DEV), huge, 1, S.METRIC_EUCLID)
+    zero = torch.zeros(1, K, D, device=DEV)                           # kmeans-style all-zero codebook
+    _, ind = _check_pair(torch.randn(rows, D, generator=g, device=DEV), zero, 1, S.METRIC_EUCLID,
+                         expect_equal=True)
+    assert (ind == 0).all()
+
+
+def test_matches_oracle_formula_on_cpu():
+    rows, K, D = 4000, 512, 256
+    g = torch.Generator().manual_seed(13)
+    x = torch.randn(rows, D, generator=g)
+    embed = torch.empty(1, K, D)
+    torch.nn.init.kaiming_uniform_(embed, generator=g)
+    ref = (-cdist_ref(x.unsqueeze(0), embed)).argmax(-1)[0]
+    ind, q, _, st = S.vq_assign_raw(x.to(DEV), embed.to(DEV), 1, S.METRIC_EUCLID, S.PATH_TENSOR,
+                                    want_stats=True)
+    bad = (ind.view(-1).cpu() != ref).nonzero().view(-1)
+    s64 = _scores64(x.unsqueeze(0), embed, S.METRIC_EUCLID)[0]
+    for m in bad.tolist():
+        assert abs(s64[m, ref[m]] - s64[m, ind.view(-1)[m].item()]) <= 1e-6 * abs(s64[m, ref[m]])
+    assert bad.numel() <= 2
+    assert torch.equal(q.cpu()[ind.view(-1).cpu() == ref], embed[0][ref][ind.view(-1).cpu() == ref])
+
+
+def test_arxiv_sized_bottleneck_full_size():
+    """BASELINE config 2 at full size: 169,343 x 512 x 256, Euclidean, kaiming-uniform codebook."""
+    rows, K, D = 169343, 512, 256
+    g = torch.Generator(device=DEV).manual_seed(14)
+    x = torch.randn(rows, D, generator=g, device=DEV)
+    embed = (torch.rand(1, K, D, generator=g, device=DEV) * 2 - 1) * (6.0 / D) ** 0.5
+    st, _ = _check_pair(x, embed, 1, S.METRIC_EUCLID)
+    assert st[1] == 0 and st[0] < rows // 2
+
+
+def test_sweep_slice_large_codebook():
+    """A slice of BASELINE config 5: 100k rows x 16,384 codes x 128 dims."""
+    rows, K, D = 100000, 16384, 128
+    g = torch.Generator(device=DEV).manual_seed(15)
+    x = torch.randn(rows, D, generator=g, device=DEV)
+    embed = torch.randn(1, K, D, generator=g, device=DEV)
+    _check_pair(x, embed, 1, S.METRIC_EUCLID)
