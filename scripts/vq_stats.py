@@ -1,0 +1,33 @@
+"""Print the tcgen05 VQ path's statistics and timing for a few (rows, K, D) points (GPU only)."""
+import sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import stemgnn_b200 as S
+
+def run(rows, K, D, metric, scale=None, iters=5):
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(rows, D, generator=g, device="cuda")
+    if scale is None:
+        e = (torch.rand(1, K, D, generator=g, device="cuda") * 2 - 1) * (6.0 / D) ** 0.5
+    else:
+        e = torch.randn(1, K, D, generator=g, device="cuda") * scale
+    if metric == S.METRIC_DOT:
+        x = torch.nn.functional.normalize(x, dim=-1); e = torch.nn.functional.normalize(e, dim=-1)
+    for path in (S.PATH_TENSOR, S.PATH_EXACT):
+        S.vq_assign_raw(x, e, 1, metric, path, want_stats=True)
+        torch.cuda.synchronize()
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(iters):
+            ind, q, sq, st = S.vq_assign_raw(x, e, 1, metric, path, want_stats=True)
+        t1.record(); torch.cuda.synchronize()
+        ms = t0.elapsed_time(t1) / iters
+        print(f"rows={rows} K={K} D={D} metric={metric} path={path}: {ms:.3f} ms  "
+              f"{2*rows*K*D/ms/1e9:.1f} TFLOP/s  rescored={st[0].item()} rescanned={st[1].item()}", flush=True)
+
+if __name__ == "__main__":
+    run(169343, 512, 256, S.METRIC_EUCLID)
+    run(169343, 512, 256, S.METRIC_EUCLID, scale=1.0)
+    run(169343, 128, 768, S.METRIC_DOT, scale=1.0)
+    run(1000000, 4096, 128, S.METRIC_EUCLID, scale=1.0, iters=2)
+    run(1000000, 16384, 256, S.METRIC_EUCLID, scale=1.0, iters=1)

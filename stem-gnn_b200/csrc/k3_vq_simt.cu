@@ -158,39 +158,68 @@ vq_gather_kernel(VqView q, const int32_t* __restrict__ best, const int32_t* __re
                  const float* __restrict__ e2, double* __restrict__ partials,
                  unsigned long long* __restrict__ stats) {
     __shared__ double wsum[8];
+    __shared__ int s_b[8];          // per-warp decision: code, or -2 = needs the exact scan
+    __shared__ float s_bs[8];
+    __shared__ int s_bi[8];
     const int w = threadIdx.x >> 5, lane = lane_id();
     const int64_t h = blockIdx.y;
     const int64_t m = (int64_t)blockIdx.x * 8 + w;
-    double part = 0.0;
+    const int64_t eh = q.embed_heads == 1 ? 0 : h;
+    const float* E = q.embed + eh * (int64_t)q.K * q.D;
+    const float* e2h = e2 + eh * (int64_t)q.K;
+    int b = 0;
     if (m < q.rows) {
         const int64_t flat = h * q.rows + m;
-        int b = best[flat];
-        const int64_t eh = q.embed_heads == 1 ? 0 : h;
-        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
-        if (b < 0) {
-            const float* E = q.embed + eh * (int64_t)q.K * q.D;
+        b = best[flat];
+        if (b == -1) {
+            const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
             const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
             const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
             float bs = -INFINITY;
             int bi = 0x7fffffff;
-            if (b == -1) {
-                for (int j = 0; j < VQ_CAND_CAP; ++j) {
-                    const int c = cand[flat * VQ_CAND_CAP + j];
-                    if (c < 0) break;
-                    const float s = vq_score(q.metric, x2, e2[eh * q.K + c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
-                    if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
-                }
-                if (lane == 0 && stats) atomicAdd(stats + 0, 1ull);
-            } else {
-                for (int c = 0; c < q.K; ++c) {
-                    const float s = vq_score(q.metric, x2, e2[eh * q.K + c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
-                    if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
-                }
-                if (lane == 0 && stats) atomicAdd(stats + 1, 1ull);
+            for (int j = 0; j < VQ_CAND_CAP; ++j) {
+                const int c = cand[flat * VQ_CAND_CAP + j];
+                if (c < 0) break;
+                const float s = vq_score(q.metric, x2, e2h[c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
+                if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
             }
-            b = bi < q.K ? bi : 0;     // all-NaN rows: argmax of NaNs is index 0
+            if (lane == 0 && stats) atomicAdd(stats + 0, 1ull);
+            b = bi < q.K ? bi : -2;
         }
-        const float* e = q.embed + (eh * q.K + b) * (int64_t)q.D;
+    }
+    if (lane == 0) s_b[w] = b;
+    __syncthreads();
+    // exact scan of the rows left open (-2), the whole CTA on one row at a time: warp w takes the
+    // codes w, w+8, ...; first index wins ties.  Normally no row gets here.
+    for (int r = 0; r < 8; ++r) {
+        if (s_b[r] != -2) continue;                       // CTA-uniform
+        const int64_t mr = (int64_t)blockIdx.x * 8 + r;
+        const float* xp = q.x + mr * q.x_row_stride + h * q.x_head_stride;
+        const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
+        const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
+        float bs = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int c = w; c < q.K; c += 8) {
+            const float s = vq_score(q.metric, x2, e2h[c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
+            if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
+        }
+        if (lane == 0) { s_bs[w] = bs; s_bi[w] = bi; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float fs = s_bs[0];
+            int fi = s_bi[0];
+            for (int k = 1; k < 8; ++k)
+                if (s_bs[k] > fs || (s_bs[k] == fs && s_bi[k] < fi)) { fs = s_bs[k]; fi = s_bi[k]; }
+            s_b[r] = fi < q.K ? fi : 0;                   // all-NaN rows: argmax of NaNs is index 0
+            if (stats) atomicAdd(stats + 1, 1ull);
+        }
+        __syncthreads();
+    }
+    double part = 0.0;
+    if (m < q.rows) {
+        b = s_b[w];
+        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
+        const float* e = E + (int64_t)b * q.D;
         float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
         float s = 0.f;
         for (int d = lane; d < q.D; d += 32) {

@@ -10,14 +10,14 @@
 // fp16 operands (11-bit significand, same kind::f16 rate as bf16) keep the error band 8x
 // tighter than bf16 would; S is a per-codebook power of two that maps max|e| to [2^13, 2^14).
 //
-// A persistent CTA owns a 128-row tile of X.  Four producer warps read the fp32 rows with
+// A persistent CTA owns a 128-row tile of X.  Eight producer warps read the fp32 rows with
 // 128-bit loads, round to fp16 and store them K-major / 128B-swizzled in shared memory (the
 // canonical UMMA operand layout) -- X is read from HBM exactly once, as fp32.  The codebook is
 // pre-converted once per call into the same swizzled tile image in global memory, so one
 // elected thread streams it with 1-D bulk async copies (cp.async.bulk -> mbarrier complete_tx)
 // through a ring of 32 KB stages.  One elected thread issues tcgen05.mma (M=128, N<=256, K=16,
-// f16 -> fp32) into a double-buffered 2 x 256-column TMEM accumulator; four epilogue warps read
-// the accumulator with tcgen05.ld (one row per thread), add -e2/2 and keep the running best
+// f16 -> fp32) into a double-buffered 2 x 256-column TMEM accumulator; eight epilogue warps read
+// the accumulator with tcgen05.ld (one row per thread, two warps per lane quarter), add -e2/2 and keep the running best
 // score plus every code within a rigorous error band of it.
 //
 // Parity: with x~ = fp16(x), e~ = S fp16(e/S) the tensor-core dot differs from the exact one by
@@ -42,11 +42,15 @@ constexpr int BK = 64;                     // bf16 columns per smem chunk (one 1
 constexpr int A_CHUNK_BYTES = BM * 128;    // 16 KB
 constexpr int B_STAGE_BYTES = BN * 128;    // 32 KB
 constexpr int CAP = VQ_CAND_CAP;           // candidates kept per row
-constexpr int NUM_THREADS = 320;           // warps 0-3 epilogue, 4-7 producers, 8 loader, 9 MMA
-constexpr int PROD_WARP0 = 4, LOAD_WARP = 8, MMA_WARP = 9;
-constexpr int MAX_KC = 16;                 // a_full barriers (resident: D <= 1024; ring: stages)
+constexpr int EPI_WARPS = 8;               // two per TMEM lane quarter: they split the columns
+constexpr int NUM_THREADS = 576;           // warps 0-7 epilogue, 8-15 producers, 16 loader, 17 MMA
+constexpr int PROD_WARP0 = 8, LOAD_WARP = 16, MMA_WARP = 17;
+constexpr int MAX_AS = 20;                 // A chunk slots (resident: kcn * 1|2 buffers; ring: 4)
 constexpr int MAX_SB = 6;
-constexpr int SMEM_EXTRA = 4 * BN * 4 + 4 * BM * 4 + 64 * 8 + 16;   // ne2 slices, band ring, barriers
+constexpr int MERGE_WORDS = 8;             // per-row state handed from the odd-chunk warp to its partner
+// ne2 slices [8][256] f32, band ring [4][128] f32, group-1 partials [128] float2, merge [128][12],
+// barriers, tmem slot
+constexpr int SMEM_EXTRA = EPI_WARPS * BN * 4 + 4 * BM * 4 + BM * 8 + BM * MERGE_WORDS * 4 + 80 * 8 + 16;
 constexpr int SMEM_MAX = 232448;           // 227 KB opt-in limit per CTA
 
 // ---------------------------------------------------------------------------------- PTX
@@ -142,6 +146,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t addr, float* v) {
         : "r"(addr)
         : "memory");
 }
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "r"(addr)
+                 : "memory");
+    return r;
+}
 __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -153,7 +165,7 @@ struct TcParams {
     int K, D;
     int n_tiles, kcn;                // code tiles of 256, 64-column chunks
     int sb;                          // B ring stages
-    int sa;                          // A ring stages (ring mode only)
+    int a_slots;                     // A chunk slots: kcn * buffers (resident) or ring stages
     const __half* img;               // [embed_heads][n_tiles][kcn][256 x 64] swizzled tile images
     const float* ne2;                // [embed_heads][n_tiles*256]: -e2/2 | 0, padded with -inf
     const uint32_t* head_stats;      // [embed_heads][4] float bits: max|e|, max e2, max |e - e~|^2, S
@@ -168,36 +180,63 @@ __device__ __forceinline__ int tile_codes32(const TcParams& p, int n) {
     return (rem + 31) & ~31;
 }
 
+// Sum 4 per-lane values across the 4 lanes of a quad so that lane j ends with the total of
+// value index j (3 shuffles instead of 8).
+__device__ __forceinline__ float transpose_reduce4(const float (&a)[4], int j) {
+    const float k0 = (j & 2) ? a[2] : a[0], s0 = (j & 2) ? a[0] : a[2];
+    const float k1 = (j & 2) ? a[3] : a[1], s1 = (j & 2) ? a[1] : a[3];
+    const float b0 = k0 + __shfl_xor_sync(0xffffffffu, s0, 2);
+    const float b1 = k1 + __shfl_xor_sync(0xffffffffu, s1, 2);
+    const float keep = (j & 1) ? b1 : b0, send = (j & 1) ? b0 : b1;
+    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
+}
+
 // ---------------------------------------------------------------------------------- kernel
+// A chunk sequence number: resident mode fills every chunk once per row tile, ring mode once per
+// (row tile, code tile).  slot = seq % a_slots, phase = (seq / a_slots) & 1.
+template <bool RESIDENT>
+__device__ __forceinline__ uint32_t a_seq(const TcParams& p, uint32_t tile_it, int n, int kc) {
+    return RESIDENT ? tile_it * (uint32_t)p.kcn + (uint32_t)kc
+                    : (tile_it * (uint32_t)p.n_tiles + (uint32_t)n) * (uint32_t)p.kcn + (uint32_t)kc;
+}
+
 template <bool RESIDENT>
 __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // dynamic smem base is 1024-aligned by the attribute on sm_100; keep an explicit round-up
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    const int a_slots = RESIDENT ? p.kcn : p.sa;
+    extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sA = smem;
-    uint8_t* sB = sA + (size_t)a_slots * A_CHUNK_BYTES;
-    float* s_ne2 = reinterpret_cast<float*>(sB + (size_t)p.sb * B_STAGE_BYTES);   // [4][256]
-    float* s_band = s_ne2 + 4 * BN;                                                // [4][128]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_band + 4 * BM);
-    uint64_t* a_full = bars;                 // [MAX_KC]
-    uint64_t* a_empty = bars + MAX_KC;       // [MAX_KC] (resident mode uses [0])
-    uint64_t* b_full = bars + 2 * MAX_KC;    // [MAX_SB]
+    uint8_t* sB = sA + (size_t)p.a_slots * A_CHUNK_BYTES;
+    float* s_ne2 = reinterpret_cast<float*>(sB + (size_t)p.sb * B_STAGE_BYTES);   // [8][256]
+    float* s_band = s_ne2 + EPI_WARPS * BN;                                        // [4][128]
+    float2* s_part = reinterpret_cast<float2*>(s_band + 4 * BM);                   // [128]
+    float* s_merge = reinterpret_cast<float*>(s_part + BM);                        // [128][12]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_merge + BM * MERGE_WORDS);
+    uint64_t* a_full = bars;                 // [MAX_AS]
+    uint64_t* a_empty = bars + MAX_AS;       // [MAX_AS]
+    uint64_t* b_full = bars + 2 * MAX_AS;    // [MAX_SB]
     uint64_t* b_empty = b_full + MAX_SB;     // [MAX_SB]
     uint64_t* t_full = b_empty + MAX_SB;     // [2]
     uint64_t* t_empty = t_full + 2;          // [2]
-    uint64_t* band_full = t_empty + 2;         // [4]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(band_full + 4);
+    uint64_t* band_full = t_empty + 2;       // [4]
+    uint64_t* part_full = band_full + 4;     // [1]
+    uint64_t* part_empty = part_full + 1;    // [1]
+    uint64_t* merge_full = part_empty + 1;   // [1]
+    uint64_t* merge_empty = merge_full + 1;  // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(merge_empty + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row_tiles = (p.rows + BM - 1) / BM;
     const int64_t n_items = row_tiles * p.heads;
 
     if (warp == LOAD_WARP && lane == 0) {
-        for (int i = 0; i < MAX_KC; ++i) { mbar_init(smem_u32(a_full + i), BM); mbar_init(smem_u32(a_empty + i), 1); }
+        if (smem_u32(smem) & 1023u) __trap();   // the swizzled operand tiles need 1024 B alignment
+        for (int i = 0; i < MAX_AS; ++i) { mbar_init(smem_u32(a_full + i), BM); mbar_init(smem_u32(a_empty + i), 1); }
         for (int i = 0; i < MAX_SB; ++i) { mbar_init(smem_u32(b_full + i), 1); mbar_init(smem_u32(b_empty + i), 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), BM); }
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), EPI_WARPS * 32); }
         for (int i = 0; i < 4; ++i) mbar_init(smem_u32(band_full + i), BM);
+        mbar_init(smem_u32(part_full), BM);
+        mbar_init(smem_u32(part_empty), BM);
+        mbar_init(smem_u32(merge_full), BM);
+        mbar_init(smem_u32(merge_empty), BM);
         fence_barrier_init();
     }
     if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -230,7 +269,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     } else if (warp == MMA_WARP) {
         // ================= MMA issuer: one thread drives the tensor core =================
         if (lane == 0) {
-            uint32_t it_b = 0, it_a = 0, acc_it = 0, tile_it = 0;
+            uint32_t it_b = 0, acc_it = 0, tile_it = 0;
             const int last_ksteps = ((p.D - (p.kcn - 1) * BK) + 15) / 16;
             for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
                 for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
@@ -241,119 +280,135 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                     const uint32_t d_tmem = tmem_base + st * BN;
                     for (int kc = 0; kc < p.kcn; ++kc, ++it_b) {
                         const uint32_t sb = it_b % (uint32_t)p.sb;
-                        uint32_t a_addr;
-                        if (RESIDENT) {
-                            if (n == 0) mbar_wait(smem_u32(a_full + kc), tile_it & 1u);
-                            a_addr = smem_u32(sA + (size_t)kc * A_CHUNK_BYTES);
-                        } else {
-                            const uint32_t sa = it_a % (uint32_t)p.sa;
-                            mbar_wait(smem_u32(a_full + sa), (it_a / (uint32_t)p.sa) & 1u);
-                            a_addr = smem_u32(sA + (size_t)sa * A_CHUNK_BYTES);
-                        }
+                        const uint32_t seq = a_seq<RESIDENT>(p, tile_it, n, kc);
+                        const uint32_t sa = seq % (uint32_t)p.a_slots;
+                        if (!RESIDENT || n == 0)
+                            mbar_wait(smem_u32(a_full + sa), (seq / (uint32_t)p.a_slots) & 1u);
                         mbar_wait(smem_u32(b_full + sb), (it_b / (uint32_t)p.sb) & 1u);
                         tc_fence_after();
-                        const uint64_t a_desc = smem_desc_sw128(a_addr);
+                        const uint64_t a_desc = smem_desc_sw128(smem_u32(sA + (size_t)sa * A_CHUNK_BYTES));
                         const uint64_t b_desc = smem_desc_sw128(smem_u32(sB + (size_t)sb * B_STAGE_BYTES));
                         const int ksteps = kc == p.kcn - 1 ? last_ksteps : BK / 16;
                         for (int k = 0; k < ksteps; ++k)   // +32 B along K inside the swizzle row
                             umma_f16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                                      (uint32_t)((kc | k) != 0));
+                                     (uint32_t)((kc | k) != 0));
                         umma_commit(smem_u32(b_empty + sb));
-                        if (!RESIDENT) { umma_commit(smem_u32(a_empty + it_a % (uint32_t)p.sa)); ++it_a; }
+                        // the A chunk is free once the last code tile that reads it has consumed it
+                        if (!RESIDENT || n == p.n_tiles - 1) umma_commit(smem_u32(a_empty + sa));
                     }
                     umma_commit(smem_u32(t_full + st));
                 }
-                if (RESIDENT) umma_commit(smem_u32(a_empty));
             }
         }
-    } else if (warp >= PROD_WARP0) {
+    } else if (warp >= PROD_WARP0 && warp < LOAD_WARP) {
         // ================= producers: fp32 rows -> fp16, swizzled K-major A chunks =================
-        const int pt = threadIdx.x - PROD_WARP0 * 32;       // 0..127
-        const int q = pt & 15, rg = pt >> 4;                // float4 slot in the chunk, row in the atom
-        const uint32_t soff = (uint32_t)(rg * 128 + (((q >> 1) ^ rg) << 4) + (q & 1) * 8);
-        uint32_t it_a = 0, tile_it = 0;
+        // Two groups of 128 threads take alternate 64-column chunks, so two chunks (2 x 32 KB of
+        // fp32) are in flight per SM.  Thread (j, rr) of a group owns rows rr, rr+32, rr+64, rr+96
+        // and the 16 B slots j, j+4, j+8, j+12 of each: a quad reads 64 contiguous bytes per load.
+        const int pt = (threadIdx.x - PROD_WARP0 * 32) & 127;
+        const int grp = (threadIdx.x - PROD_WARP0 * 32) >> 7;
+        const int j = pt & 3, rr = pt >> 2;
+        // byte offset of slot f = j + 4k of row rr in the swizzled chunk: 16 B unit (f>>1)^(rr&7), half f&1
+        uint32_t soff[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            soff[k] = (uint32_t)((rr >> 3) * 1024 + (rr & 7) * 128 + (((((j + 4 * k) >> 1)) ^ (rr & 7)) << 4) + (j & 1) * 8);
+        uint32_t tile_it = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int64_t h = item / row_tiles, mt = item - h * row_tiles;
             const int64_t eh = p.embed_heads == 1 ? 0 : h;
             const int64_t row0 = mt * BM;
             const float* xb = p.x + h * p.x_head_stride;
-            float sq[16], rq[16];       // |x|^2 and |x - fp16(x)|^2 of this thread's slice of 16 rows
+            float sq[4], rq[4];         // |x|^2 and |x - fp16(x)|^2 of this thread's slices of 4 rows
 #pragma unroll
-            for (int i = 0; i < 16; ++i) { sq[i] = 0.f; rq[i] = 0.f; }
-            if (RESIDENT) mbar_wait(smem_u32(a_empty), (tile_it & 1u) ^ 1u);
+            for (int i = 0; i < 4; ++i) { sq[i] = 0.f; rq[i] = 0.f; }
             const int n_pass = RESIDENT ? 1 : p.n_tiles;
+#pragma unroll 1
             for (int n = 0; n < n_pass; ++n) {
-                for (int kc = 0; kc < p.kcn; ++kc) {
-                    uint32_t slot = kc;
-                    if (!RESIDENT) {
-                        slot = it_a % (uint32_t)p.sa;
-                        mbar_wait(smem_u32(a_empty + slot), ((it_a / (uint32_t)p.sa) & 1u) ^ 1u);
-                        ++it_a;
-                    }
-                    const int col = kc * BK + q * 4;
-                    const bool col_ok = col < p.D;
-                    float4 v[16];
+#pragma unroll 1
+                for (int kc = grp; kc < p.kcn; kc += 2) {
+                    const uint32_t seq = a_seq<RESIDENT>(p, tile_it, n, kc);
+                    const uint32_t slot = seq % (uint32_t)p.a_slots;
+                    mbar_wait(smem_u32(a_empty + slot), ((seq / (uint32_t)p.a_slots) & 1u) ^ 1u);
+                    float4 v[4][4];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const int64_t r = row0 + rg + 8 * i;
-                        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (col_ok && r < p.rows)
-                            v[i] = __ldg(reinterpret_cast<const float4*>(xb + r * p.x_row_stride + col));
-                    }
-                    uint8_t* dst = sA + (size_t)slot * A_CHUNK_BYTES + soff;
+                    for (int i = 0; i < 4; ++i) {
+                        const int64_t r = row0 + rr + 32 * i;
+                        const float* rp = xb + r * p.x_row_stride + kc * BK + 4 * j;
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const __half2 lo = __floats2half2_rn(v[i].x, v[i].y);
-                        const __half2 hi = __floats2half2_rn(v[i].z, v[i].w);
-                        uint2 pk;
-                        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
-                        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-                        *reinterpret_cast<uint2*>(dst + i * 1024) = pk;
-                        if (n == 0) {
-                            const float2 fl = __half22float2(lo), fh = __half22float2(hi);
-                            float d;
-                            sq[i] = fmaf(v[i].x, v[i].x, sq[i]); d = v[i].x - fl.x; rq[i] = fmaf(d, d, rq[i]);
-                            sq[i] = fmaf(v[i].y, v[i].y, sq[i]); d = v[i].y - fl.y; rq[i] = fmaf(d, d, rq[i]);
-                            sq[i] = fmaf(v[i].z, v[i].z, sq[i]); d = v[i].z - fh.x; rq[i] = fmaf(d, d, rq[i]);
-                            sq[i] = fmaf(v[i].w, v[i].w, sq[i]); d = v[i].w - fh.y; rq[i] = fmaf(d, d, rq[i]);
+                        for (int k = 0; k < 4; ++k) {
+                            v[i][k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (r < p.rows && kc * BK + 4 * (j + 4 * k) < p.D)
+                                v[i][k] = __ldg(reinterpret_cast<const float4*>(rp + 16 * k));
+                        }
+                    }
+                    uint8_t* dst = sA + (size_t)slot * A_CHUNK_BYTES;
+                    const bool first = n == 0;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float4 t = v[i][k];
+                            const __half2 lo = __floats2half2_rn(t.x, t.y);
+                            const __half2 hi = __floats2half2_rn(t.z, t.w);
+                            uint2 pk;
+                            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                            *reinterpret_cast<uint2*>(dst + i * 4096 + soff[k]) = pk;
+                            if (first) {
+                                const float2 fl = __half22float2(lo), fh = __half22float2(hi);
+                                float d;
+                                sq[i] = fmaf(t.x, t.x, sq[i]); d = t.x - fl.x; rq[i] = fmaf(d, d, rq[i]);
+                                sq[i] = fmaf(t.y, t.y, sq[i]); d = t.y - fl.y; rq[i] = fmaf(d, d, rq[i]);
+                                sq[i] = fmaf(t.z, t.z, sq[i]); d = t.z - fh.x; rq[i] = fmaf(d, d, rq[i]);
+                                sq[i] = fmaf(t.w, t.w, sq[i]); d = t.w - fh.y; rq[i] = fmaf(d, d, rq[i]);
+                            }
                         }
                     }
                     fence_async_smem();
                     mbar_arrive(smem_u32(a_full + slot));
-                    if (n == 0 && kc == p.kcn - 1) {
-                        // per-row error band -> band ring (4 deep: the epilogue of tile t-4 has
-                        // finished before the producers of tile t can run)
-                        const float emax = sqrtf(__uint_as_float(__ldg(p.head_stats + eh * 4 + 1)));
+                }
+                if (n == 0) {
+                    // lane j of the quad gets the totals of row rr + 32j over this group's chunks
+                    const float s_g = transpose_reduce4(sq, j), r_g = transpose_reduce4(rq, j);
+                    const int row = rr + 32 * j;
+                    if (grp == 1) {
+                        mbar_wait(smem_u32(part_empty), (tile_it & 1u) ^ 1u);
+                        s_part[row] = make_float2(s_g, r_g);
+                        mbar_arrive(smem_u32(part_full));
+                    } else {
+                        mbar_wait(smem_u32(part_full), tile_it & 1u);
+                        const float2 o = s_part[row];
+                        mbar_arrive(smem_u32(part_empty));
+                        const float s = s_g + o.x, r = r_g + o.y;
                         const float e2max = __uint_as_float(__ldg(p.head_stats + eh * 4 + 1));
+                        const float emax = sqrtf(e2max);
                         const float remax = sqrtf(__uint_as_float(__ldg(p.head_stats + eh * 4 + 2)));
-                        float* bd = s_band + (tile_it & 3u) * BM;
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            float s = sq[i], r = rq[i];
-#pragma unroll
-                            for (int o = 1; o < 16; o <<= 1) {
-                                s += __shfl_xor_sync(0xffffffffu, s, o);
-                                r += __shfl_xor_sync(0xffffffffu, r, o);
-                            }
-                            if (q == 0) {
-                                const float xn = sqrtf(s);
-                                float b = 2.f * (1.001f * sqrtf(r) * emax + 1.001f * xn * remax + p.c_acc * xn * emax) +
-                                          p.c2 * (s + e2max);
-                                // |x| >= 2^15 could overflow fp16: an infinite band sends the row
-                                // to the exact re-scan (NaN/Inf rows end there as well)
-                                if (!(s < 1073741824.f)) b = INFINITY;
-                                bd[rg + 8 * i] = b;
-                            }
-                        }
+                        const float xn = sqrtf(s);
+                        float b = 2.f * (1.001f * sqrtf(r) * emax + 1.001f * xn * remax + p.c_acc * xn * emax) +
+                                  p.c2 * (s + e2max);
+                        // |x| >= 2^15 could overflow fp16: an infinite band sends the row to the
+                        // exact re-scan (NaN/Inf rows end there as well).  The ring is 4 deep: the
+                        // epilogue of tile t-4 is done before the producers of tile t can run.
+                        if (!(s < 1073741824.f)) b = INFINITY;
+                        s_band[(tile_it & 3u) * BM + row] = b;
                         mbar_arrive(smem_u32(band_full + (tile_it & 3u)));
                     }
                 }
             }
         }
-    } else {
+    } else if (warp < EPI_WARPS) {
         // ================= epilogue: TMEM -> registers, running best + candidate band =================
-        const int row_in_tile = warp * 32 + lane;
-        float* ne2s = s_ne2 + warp * BN;
+        // One row per thread; warps w and w+4 share TMEM lane quarter w&3 and take alternate
+        // 32-column chunks (two warps per scheduler hide each other's latencies).  Every code tile
+        // is swept twice while it sits in TMEM: sweep 1 is a pure max (FFMA + FMNMX tree), sweep 2
+        // records -- branch-free, three index slots + a count -- the codes with score >= max - band.
+        // No values are kept: when a later tile beats the old best by more than the band the list
+        // is simply cleared, otherwise it stays a superset of the in-band codes, which is all the
+        // fp32 re-scoring needs.  More than three in-band codes -> exact re-scan of the row.
+        const int quarter = warp & 3, half = warp >> 2;
+        const int row_in_tile = quarter * 32 + lane;
+        const uint32_t ne2s = smem_u32(s_ne2 + warp * BN);
         uint32_t acc_it = 0, tile_it = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int64_t h = item / row_tiles, mt = item - h * row_tiles;
@@ -362,15 +417,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
             const float* ne2g = p.ne2 + eh * (int64_t)p.n_tiles * BN;
             const float scale = __uint_as_float(__ldg(p.head_stats + eh * 4 + 3));
             float rb = -INFINITY, thr = -INFINITY, band = 0.f;
-            float cv[CAP];
-            int ci[CAP];
-            int nc = 0;
-            bool overflow = false;
+            int cnt = 0, p0 = -1, p1 = -1, p2 = -1;
+#pragma unroll 1
             for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
                 const int ncols = tile_codes32(p, n);
                 __syncwarp();
 #pragma unroll
-                for (int j = 0; j < BN / 32; ++j) ne2s[j * 32 + lane] = __ldg(ne2g + n * BN + j * 32 + lane);
+                for (int j = 0; j < BN / 32; ++j)
+                    s_ne2[warp * BN + j * 32 + lane] = __ldg(ne2g + n * BN + j * 32 + lane);
                 __syncwarp();
                 const uint32_t st = acc_it & 1u;
                 if (n == 0) {
@@ -379,55 +433,95 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                 }
                 mbar_wait(smem_u32(t_full + st), (acc_it >> 1) & 1u);
                 tc_fence_after();
-                const uint32_t t_addr = tmem_base + ((uint32_t)(warp * 32) << 16) + st * BN;
-                for (int c0 = 0; c0 < ncols; c0 += 32) {
-                    float v[32];
-                    tmem_ld32(t_addr + (uint32_t)c0, v);
-                    tmem_ld_wait();
+                const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + st * BN;
+                float tmax = -INFINITY;
+                bool any_hit = true;
+#pragma unroll 1
+                for (int pass = 0; pass < 2 && any_hit; ++pass) {
+#pragma unroll 1
+                    for (int c0 = half * 32; c0 < ncols; c0 += 64) {
+                        float v[32];
+                        tmem_ld32(t_addr + (uint32_t)c0, v);
+                        tmem_ld_wait();
+                        float cm = -INFINITY;
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        float mx = -INFINITY;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            v[g * 8 + i] = fmaf(v[g * 8 + i], scale, ne2s[c0 + g * 8 + i]);
-                            mx = fmaxf(mx, v[g * 8 + i]);
+                        for (int g = 0; g < 4; ++g) {
+                            const float4 na = lds128(ne2s + (uint32_t)(c0 + g * 8) * 4u);
+                            const float4 nb = lds128(ne2s + (uint32_t)(c0 + g * 8 + 4) * 4u);
+                            float* w = v + g * 8;
+                            w[0] = fmaf(w[0], scale, na.x); w[1] = fmaf(w[1], scale, na.y);
+                            w[2] = fmaf(w[2], scale, na.z); w[3] = fmaf(w[3], scale, na.w);
+                            w[4] = fmaf(w[4], scale, nb.x); w[5] = fmaf(w[5], scale, nb.y);
+                            w[6] = fmaf(w[6], scale, nb.z); w[7] = fmaf(w[7], scale, nb.w);
+                            cm = fmaxf(cm, fmaxf(fmaxf(fmaxf(w[0], w[1]), fmaxf(w[2], w[3])),
+                                                 fmaxf(fmaxf(w[4], w[5]), fmaxf(w[6], w[7]))));
                         }
-                        if (mx >= thr) {
+                        if (pass == 0) {
+                            tmax = fmaxf(tmax, cm);
+                        } else if (__any_sync(0xffffffffu, cm >= thr)) {
+                            const int base = n * BN + c0;
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                const float s = v[g * 8 + i];
-                                if (s >= thr && !overflow) {
-                                    if (s > rb) { rb = s; thr = rb - band; }
-                                    if (nc == CAP) {       // compact against the current threshold
-                                        int keep = 0;
-                                        for (int j = 0; j < CAP; ++j)
-                                            if (cv[j] >= thr) { cv[keep] = cv[j]; ci[keep] = ci[j]; ++keep; }
-                                        nc = keep;
-                                        if (nc == CAP) { overflow = true; nc = 0; }
-                                    }
-                                    cv[nc] = s;
-                                    ci[nc] = n * BN + c0 + g * 8 + i;
-                                    ++nc;
-                                }
+                            for (int i = 0; i < 32; ++i) {
+                                const bool hit = v[i] >= thr;
+                                p2 = hit ? p1 : p2;
+                                p1 = hit ? p0 : p1;
+                                p0 = hit ? base + i : p0;
+                                cnt += hit ? 1 : 0;
                             }
                         }
+                    }
+                    if (pass == 0) {
+                        // everything recorded so far drops out of the band when this tile wins clearly
+                        if (tmax - band > rb) { cnt = 0; p0 = -1; p1 = -1; p2 = -1; }
+                        rb = fmaxf(rb, tmax);
+                        thr = rb - band;
+                        any_hit = __any_sync(0xffffffffu, tmax >= thr);
                     }
                 }
                 tc_fence_before();
                 mbar_arrive(smem_u32(t_empty + st));
             }
-            if (m < p.rows) {
-                const int64_t flat = h * p.rows + m;
-                int keep = 0, only = -1;
-                for (int j = 0; j < nc; ++j)
-                    if (cv[j] >= thr) { only = ci[j]; p.cand[flat * CAP + keep] = ci[j]; ++keep; }
-                if (overflow || keep == 0) {
-                    p.best[flat] = -2;
-                } else if (keep == 1) {
-                    p.best[flat] = only;
-                } else {
-                    for (int j = keep; j < CAP; ++j) p.cand[flat * CAP + j] = -1;
-                    p.best[flat] = -1;
+            // ---- merge the two column halves of the row and publish
+            float* mg = s_merge + row_in_tile * MERGE_WORDS;
+            if (half == 1) {
+                mbar_wait(smem_u32(merge_empty), (tile_it & 1u) ^ 1u);
+                mg[0] = rb;
+                mg[1] = __int_as_float(cnt); mg[2] = __int_as_float(p0);
+                mg[3] = __int_as_float(p1); mg[4] = __int_as_float(p2);
+                mbar_arrive(smem_u32(merge_full));
+            } else {
+                mbar_wait(smem_u32(merge_full), tile_it & 1u);
+                const float rb1 = mg[0];
+                const int cnt1 = __float_as_int(mg[1]);
+                const int o0 = __float_as_int(mg[2]), o1 = __float_as_int(mg[3]), o2 = __float_as_int(mg[4]);
+                mbar_arrive(smem_u32(merge_empty));
+                if (m < p.rows) {
+                    const int64_t flat = h * p.rows + m;
+                    const float t = fmaxf(rb, rb1) - band;
+                    // a half whose own best is below the row's band contributes nothing
+                    const bool use0 = rb >= t, use1 = rb1 >= t;
+                    const bool lost = (use0 && cnt > 3) || (use1 && cnt1 > 3);
+                    int keep = 0, only = -1;
+                    int32_t* cd = p.cand + flat * CAP;
+                    if (use0) {
+                        if (p2 >= 0) { only = p2; cd[keep++] = p2; }
+                        if (p1 >= 0) { only = p1; cd[keep++] = p1; }
+                        if (p0 >= 0) { only = p0; cd[keep++] = p0; }
+                    }
+                    if (use1) {
+                        if (o2 >= 0) { only = o2; cd[keep++] = o2; }
+                        if (o1 >= 0) { only = o1; cd[keep++] = o1; }
+                        if (o0 >= 0) { only = o0; cd[keep++] = o0; }
+                    }
+                    // NaN rows / infinite band (|x| outside the fp16 range) / lost candidates
+                    if (lost || keep == 0 || !(t > -INFINITY)) {
+                        p.best[flat] = -2;
+                    } else if (keep == 1) {
+                        p.best[flat] = only;
+                    } else {
+                        for (int j = keep; j < CAP; ++j) cd[j] = -1;
+                        p.best[flat] = -1;
+                    }
                 }
             }
         }
@@ -524,7 +618,7 @@ __global__ void vq_tc_ne2_kernel(const float* __restrict__ embed, const float* _
 }
 
 struct Plan {
-    int n_tiles, kcn, sb, sa;
+    int n_tiles, kcn, sb, a_slots;
     bool resident;
     size_t smem, img_bytes, ne2_bytes;
 };
@@ -532,20 +626,25 @@ struct Plan {
 static bool make_plan(const VqView& q, Plan& pl) {
     pl.n_tiles = (q.K + BN - 1) / BN;
     pl.kcn = (q.D + BK - 1) / BK;
-    const size_t avail = SMEM_MAX - SMEM_EXTRA - 1024;
+    const size_t avail = SMEM_MAX - SMEM_EXTRA;
     const size_t a_res = (size_t)pl.kcn * A_CHUNK_BYTES;
-    pl.resident = pl.kcn <= MAX_KC && a_res + 2 * (size_t)B_STAGE_BYTES <= avail;
+    // the B ring needs as many stages as one code tile has chunks to keep a whole tile in
+    // flight, but never more than 4; at least 2
+    const size_t sb_want = pl.kcn >= 4 ? 4 : (pl.kcn >= 2 ? (size_t)pl.kcn : 2);
+    pl.resident = a_res + 2 * (size_t)B_STAGE_BYTES <= avail;
     if (pl.resident) {
-        pl.sa = 0;
-        size_t sb = (avail - a_res) / B_STAGE_BYTES;
-        pl.sb = (int)(sb > 4 ? 4 : sb);
+        // second A buffer (next row tile loads under this tile's MMAs) when it still leaves >= 2 stages
+        const bool dbl = 2 * a_res + 2 * (size_t)B_STAGE_BYTES <= avail && 2 * pl.kcn <= MAX_AS;
+        pl.a_slots = pl.kcn * (dbl ? 2 : 1);
+        size_t sb = (avail - (size_t)pl.a_slots * A_CHUNK_BYTES) / B_STAGE_BYTES;
+        pl.sb = (int)(sb > sb_want ? sb_want : sb);
     } else {
-        pl.sa = 4;
+        pl.a_slots = 4;
         pl.sb = 4;
     }
-    const size_t a_bytes = pl.resident ? a_res : (size_t)pl.sa * A_CHUNK_BYTES;
-    pl.smem = a_bytes + (size_t)pl.sb * B_STAGE_BYTES + SMEM_EXTRA + 1024;
-    // at least half of the SM's shared memory: one CTA per SM (it owns all 512 TMEM columns)
+    if (pl.a_slots > MAX_AS || pl.sb > MAX_SB || pl.sb < 2) return false;
+    pl.smem = (size_t)pl.a_slots * A_CHUNK_BYTES + (size_t)pl.sb * B_STAGE_BYTES + SMEM_EXTRA;
+    // more than half of the SM's shared memory: one CTA per SM (it owns all 512 TMEM columns)
     if (pl.smem < 120 * 1024) pl.smem = 120 * 1024;
     pl.img_bytes = (size_t)q.embed_heads * pl.n_tiles * pl.kcn * B_STAGE_BYTES;
     pl.ne2_bytes = (size_t)q.embed_heads * pl.n_tiles * BN * 4;
@@ -612,7 +711,7 @@ int vq_assign_tc(const VqView& q, const float* e2, int32_t* best, int32_t** cand
     TcParams p;
     p.x = q.x; p.x_row_stride = q.x_row_stride; p.x_head_stride = q.x_head_stride;
     p.heads = q.heads; p.embed_heads = q.embed_heads; p.rows = q.rows;
-    p.K = q.K; p.D = q.D; p.n_tiles = pl.n_tiles; p.kcn = pl.kcn; p.sb = pl.sb; p.sa = pl.sa;
+    p.K = q.K; p.D = q.D; p.n_tiles = pl.n_tiles; p.kcn = pl.kcn; p.sb = pl.sb; p.a_slots = pl.a_slots;
     p.img = img; p.ne2 = ne2; p.head_stats = head_stats;
     // fp32 accumulation of D exact fp16 x fp16 products (tensor core) and of the fp32 re-score
     // chain: <= D 2^-22 |x||e| together.  The Euclidean score adds the fp32 roundings of
