@@ -378,6 +378,125 @@ def run_ours(args, w):
         dist.destroy_process_group()
 
 
+def run_partitioned(args, w):
+    """Strong scaling of one full-batch step on a 1-D destination-partitioned graph (BASELINE
+    configs[3], ogbn-products-shaped): every rank owns N/world nodes, their in-edges (forward) and
+    out-edges (backward); per layer one NCCL all-gather of the row blocks (halo exchange) forward
+    and one of the g_out blocks backward; SyncBatchNorm statistics, EMA code statistics and dense
+    gradients are all-reduced.  The graph is static (full-batch training), so K0 runs once."""
+    import torch.distributed as dist
+    import __graft_entry__ as G
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    if rank == 0:
+        G.build()
+    if world > 1:
+        dist.barrier()
+    import stemgnn_b200 as S
+    from stemgnn_b200 import _lib
+    g = torch.Generator().manual_seed(4)
+    n, e = w["n"], w["e"]
+    lo, hi = S.partition_1d(n, world)[rank]
+    # same seeded global edge list on every rank, generated in slices to bound host memory
+    fwd_parts, bwd_parts, chunk = [], [], 1 << 24
+    for c0 in range(0, e, chunk):
+        ei = torch.randint(0, n, (2, min(chunk, e - c0)), generator=g).to(dev)
+        fwd_parts.append(S.local_edges(ei, lo, hi, 1)[0])
+        bwd_parts.append(S.local_edges(ei, lo, hi, 0)[0])
+        del ei
+    x_all = torch.randn(n, w["f"], generator=g)
+    x_h = x_all[lo:hi].contiguous().pin_memory()
+    del x_all
+    pg = S.PartitionedGraph(None, n, rank=rank, world=world,
+                            pre_split=(torch.cat(fwd_parts, 1), torch.cat(bwd_parts, 1)))
+    del fwd_parts, bwd_parts
+    enc, vq, opt = build_models(w, dev, S)
+    if world > 1:
+        enc = nn.SyncBatchNorm.convert_sync_batchnorm(enc)
+        opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
+    params = list(enc.parameters())
+
+    def step(x):
+        opt.zero_grad(set_to_none=True)
+        z = enc(x, pg)
+        q, ind, vq_loss, _ = vq(z)
+        loss = (q.square().sum() / (n * q.size(1))) + vq_loss.sum() * ((hi - lo) / n)
+        loss.backward()
+        if world > 1:
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat)
+            o = 0
+            for p in params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
+        opt.step()
+        return loss
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    x_d = x_h.to(dev)
+    for _ in range(max(args.warmup, 3)):
+        step(x_d)
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _lib.TRACE = []
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step(x_d)
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    launches = (_lib.launch_count() - l0) / args.steps
+    trace, _lib.TRACE = _lib.TRACE, None
+    x_s = torch.empty_like(x_d)
+    loss_h = torch.empty(1).pin_memory()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        x_s.copy_(x_h, non_blocking=True)
+        loss_h.copy_(step(x_s).detach().reshape(1), non_blocking=True)
+    e3.record()
+    sync_all()
+    ms_e2e = e2.elapsed_time(e3)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    if rank == 0:
+        pk = peaks()
+        kern = summarize_trace(trace, args.steps, pk, False)
+        roof = roofline_of(kern, "aggregate", pk, False)
+        units = w["layers"] * e
+        line = dict(metric=METRIC, value=units * args.steps / (ms / 1e3), unit="edges/s", n_gpus=world,
+                    steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms / args.steps,
+                    higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
+                    data="synthetic", vq_nodes_per_s=n * args.steps / (ms / 1e3),
+                    config=dict(workload=w["desc"], layers=w["layers"], nodes=n, edges=e,
+                                l2="working set (N x F fp32 >= 980 MB) exceeds the 126 MB L2",
+                                parallelism=f"1-D destination partition x{world}, NCCL halo all-gather per layer"),
+                    e2e=dict(value=units * args.steps / (ms_e2e / 1e3), unit="edges/s",
+                             ms_per_step=ms_e2e / args.steps,
+                             h2d_bytes_per_step=x_h.numel() * 4 * world, d2h_bytes_per_step=4 * world),
+                    gpu_launches=launches, roofline=roof, kernels=kern, clocks=clocks)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -388,10 +507,14 @@ def main():
     ap.add_argument("--cpu-frac", type=float, default=1.0,
                     help="fraction of the graph the CPU arm runs per step (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--partition", action="store_true",
+                    help="1-D destination partition across the ranks (strong scaling, static graph)")
     args = ap.parse_args()
     w = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, w)
+    elif args.partition or args.workload == "products":
+        run_partitioned(args, w)
     else:
         run_ours(args, w)
 

@@ -10,11 +10,12 @@ import torch.nn.functional as F
 from torch import Tensor
 
 from .graph import GraphStructure, structure_of
+from .partition import PartitionedGraph
 from .ops import aggregate
 
 
 def _graph(edge_index, num_nodes):
-    if isinstance(edge_index, GraphStructure):
+    if isinstance(edge_index, (GraphStructure, PartitionedGraph)):
         return edge_index
     if not isinstance(edge_index, Tensor):
         raise NotImplementedError("SparseTensor adjacency is not supported; pass edge_index [2,E]")
@@ -105,7 +106,11 @@ class GCNConv(nn.Module):
     def forward(self, x: Tensor, edge_index, edge_weight: Optional[Tensor] = None) -> Tensor:
         if edge_weight is not None:
             raise NotImplementedError("GCNConv with explicit edge_weight is not on the hot path")
-        g_sl, w = _graph(edge_index, x.size(0)).gcn()
+        g = _graph(edge_index, x.size(0))
+        if isinstance(g, PartitionedGraph):
+            raise NotImplementedError("GCNConv on a partitioned graph (symmetric normalisation needs "
+                                      "the degrees of remote sources) is not built yet")
+        g_sl, w = g.gcn()
         out = aggregate(self.lin(x), g_sl, reduce="sum", edge_weight=w)
         return out + self.bias if self.bias is not None else out
 

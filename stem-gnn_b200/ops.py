@@ -6,6 +6,7 @@ import torch
 
 from . import _lib
 from .graph import GraphStructure
+from .partition import PartitionedGraph
 
 REDUCE_SUM, REDUCE_MEAN = 0, 1
 ACT_NONE, ACT_RELU = 0, 1
@@ -80,6 +81,37 @@ class _Aggregate(torch.autograd.Function):
         return g_x, None, None, None, None, None, None, None, None
 
 
+class _PartAggregate(torch.autograd.Function):
+    """The same aggregation on a 1-D destination-partitioned graph: x holds this rank's rows;
+    the forward all-gathers the row blocks (halo exchange) and runs K1 on the owned destination
+    rows, the backward all-gathers the g_out blocks and runs K2 on the owned source rows."""
+
+    @staticmethod
+    def forward(ctx, x, pg, reduce, act):
+        x = _f32c(x, "x")
+        if x.dim() != 2 or x.size(0) != pg.num_nodes:
+            raise ValueError(f"x must hold this rank's {pg.num_nodes} rows")
+        fwd = pg.fwd_csr()
+        x_full = pg.gather_rows(x)
+        out = torch.empty_like(x)
+        _aggregate_call(fwd, x_full.size(0), x_full, out,
+                        row_cnt=fwd.cnt if reduce == REDUCE_MEAN else None, act=act)
+        ctx.pg, ctx.reduce, ctx.act = pg, reduce, act
+        ctx.save_for_backward(x)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        (x,) = ctx.saved_tensors
+        pg = ctx.pg
+        g_full = pg.gather_rows(_f32c(g_out, "grad"))
+        g_x = torch.empty_like(x)
+        _aggregate_call(pg.bwd_csr(), g_full.size(0), g_full, g_x,
+                        gather_cnt=pg.cnt_full() if ctx.reduce == REDUCE_MEAN else None,
+                        row_x=x if ctx.act == ACT_RELU else None, act=ctx.act, backward=True)
+        return g_x, None, None, None
+
+
 def aggregate(x, graph, *, to_row=1, reduce="mean", act="none", edge_attr=None, edge_type=None,
               type_table=None, edge_weight=None):
     """Fused gather -> message -> reduce over a GraphStructure.
@@ -87,8 +119,15 @@ def aggregate(x, graph, *, to_row=1, reduce="mean", act="none", edge_attr=None, 
     edge_attr: dense [E, F] per-edge features in original edge order (what the reference passes,
     model/encoder.py:94-97), or (type_table [T,F], edge_type [E] int32/int64) for the table form.
     Gradients flow to `x` only: edge features / weights are data on this path."""
+    if isinstance(graph, PartitionedGraph):
+        if to_row != 1 or any(t is not None for t in (edge_attr, edge_type, type_table, edge_weight)):
+            raise NotImplementedError("partitioned graphs: destination aggregation without per-edge "
+                                      "data (the BASELINE products-shaped configuration)")
+        r = {"mean": REDUCE_MEAN, "sum": REDUCE_SUM, "add": REDUCE_SUM}[reduce]
+        a = {"none": ACT_NONE, "relu": ACT_RELU}[act]
+        return _PartAggregate.apply(x, graph, r, a)
     if not isinstance(graph, GraphStructure):
-        raise TypeError("graph must be a GraphStructure")
+        raise TypeError("graph must be a GraphStructure or a PartitionedGraph")
     for t, n in ((edge_attr, "edge_attr"), (type_table, "type_table"), (edge_weight, "edge_weight")):
         if t is not None and t.requires_grad:
             raise NotImplementedError(f"gradient w.r.t. {n} is not part of the hot path")

@@ -1,0 +1,97 @@
+"""CPU (gloo, world_size 2): the integer bookkeeping of the 1-D destination partition and the
+halo all-gather layout.  The partitioned aggregation is emulated with the oracle's CPU propagate
+on each rank's local edge list and must equal the single-graph oracle bit for bit."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def test_partition_ranges_cover_the_nodes():
+    from stemgnn_b200.partition import block_size, partition_1d
+    from oracle.graph_ref import partition_1d_ref
+    for n, p in [(10, 4), (0, 3), (7, 8), (169343, 8), (2449029, 8), (16, 2)]:
+        parts = partition_1d(n, p)
+        assert parts == partition_1d_ref(n, p) if n > 0 else all(a == b == 0 for a, b in parts)
+        assert sum(hi - lo for lo, hi in parts) == n
+        assert all(hi - lo <= block_size(n, p) for lo, hi in parts)
+        assert all(lo == r * block_size(n, p) or lo == n for r, (lo, hi) in enumerate(parts))
+
+
+def test_local_edges_keep_original_order():
+    from stemgnn_b200.partition import local_edges, partition_1d
+    g = torch.Generator().manual_seed(0)
+    n, e = 53, 700
+    ei = torch.randint(0, n, (2, e), generator=g)
+    seen = torch.zeros(e, dtype=torch.int64)
+    for owner_row in (0, 1):
+        seen.zero_()
+        for lo, hi in partition_1d(n, 4):
+            loc, eid = local_edges(ei, lo, hi, owner_row)
+            assert torch.all(eid[1:] > eid[:-1])                       # original order kept
+            assert torch.equal(loc[owner_row] + lo, ei[owner_row, eid])
+            assert torch.equal(loc[1 - owner_row], ei[1 - owner_row, eid])
+            assert loc.numel() == 0 or (0 <= int(loc[owner_row].min()) and int(loc[owner_row].max()) < hi - lo)
+            seen[eid] += 1
+        assert torch.all(seen == 1)                                    # every edge on exactly one rank
+
+
+def _worker(rank, world, port, n, e, f, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import propagate_ref as P
+        from stemgnn_b200.partition import block_size, local_edges, partition_1d
+        g = torch.Generator().manual_seed(3)
+        ei = torch.randint(0, n, (2, e), generator=g)
+        x = torch.randn(n, f, generator=g)
+        go = torch.randn(n, f, generator=g)
+        lo, hi = partition_1d(n, world)[rank]
+        per = block_size(n, world)
+        # halo exchange of the padded row blocks: row g of the result is global node g
+        blk = torch.zeros(per, f)
+        blk[:hi - lo] = x[lo:hi]
+        full = torch.empty(world * per, f)
+        dist.all_gather_into_tensor(full, blk)
+        assert torch.equal(full[:n], x)
+        # forward on the owned destinations == the rows of the single-graph result
+        ref_x = x.clone().requires_grad_(True)
+        ref = P.sage_propagate_ref(ref_x, ei, None, n, "mean")
+        ref.backward(go)
+        fwd, _ = local_edges(ei, lo, hi, 1)
+        xf = full.clone()
+        x_j = torch.relu(xf.index_select(0, fwd[0]))
+        out = P.scatter_mean_ref(x_j, fwd[1], hi - lo)
+        assert torch.equal(out, ref.detach()[lo:hi])
+        # backward on the owned sources: gathered g_out / count of the destination, relu mask of x
+        deg = torch.bincount(ei[1], minlength=n).clamp(min=1).float()
+        gs = go / deg.view(-1, 1)
+        bwd, _ = local_edges(ei, lo, hi, 0)
+        contrib = gs.index_select(0, bwd[1]) * (x[lo:hi].index_select(0, bwd[0]) > 0)
+        gx = torch.zeros(hi - lo, f).index_add_(0, bwd[0], contrib)
+        assert torch.equal(gx, ref_x.grad[lo:hi])
+        ret[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_partitioned_aggregation_two_ranks_gloo():
+    world = 2
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, world, port, 101, 900, 12, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(100)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert dict(ret) == {0: 1, 1: 1}
