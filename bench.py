@@ -151,17 +151,19 @@ def summarize_trace(trace, steps, pk, n_feat_bytes_l2):
     for name, nbytes, flops, launches, e0, e1 in trace:
         ms = e0.elapsed_time(e1)
         key = "aggregate" if name.startswith("aggregate") else name
-        d = fam.setdefault(key, dict(ms=0.0, calls=0, bytes_min=0, bytes_gather=0, flops=0))
+        d = fam.setdefault(key, dict(ms=0.0, calls=0, bytes_min=0, bytes_gather=0, bytes_alg=0, flops=0))
         d["ms"] += ms; d["calls"] += 1; d["flops"] += flops
         if isinstance(nbytes, tuple):
-            d["bytes_min"] += nbytes[0]; d["bytes_gather"] += nbytes[1]
+            d["bytes_min"] += nbytes[0]; d["bytes_gather"] += nbytes[1]; d["bytes_alg"] += nbytes[2]
         else:
-            d["bytes_min"] += nbytes; d["bytes_gather"] += nbytes
+            d["bytes_min"] += nbytes; d["bytes_gather"] += nbytes; d["bytes_alg"] += nbytes
     out = {}
     for k, d in fam.items():
         sec = d["ms"] / 1e3
         o = dict(ms_per_step=d["ms"] / steps, calls_per_step=d["calls"] / steps)
         if sec > 0:
+            o["gbps_alg"] = d["bytes_alg"] / sec / 1e9
+            o["alg_bytes_per_call"] = d["bytes_alg"] / d["calls"]
             o["gbps_alg_min"] = d["bytes_min"] / sec / 1e9
             o["gbps_alg_gather"] = d["bytes_gather"] / sec / 1e9
             if d["flops"]:
@@ -177,10 +179,11 @@ def roofline_of(kern, name, pk, x_fits_l2):
         return dict(kernel=name, bound="tensor", achieved=k["tflops"], peak=pk["tc_sus"] or pk["tc"],
                     unit="TFLOP/s", frac=k["tflops"] / (pk["tc_sus"] or pk["tc"]), traffic=None,
                     peak_source=pk["src"] + " (sustained: kernel timed inside a long step)")
-    a = k["gbps_alg_min"] if x_fits_l2 else k["gbps_alg_gather"]
+    a = k["gbps_alg"]
     return dict(kernel=name, bound="hbm", achieved=a, peak=pk["hbm"], unit="GB/s", frac=a / pk["hbm"],
-                traffic=None, peak_source=pk["src"],
-                bytes_model="compulsory (X fits L2)" if x_fits_l2 else "one source row per edge")
+                traffic=None, peak_source=pk["src"], alg_bytes_per_launch=k["alg_bytes_per_call"],
+                bytes_model="per launch: compulsory bytes (every row once) while the gathered matrix "
+                            "fits the 126 MB L2, else one source row per edge (SURVEY.md 8d)")
 
 
 def cpu_baseline_step_fn(w, threads):
@@ -348,7 +351,10 @@ def run_ours(args, w):
     roof = roofline_of(kern, top, pk, x_fits_l2)
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
-        roof["traffic"] = json.load(open(traffic_file)).get(top)
+        tr = json.load(open(traffic_file)).get(args.workload, {}).get(top)
+        if tr:
+            roof["traffic"] = tr["bytes_per_launch"]
+            roof["traffic_source"] = tr["source"]
     line = dict(metric=METRIC, value=value, unit="edges/s", n_gpus=world, steps=args.steps,
                 warmup=max(args.warmup, 3), ms_per_step=ms / args.steps, higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",

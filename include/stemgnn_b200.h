@@ -94,6 +94,16 @@ typedef struct {
 
 int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t stream);
 
+/* K2a. out[r, :] = x[r, :] / cnt[r] (IEEE division, rows of `feat` floats; out may alias x).
+ * MeanAggregation's backward divides the upstream gradient of a destination by its clamped count
+ * BEFORE index_add_ scatters it over the edges (torch_geometric MeanAggregation -> scatter 'mean'
+ * autograd; reference call site STEM-GNN/model/encoder.py:82).  The quotient is the same for every
+ * edge of that destination, so the host op applies it once per row with this call and then runs
+ * stemgnn_aggregate(backward=1, gather_cnt=NULL): same bits as dividing per edge, E*F fewer
+ * divisions, and in the partitioned path no count exchange. */
+int stemgnn_row_scale(int64_t n_rows, int64_t feat, const float* x, const float* cnt, float* out,
+                      stemgnn_stream_t stream);
+
 /* ------------------------------------------------------------------ K3: VQ assignment
  * Replaces dist = -cdist / einsum, argmax, one_hot, one_hot @ embed (or the eval gather) and
  * the MSE commitment partial (model/vq.py:472-482, 650-659, 79-80, 1007), and fuses the head

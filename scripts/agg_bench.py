@@ -1,0 +1,41 @@
+"""A/B timing of the aggregation kernel (K1/K2) alone on graph shapes of the bench workloads.
+CUDA events on the current stream, L2 flushed between launches.  Usage: python scripts/agg_bench.py [tag]"""
+import importlib, json, os, sys, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+pkg = importlib.import_module("stem-gnn_b200")
+from importlib import import_module
+ops = import_module("stem-gnn_b200.ops"); graph = import_module("stem-gnn_b200.graph")
+
+def run(n, e, f, reps=5, seed=0):
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(seed)
+    ei = torch.randint(0, n, (2, e), generator=g).to(dev)
+    x = torch.randn(n, f, device=dev, requires_grad=True)
+    gs = graph.GraphStructure(ei, n)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    res = {}
+    for name in ("fwd", "bwd"):
+        ts = []
+        for r in range(reps + 2):
+            flush.zero_()
+            if name == "fwd":
+                s, t = torch.cuda.Event(True), torch.cuda.Event(True)
+                s.record(); out = ops.aggregate(x, gs, reduce="mean"); t.record()
+            else:
+                out = ops.aggregate(x, gs, reduce="mean"); go = torch.ones_like(out)
+                flush.zero_()
+                s, t = torch.cuda.Event(True), torch.cuda.Event(True)
+                s.record(); out.backward(go); t.record(); x.grad = None
+            torch.cuda.synchronize()
+            if r >= 2: ts.append(s.elapsed_time(t) * 1e3)
+        res[name] = min(ts)
+    gb_gather = (e * f * 4 + n * f * 4 + e * 4 + n * 4) / 1e9
+    gb_min = (2 * n * f * 4 + e * 4 + n * 4) / 1e9
+    print(json.dumps(dict(n=n, e=e, f=f, fwd_us=round(res["fwd"], 1), bwd_us=round(res["bwd"], 1),
+                          fwd_gather_GBps=round(gb_gather / res["fwd"] * 1e6), fwd_min_GBps=round(gb_min / res["fwd"] * 1e6))), flush=True)
+
+if __name__ == "__main__":
+    print("tag", sys.argv[1:] , os.environ.get("STEMGNN_AGG_ROWWARP"))
+    run(169343, 1166243, 128); run(169343, 1166243, 256)
+    run(2449029 // 2, 61859140 // 2, 100); run(2449029 // 2, 61859140 // 2, 256)
+    run(2708, 10556, 1432); run(500000, 5000000, 64); run(500000, 2000000, 512)

@@ -45,6 +45,7 @@ SIGNATURES = {
     "stemgnn_csr_build": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
     "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "stemgnn_aggregate": (_i32, [C.POINTER(AggregateArgs), _vp]),
+    "stemgnn_row_scale": (_i32, [_i64, _i64, _vp, _vp, _vp, _vp]),
     "stemgnn_vq_assign_workspace": (_i32, [C.POINTER(VqAssignArgs), C.POINTER(C.c_size_t)]),
     "stemgnn_vq_assign": (_i32, [C.POINTER(VqAssignArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_vq_backward": (_i32, [_vp, _vp, _vp, _vp, _f32, _i64, _vp, _vp]),

@@ -9,6 +9,7 @@ from .graph import GraphStructure
 from .partition import PartitionedGraph
 
 REDUCE_SUM, REDUCE_MEAN = 0, 1
+L2_BYTES = 126e6
 ACT_NONE, ACT_RELU = 0, 1
 
 
@@ -42,9 +43,21 @@ def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_c
         idx += E * 4 + (E * F * 4 if edge_feat is not None else 0) + (E * 4 if edge_type is not None or edge_weight is not None else 0)
     rows = csr.n * F * 4 * (2 if row_x is not None else 1)
     b_min, b_gather = n_g * F * 4 + rows + idx, E * F * 4 + rows + idx
+    # the compulsory model while the gathered matrix fits the 126 MB L2, one
+    # source row per edge once it does not
+    b_alg = b_min if n_g * F * 4 <= L2_BYTES else b_gather
     name = "aggregate_bwd" if backward else "aggregate_fwd"
-    with _lib.traced(name, (b_min, b_gather), 0, 1):
+    with _lib.traced(name, (b_min, b_gather, b_alg), 0, 1):
         _lib.check(_lib.lib().stemgnn_aggregate(C.byref(a), _lib.stream()))
+
+
+def _row_scale(g, cnt):
+    """g[r, :] / cnt[r] (K2a): MeanAggregation's backward division, once per destination row."""
+    out = torch.empty_like(g)
+    n, f = g.shape
+    with _lib.traced("row_scale", 2 * n * f * 4 + n * 4, 0, 1):
+        _lib.check(_lib.lib().stemgnn_row_scale(n, f, _lib.ptr(g), _lib.ptr(cnt), _lib.ptr(out), _lib.stream()))
+    return out
 
 
 class _Aggregate(torch.autograd.Function):
@@ -73,8 +86,9 @@ class _Aggregate(torch.autograd.Function):
         graph = ctx.graph
         bwd = graph.grouped_by(1 - ctx.to_row)
         g_x = torch.empty_like(x)
+        if ctx.reduce == REDUCE_MEAN:
+            g_out = _row_scale(g_out, graph.grouped_by(ctx.to_row).cnt)
         _aggregate_call(bwd, x.size(0), g_out, g_x,
-                        gather_cnt=graph.grouped_by(ctx.to_row).cnt if ctx.reduce == REDUCE_MEAN else None,
                         edge_feat=edge_feat, type_table=type_table, edge_type=edge_type,
                         edge_weight=edge_weight, row_x=x if ctx.act == ACT_RELU else None,
                         act=ctx.act, backward=True)
@@ -104,10 +118,12 @@ class _PartAggregate(torch.autograd.Function):
     def backward(ctx, g_out):
         (x,) = ctx.saved_tensors
         pg = ctx.pg
-        g_full = pg.gather_rows(_f32c(g_out, "grad"))
+        g_out = _f32c(g_out, "grad")
+        if ctx.reduce == REDUCE_MEAN:       # own rows, own counts: no count exchange
+            g_out = _row_scale(g_out, pg.fwd_csr().cnt)
+        g_full = pg.gather_rows(g_out)
         g_x = torch.empty_like(x)
         _aggregate_call(pg.bwd_csr(), g_full.size(0), g_full, g_x,
-                        gather_cnt=pg.cnt_full() if ctx.reduce == REDUCE_MEAN else None,
                         row_x=x if ctx.act == ACT_RELU else None, act=ctx.act, backward=True)
         return g_x, None, None, None
 

@@ -9,7 +9,8 @@ splitting the nodes into `world` contiguous, equal-sized blocks: rank r owns the
   layer.  Because the blocks are equal-sized and contiguous, a node's row in the gathered matrix is
   its global id: no index remap.
 * backward (autograd of the above): g_x of an owned source sums over the edges whose SOURCE the
-  rank owns, gathering g_out / count of all destinations -> one all-gather of the g_out blocks.
+  rank owns, gathering g_out / count of all destinations; each rank divides its own g_out rows by
+  its own counts first (K2a), so one all-gather of the scaled g_out blocks is all that moves.
 
 A row's edges all live on one rank and keep their relative order, so the sums are the same fp32
 sums, in the same order, as on one GPU: partitioned results are bit-identical to single-GPU ones.
@@ -77,7 +78,6 @@ class PartitionedGraph:
         self.fwd_edges, self.bwd_edges = fwd, bwd
         self._gather = gather
         self._csr = {}
-        self._cnt_full = None
 
     # ---- structure (K0 on the local edge lists) ------------------------------------------------
     def fwd_csr(self) -> CSR:
@@ -108,10 +108,3 @@ class PartitionedGraph:
         with _lib.traced("halo_all_gather", (self.world - 1) * self.per * f * local.element_size(), 0, 0):
             dist.all_gather_into_tensor(out, blk.contiguous(), group=self.group)
         return out
-
-    def cnt_full(self) -> torch.Tensor:
-        """float(max(in-degree, 1)) of EVERY node, [world*per]: the divisor of the gathered g_out
-        rows in the backward pass (MeanAggregation's clamped count of the destination)."""
-        if self._cnt_full is None:
-            self._cnt_full = self.gather_rows(self.fwd_csr().cnt.view(-1, 1)).view(-1).contiguous()
-        return self._cnt_full

@@ -153,3 +153,25 @@ def test_linearity_property_large():
     deg = torch.bincount(ei[1], minlength=n).float()
     ones = S.aggregate(torch.ones(n, 4, device=DEV), gs, reduce="sum")
     assert torch.equal(ones[:, 0], deg)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,e,f", [(300, 2000, 256), (1000, 3000, 100), (50, 400, 7)])
+def test_row_scale_then_sum_equals_per_edge_division(n, e, f):
+    """K2a + K2 without gather_cnt gives the same bits as K2 dividing every gathered row per edge
+    (the C-ABI keeps both; the host op uses the first)."""
+    from importlib import import_module
+    ops = import_module("stem-gnn_b200.ops"); graph = import_module("stem-gnn_b200.graph")
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(n + e)
+    ei = torch.randint(0, n, (2, e), generator=g).to(dev)
+    gs = graph.GraphStructure(ei, n)
+    go = torch.randn(n, f, generator=g).to(dev)
+    cnt = gs.grouped_by(1).cnt
+    bwd = gs.grouped_by(0)
+    a = torch.empty_like(go); b = torch.empty_like(go)
+    ops._aggregate_call(bwd, n, go, a, gather_cnt=cnt, backward=True)
+    scaled = ops._row_scale(go, cnt)
+    assert torch.equal(scaled, go / cnt[:, None])
+    ops._aggregate_call(bwd, n, scaled, b, backward=True)
+    assert torch.equal(a, b)

@@ -41,7 +41,7 @@ def test_partitioned_rows_equal_single_graph(world, reduce, act):
     pad = lambda t: torch.cat([t, t.new_zeros(world * per - n, t.size(1))])
     deg = torch.bincount(ei[1], minlength=n).clamp(min=1).float().view(-1, 1)
     for rank, (lo, hi) in enumerate(S.partition_1d(n, world)):
-        q = [pad(x), pad(go)] + ([pad(deg)] if reduce == "mean" else [])
+        q = [pad(x), pad(go / deg if reduce == "mean" else go)]   # each rank scales its own g_out rows
         pg = S.PartitionedGraph(ei, n, rank=rank, world=world, gather=_Queue(q))
         assert pg.num_nodes == hi - lo
         xl = x[lo:hi].clone().requires_grad_(True)
