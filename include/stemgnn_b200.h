@@ -143,6 +143,59 @@ int stemgnn_vq_assign(const stemgnn_vq_assign_args* args_host, void* workspace,
 int stemgnn_vq_backward(const float* g_q, const float* x, const float* q, const float* g_loss,
                         float coef, int64_t numel, float* g_x, stemgnn_stream_t stream);
 
+/* ------------------------------------------------------------------ K5: dense layers (next row f-1)
+ * out[m, n] = sum_{s < n_src} sum_k A_s[m, k] * W_s[n, k]  (+ bias[n]),  fp32 in / fp32 out.
+ * Replaces `self.lin_l(out) + self.lin_r(x_r)` of MySAGEConv.forward (reference
+ * STEM-GNN/model/encoder.py:84-88) as ONE call with two sources, the single Linear of the GCN / GIN
+ * layers, and -- with w_transposed = 1, W_s given as [k, n] -- any A @ W product such as the
+ * backward-data term g_out @ lin.weight.  Runs on the tcgen05 tensor cores as 3xTF32 (operands
+ * split hi + lo, three MMAs, fp32 accumulate): within 1e-5 of torch's fp32 result, full fp32 range.
+ * k[s], lda[s] must be multiples of 4 and a[s] 16-byte aligned (row segments are read as float4). */
+typedef struct {
+    int64_t m;            /* rows */
+    int64_t n;            /* output features */
+    int32_t n_src;        /* 1 or 2 */
+    int32_t w_transposed; /* 0: w[s] is [n, k[s]] (nn.Linear.weight); 1: w[s] is [k[s], n] */
+    const float* a[2];    /* [m, k[s]] row-major, row stride lda[s] floats */
+    int64_t lda[2];
+    int64_t k[2];
+    const float* w[2];    /* row stride ldw[s] floats */
+    int64_t ldw[2];
+    const float* bias;    /* [n] or NULL */
+    float* out;           /* [m, n], row stride ldo floats */
+    int64_t ldo;
+} stemgnn_linear_args;
+
+int stemgnn_linear_workspace(const stemgnn_linear_args* args_host, size_t* bytes_host);
+int stemgnn_linear(const stemgnn_linear_args* args_host, void* workspace, size_t workspace_bytes,
+                   stemgnn_stream_t stream);
+
+/* K6. Weight (and bias) gradients of the same layers:
+ *     gw[s][n, k] = sum_m g[m, n] * a[s][m, k],      gbias[n] = sum_m g[m, n]
+ * (autograd of nn.Linear inside MySAGEConv / GCN / GIN, reference model/encoder.py:84-88).  3xTF32 on
+ * tcgen05 with the row reduction cut into slabs of 512 rows whose fp32 tiles are added round-to-
+ * nearest: the tensor-core accumulator truncates, so a single 169k-row accumulation would not hold
+ * 1e-5.  Deterministic (fixed summation order).  n, k[s], ldg, lda[s] multiples of 4; g, a[s]
+ * 16-byte aligned; at most 64 tiles of 256 x 256 weights per call. */
+typedef struct {
+    int64_t m;
+    int64_t n;
+    int32_t n_src;
+    int32_t reserved;
+    const float* g;       /* [m, n] upstream gradient, row stride ldg */
+    int64_t ldg;
+    const float* a[2];    /* [m, k[s]] layer inputs */
+    int64_t lda[2];
+    int64_t k[2];
+    float* gw[2];         /* [n, k[s]] outputs, row stride ldgw[s] */
+    int64_t ldgw[2];
+    float* gbias;         /* [n] or NULL */
+} stemgnn_linear_wgrad_args;
+
+int stemgnn_linear_wgrad_workspace(const stemgnn_linear_wgrad_args* args_host, size_t* bytes_host);
+int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* args_host, void* workspace,
+                         size_t workspace_bytes, stemgnn_stream_t stream);
+
 /* ------------------------------------------------------------------ K4: EMA statistics
  * Replaces onehot.sum(1) and einsum('h n d, h n c -> h c d') (model/vq.py:492,497 / 665,670):
  * counts [embed_heads,K] fp32 and sums [embed_heads,K,D] fp32.  Deterministic: rows are

@@ -36,6 +36,18 @@ class VqCodeStatsArgs(C.Structure):
                 ("counts", _vp), ("sums", _vp)]
 
 
+class LinearArgs(C.Structure):
+    _fields_ = [("m", _i64), ("n", _i64), ("n_src", _i32), ("w_transposed", _i32), ("a", _vp * 2),
+                ("lda", _i64 * 2), ("k", _i64 * 2), ("w", _vp * 2), ("ldw", _i64 * 2), ("bias", _vp),
+                ("out", _vp), ("ldo", _i64)]
+
+
+class LinearWgradArgs(C.Structure):
+    _fields_ = [("m", _i64), ("n", _i64), ("n_src", _i32), ("reserved", _i32), ("g", _vp), ("ldg", _i64),
+                ("a", _vp * 2), ("lda", _i64 * 2), ("k", _i64 * 2), ("gw", _vp * 2), ("ldgw", _i64 * 2),
+                ("gbias", _vp)]
+
+
 # name -> (restype, argtypes); every symbol include/stemgnn_b200.h declares
 SIGNATURES = {
     "stemgnn_last_error": (C.c_char_p, []),
@@ -46,6 +58,10 @@ SIGNATURES = {
     "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "stemgnn_aggregate": (_i32, [C.POINTER(AggregateArgs), _vp]),
     "stemgnn_row_scale": (_i32, [_i64, _i64, _vp, _vp, _vp, _vp]),
+    "stemgnn_linear_workspace": (_i32, [C.POINTER(LinearArgs), C.POINTER(C.c_size_t)]),
+    "stemgnn_linear": (_i32, [C.POINTER(LinearArgs), _vp, C.c_size_t, _vp]),
+    "stemgnn_linear_wgrad_workspace": (_i32, [C.POINTER(LinearWgradArgs), C.POINTER(C.c_size_t)]),
+    "stemgnn_linear_wgrad": (_i32, [C.POINTER(LinearWgradArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_vq_assign_workspace": (_i32, [C.POINTER(VqAssignArgs), C.POINTER(C.c_size_t)]),
     "stemgnn_vq_assign": (_i32, [C.POINTER(VqAssignArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_vq_backward": (_i32, [_vp, _vp, _vp, _vp, _f32, _i64, _vp, _vp]),

@@ -11,6 +11,7 @@ from torch import Tensor
 
 from .graph import GraphStructure, structure_of
 from .partition import PartitionedGraph
+from . import dense
 from .ops import aggregate
 
 
@@ -69,9 +70,16 @@ class MySAGEConv(nn.Module):
                             edge_type=edge_attr[1])
         else:
             out = aggregate(x, g, reduce=self.aggr, act="relu", edge_attr=edge_attr)
-        out = self.lin_l(out)
-        if self.root_weight:
-            out = out + self.lin_r(x_r)
+        if x.is_cuda and dense.supported(out.size(1), self.out_channels):
+            # lin_l(out) + lin_r(x_r) as ONE tensor-core GEMM over the concatenated K (K5/K6)
+            if self.root_weight:
+                out = dense.linear_sum([out, x_r], [self.lin_l.weight, self.lin_r.weight], self.lin_l.bias)
+            else:
+                out = dense.linear_sum([out], [self.lin_l.weight], self.lin_l.bias)
+        else:
+            out = self.lin_l(out)
+            if self.root_weight:
+                out = out + self.lin_r(x_r)
         if self.normalize:
             out = F.normalize(out, p=2.0, dim=-1)
         return out

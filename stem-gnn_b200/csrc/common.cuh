@@ -33,6 +33,15 @@ void count_launch();  // process-wide launch counter behind stemgnn_launch_count
         }                                                                          \
     } while (0)
 
+#define SG_CHECK_CUDA(expr)                                                        \
+    do {                                                                           \
+        cudaError_t e__ = (expr);                                                  \
+        if (e__ != cudaSuccess) {                                                  \
+            stemgnn::set_error("%s: CUDA error %s", __func__, cudaGetErrorString(e__)); \
+            return STEMGNN_ECUDA;                                                  \
+        }                                                                          \
+    } while (0)
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Bump allocator over the caller-provided workspace.
