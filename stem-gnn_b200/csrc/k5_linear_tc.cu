@@ -8,8 +8,8 @@
 //
 //   out[m, n] = sum_s sum_k A_s[m, k] * W_s[n, k]  (+ bias[n])          fp32 in, fp32 out
 //
-// Accuracy: "3xTF32".  Every operand is split x = hi + lo with hi = tf32(x), lo = tf32(x - hi)
-// (round to nearest; x - hi is exact in fp32), and three kind::tf32 MMAs accumulate
+// Accuracy: "3xTF32".  Every operand is split x = hi + lo with hi = tf32(x) (round to nearest),
+// lo = x - hi (exact in fp32; the MMA reads its tf32 part), and three kind::tf32 MMAs accumulate
 // hi*hi + lo*hi + hi*lo in fp32 TMEM accumulators.  The dropped lo*lo term and the rounding of lo
 // are 2^-22 relative: the result sits within ~1e-6 of the fp32 product (tests hold 1e-5, the
 // north_star bound) with the full fp32 exponent range -- no scaling pass, no overflow cases.
@@ -86,10 +86,9 @@ __global__ void __launch_bounds__(256) lin_w_image_kernel(const WPrep p) {
         for (int t = 0; t < 4; ++t) {
             float v = 0.f;
             const int k = kbase + t;
-            if (n < p.n && k < p.k[s])
-                v = p.transposed ? __ldg(p.w[s] + (int64_t)k * p.ldw[s] + n) : __ldg(p.w[s] + (int64_t)n * p.ldw[s] + k);
-            hi[t] = __uint_as_float(f32_to_tf32(v));
-            lo[t] = __uint_as_float(f32_to_tf32(v - hi[t]));
+            if (n < p.n && k < (s ? p.k[1] : p.k[0]))
+                v = p.transposed ? __ldg((s ? p.w[1] : p.w[0]) + (int64_t)k * (s ? p.ldw[1] : p.ldw[0]) + n) : __ldg((s ? p.w[1] : p.w[0]) + (int64_t)n * (s ? p.ldw[1] : p.ldw[0]) + k);
+            tf32_split(v, hi[t], lo[t]);
         }
         uint8_t* st = reinterpret_cast<uint8_t*>(p.img) + ((int64_t)nt * p.kct + c) * W_STAGE_BYTES + sw64_off(r, j);
         *reinterpret_cast<float4*>(st) = make_float4(hi[0], hi[1], hi[2], hi[3]);
@@ -200,9 +199,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                 const uint32_t slot = seq % NS;
                 const int s = c < p.kc[0] ? 0 : 1;
                 const int kcol = (s == 0 ? c : c - p.kc[0]) * BK + 4 * j;
-                const bool col_ok = kcol < p.k[s];
-                const float* ap = p.a[s] + kcol;
-                const int64_t lda = p.lda[s];
+                const bool col_ok = kcol < (s ? p.k[1] : p.k[0]);
+                const float* ap = (s ? p.a[1] : p.a[0]) + kcol;
+                const int64_t lda = (s ? p.lda[1] : p.lda[0]);
                 float4 v[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -210,15 +209,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (col_ok && r < p.m) v[i] = __ldg(reinterpret_cast<const float4*>(ap + r * lda));
                 }
+                // pull this group's next chunk towards L2 while this one is converted
+                if (c + 2 < p.kct) {
+                    const int c2 = c + 2;
+                    const int s2 = c2 < p.kc[0] ? 0 : 1;
+                    const int kcol2 = (s2 == 0 ? c2 : c2 - p.kc[0]) * BK + 4 * j;
+                    if (kcol2 < (s2 ? p.k[1] : p.k[0])) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int64_t r = row0 + rr + 32 * i;
+                            if (r < p.m) prefetch_l2((s2 ? p.a[1] : p.a[0]) + kcol2 + r * (s2 ? p.lda[1] : p.lda[0]));
+                        }
+                    }
+                }
                 mbar_wait(smem_u32(empty + slot), ((seq / NS) & 1u) ^ 1u);
                 uint8_t* dst = stages + slot * STAGE_BYTES + soff;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     float4 hi, lo;
-                    hi.x = __uint_as_float(f32_to_tf32(v[i].x)); lo.x = __uint_as_float(f32_to_tf32(v[i].x - hi.x));
-                    hi.y = __uint_as_float(f32_to_tf32(v[i].y)); lo.y = __uint_as_float(f32_to_tf32(v[i].y - hi.y));
-                    hi.z = __uint_as_float(f32_to_tf32(v[i].z)); lo.z = __uint_as_float(f32_to_tf32(v[i].z - hi.z));
-                    hi.w = __uint_as_float(f32_to_tf32(v[i].w)); lo.w = __uint_as_float(f32_to_tf32(v[i].w - hi.w));
+                    tf32_split4(v[i], hi, lo);
                     *reinterpret_cast<float4*>(dst + i * 2048) = hi;
                     *reinterpret_cast<float4*>(dst + IMG_BYTES + i * 2048) = lo;
                 }

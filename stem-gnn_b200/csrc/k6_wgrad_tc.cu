@@ -31,8 +31,12 @@ constexpr int KM = 16;                    // rows per stage (two K=8 MMA steps)
 constexpr int IMG_BYTES = KM * BT * 4;    // 16 KB: one operand image of a stage
 constexpr int STAGE_BYTES = 4 * IMG_BYTES;    // G hi, G lo, A hi, A lo
 constexpr int NS = 3;
-constexpr int EPI_WARPS = 8, PROD_WARP0 = 8, MMA_WARP = 16;
-constexpr int NUM_THREADS = 544;          // warps 0-7 epilogue, 8-15 producers, 16 MMA
+constexpr int EPI_WARPS = 8, PROD_WARP0 = 8, MMA_WARP = 0;
+// warps 0-7 epilogue, 8-15 producers.  Lane 0 of warp 0 also issues the MMAs of an item before the
+// warp joins its epilogue: the accumulators are single-buffered, so the two never overlap, and 512
+// threads leave 128 registers per thread (544 spilled, and local-memory loads behind the streaming
+// global loads were the measured bottleneck).
+constexpr int NUM_THREADS = 512;
 constexpr int STAGING_WORDS = 32 * 33;
 constexpr int SMEM_BYTES = NS * STAGE_BYTES + EPI_WARPS * STAGING_WORDS * 4 + 16 * 8 + 16;
 constexpr int MAX_COMBOS = 64;
@@ -56,10 +60,7 @@ __device__ __forceinline__ uint32_t sw64_off(int c, int ku) {
 
 __device__ __forceinline__ void split_store(uint8_t* hi_p, uint8_t* lo_p, float x, float y, float z, float w) {
     float4 hi, lo;
-    hi.x = __uint_as_float(f32_to_tf32(x)); lo.x = __uint_as_float(f32_to_tf32(x - hi.x));
-    hi.y = __uint_as_float(f32_to_tf32(y)); lo.y = __uint_as_float(f32_to_tf32(y - hi.y));
-    hi.z = __uint_as_float(f32_to_tf32(z)); lo.z = __uint_as_float(f32_to_tf32(z - hi.z));
-    hi.w = __uint_as_float(f32_to_tf32(w)); lo.w = __uint_as_float(f32_to_tf32(w - hi.w));
+    tf32_split4(make_float4(x, y, z, w), hi, lo);
     *reinterpret_cast<float4*>(hi_p) = hi;
     *reinterpret_cast<float4*>(lo_p) = lo;
 }
@@ -113,43 +114,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == MMA_WARP) {
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_tf32(128, BT, 0, 0);
-            uint32_t seq = 0, item_it = 0;
-            for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++item_it) {
-                const int64_t slab = item / combos;
-                int64_t rows = p.m - slab * SLAB;
-                rows = rows > SLAB ? SLAB : rows;
-                const int n_st = (int)((rows + KM - 1) / KM);
-                mbar_wait(smem_u32(acc_empty), (item_it & 1u) ^ 1u);
-                tc_fence_after();
-                for (int c = 0; c < n_st; ++c, ++seq) {
-                    const uint32_t slot = seq % NS;
-                    mbar_wait(smem_u32(full + slot), (seq / NS) & 1u);
-                    tc_fence_after();
-                    const uint32_t base = smem_u32(stages + slot * STAGE_BYTES);
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-#pragma unroll
-                        for (int ks = 0; ks < 2; ++ks) {
-                            const uint32_t go = base + h * (IMG_BYTES / 2) + ks * 32;
-                            const uint64_t g_hi = smem_desc_sw64(go);
-                            const uint64_t g_lo = smem_desc_sw64(go + IMG_BYTES);
-                            const uint64_t a_hi = smem_desc_sw64(base + 2 * IMG_BYTES + ks * 32);
-                            const uint64_t a_lo = smem_desc_sw64(base + 3 * IMG_BYTES + ks * 32);
-                            const uint32_t d = tmem_base + (uint32_t)h * BT;
-                            umma_tf32(d, g_lo, a_hi, idesc, (c > 0 || ks > 0) ? 1u : 0u);
-                            umma_tf32(d, g_hi, a_lo, idesc, 1u);
-                            umma_tf32(d, g_hi, a_hi, idesc, 1u);
-                        }
-                    }
-                    umma_commit(smem_u32(empty + slot));
-                }
-                umma_commit(smem_u32(acc_full));
-            }
-        }
-    } else if (warp >= PROD_WARP0 && warp < MMA_WARP) {
+    if (warp >= PROD_WARP0) {
         // ================= producers: 16 nodes x (256 G features + 256 A features) per stage =====
         // Two groups of 128 threads take alternate stages.  Lane (mg, uo) of warp w owns the 4-node
         // group mg and the 16 B column units 16 w + uo and 16 w + uo + 8 of both operands: one load
@@ -179,9 +144,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
                 const int kc = kblk + 4 * (16 * wq + uo + 8 * b);
                 const int s = kc < p.k[0] ? 0 : 1;
                 const int cs = s == 0 ? kc : kc - p.k[0];
-                a_ok2[b] = cs < p.k[s];
-                acol[b] = a_ok2[b] ? p.a[s] + cs : nullptr;
-                lda2[b] = p.lda[s];
+                a_ok2[b] = cs < (s ? p.k[1] : p.k[0]);
+                acol[b] = a_ok2[b] ? (s ? p.a[1] : p.a[0]) + cs : nullptr;
+                lda2[b] = (s ? p.lda[1] : p.lda[0]);
             }
 #pragma unroll 1
             for (int c = grp; c < n_st; c += 2) {
@@ -203,6 +168,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
                         }
                     }
                 }
+                if (c + 2 < n_st) {      // pull this group's next stage towards L2
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) {
+                        const int col = 4 * (16 * wq + uo + 8 * b);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const int64_t r = m0 + (c + 2) * KM + 4 * mg + i;
+                            if (r < m0 + rows) {
+                                if (nblk + col < p.n) prefetch_l2(gbase + r * ldg + col);
+                                if (a_ok2[b]) prefetch_l2(acol[b] + r * lda2[b]);
+                            }
+                        }
+                    }
+                }
                 mbar_wait(smem_u32(empty + slot), ((seq / NS) & 1u) ^ 1u);
                 uint8_t* st = stages + slot * STAGE_BYTES;
 #pragma unroll
@@ -220,7 +199,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
         // ================= epilogue: partial[cta][combo] (+)= accumulator =================
         const int q = warp & 3, h = warp >> 2;
         float* st = s_stage + warp * STAGING_WORDS;
-        uint32_t item_it = 0;
+        const uint32_t idesc = make_idesc_tf32(128, BT, 0, 0);
+        uint32_t item_it = 0, mma_seq = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++item_it) {
             const bool first = item_it < (uint32_t)p.slots;
             float* tile = p.partial + ((int64_t)blockIdx.x * p.slots + item_it % (uint32_t)p.slots) * (BT * BT);
@@ -229,6 +209,41 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(tile + (int64_t)(row_base + lane) * BT + i * 32));
+            }
+            if (warp == MMA_WARP) {
+                if (lane == 0) {
+                    // ---- MMA issue for this item (the previous epilogue has drained TMEM)
+                    const int64_t slab = item / combos;
+                    int64_t rows = p.m - slab * SLAB;
+                    rows = rows > SLAB ? SLAB : rows;
+                    const int n_st = (int)((rows + KM - 1) / KM);
+                    mbar_wait(smem_u32(acc_empty), (item_it & 1u) ^ 1u);
+                    tc_fence_after();
+                    for (int c = 0; c < n_st; ++c, ++mma_seq) {
+                        const uint32_t slot = mma_seq % NS;
+                        mbar_wait(smem_u32(full + slot), (mma_seq / NS) & 1u);
+                        tc_fence_after();
+                        const uint32_t base = smem_u32(stages + slot * STAGE_BYTES);
+#pragma unroll
+                        for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+                            for (int ks = 0; ks < 2; ++ks) {
+                                const uint32_t go = base + hh * (IMG_BYTES / 2) + ks * 32;
+                                const uint64_t g_hi = smem_desc_sw64(go);
+                                const uint64_t g_lo = smem_desc_sw64(go + IMG_BYTES);
+                                const uint64_t a_hi = smem_desc_sw64(base + 2 * IMG_BYTES + ks * 32);
+                                const uint64_t a_lo = smem_desc_sw64(base + 3 * IMG_BYTES + ks * 32);
+                                const uint32_t d = tmem_base + (uint32_t)hh * BT;
+                                umma_tf32(d, g_lo, a_hi, idesc, (c > 0 || ks > 0) ? 1u : 0u);
+                                umma_tf32(d, g_hi, a_lo, idesc, 1u);
+                                umma_tf32(d, g_hi, a_hi, idesc, 1u);
+                            }
+                        }
+                        umma_commit(smem_u32(empty + slot));
+                    }
+                    umma_commit(smem_u32(acc_full));
+                }
+                __syncwarp();
             }
             mbar_wait(smem_u32(acc_full), item_it & 1u);
             tc_fence_after();
@@ -276,17 +291,18 @@ struct WgReduce {
 };
 
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgReduce p) {
+    // A block owns 32 float4 (128 consecutive elements of one tile); its 8 warps split the list of
+    // partial tiles (warp w takes every 8th), each summing in list order with several 512-byte loads
+    // in flight; the 8 warp sums are added in warp order.  Fixed order: deterministic.
+    __shared__ float4 sh[8][32];
     const int combos = p.nb * p.kbt;
-    const int64_t total = (int64_t)combos * (BT * BT / 4);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int combo = (int)(i / (BT * BT / 4));
-        const int e = (int)(i - (int64_t)combo * (BT * BT / 4)) * 4;
-        const int nbi = combo / p.kbt, kbi = combo - nbi * p.kbt;
-        const int row = nbi * BT + e / BT, kc = kbi * BT + (e % BT);
-        const int s = kc < p.k[0] ? 0 : 1;
-        const int col = s == 0 ? kc : kc - p.k[0];
-        if (row >= p.n || col >= p.k[s]) continue;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t blocks = (int64_t)combos * (BT * BT / 128);
+    for (int64_t blk = blockIdx.x; blk < blocks; blk += gridDim.x) {
+        const int combo = (int)(blk / (BT * BT / 128));
+        const int e = ((int)(blk - (int64_t)combo * (BT * BT / 128)) * 32 + lane) * 4;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int idx = 0;      // running index over this combo's partial tiles
         for (int sl = 0; sl < p.slots; ++sl) {
             const int64_t first_item = (int64_t)sl * p.grid;
             if (first_item >= p.n_items) break;
@@ -294,14 +310,33 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgReduce p) {
             const int c_end = (int)(p.n_items - first_item < p.grid ? p.n_items - first_item : p.grid);
             const float* src = p.partial + (int64_t)sl * (BT * BT) + e;
             const int64_t cstride = (int64_t)p.slots * (BT * BT);
-#pragma unroll 8
-            for (int c = (combo - base + combos) % combos; c < c_end; c += combos) {
-                const float4 v = __ldg(reinterpret_cast<const float4*>(src + c * cstride));
+            const int c_first = (combo - base + combos) % combos;
+            const int cnt = c_first < c_end ? (c_end - c_first + combos - 1) / combos : 0;
+            // tiles idx .. idx+cnt-1 of the list; warp w takes list positions == w (mod 8)
+            int t = ((w - idx) % 8 + 8) % 8;
+#pragma unroll 4
+            for (; t < cnt; t += 8) {
+                const float4 v = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(c_first + t * combos) * cstride));
                 acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
             }
+            idx += cnt;
         }
-        float* o = p.gw[s] + (int64_t)row * p.ldgw[s] + col;      // k % 4 == 0: the 4 columns are in range together
-        o[0] = acc.x; o[1] = acc.y; o[2] = acc.z; o[3] = acc.w;
+        sh[w][lane] = acc;
+        __syncthreads();
+        if (w == 0) {
+            float4 r = sh[0][lane];
+#pragma unroll
+            for (int i = 1; i < 8; ++i) { const float4 v = sh[i][lane]; r.x += v.x; r.y += v.y; r.z += v.z; r.w += v.w; }
+            const int nbi = combo / p.kbt, kbi = combo - nbi * p.kbt;
+            const int row = nbi * BT + e / BT, kc = kbi * BT + (e % BT);
+            const int s = kc < p.k[0] ? 0 : 1;
+            const int col = s == 0 ? kc : kc - p.k[0];
+            if (row < p.n && col < (s ? p.k[1] : p.k[0])) {      // k % 4 == 0: the 4 columns are in range together
+                float* o = (s ? p.gw[1] : p.gw[0]) + (int64_t)row * (s ? p.ldgw[1] : p.ldgw[0]) + col;
+                o[0] = r.x; o[1] = r.y; o[2] = r.z; o[3] = r.w;
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -309,17 +344,37 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const WgReduce p) {
 // sum of the block partials
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ g, int64_t ldg, int64_t m, int n,
                                                              int64_t rows_per_block, float* __restrict__ part) {
+    // thread (cu, rl): 16 B column unit cu + 64 t, rows r0 + rl, r0 + rl + 4, ...; the four row lanes of a
+    // unit are summed through shared memory in a fixed order
+    __shared__ float4 sh[4][64];
+    const int cu = threadIdx.x & 63, rl = threadIdx.x >> 6;
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     const int64_t r1 = r0 + rows_per_block < m ? r0 + rows_per_block : m;
-    for (int c = threadIdx.x; c < n; c += blockDim.x) {
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        int64_t r = r0;
-        for (; r + 4 <= r1; r += 4) {
-            s0 += __ldg(g + r * ldg + c); s1 += __ldg(g + (r + 1) * ldg + c);
-            s2 += __ldg(g + (r + 2) * ldg + c); s3 += __ldg(g + (r + 3) * ldg + c);
+    for (int c0 = 0; c0 < n; c0 += 256) {
+        const int c = c0 + 4 * cu;
+        float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+        if (c < n) {
+            int64_t r = r0 + rl;
+            for (; r + 4 < r1; r += 8) {
+                const float4 a = __ldg(reinterpret_cast<const float4*>(g + r * ldg + c));
+                const float4 b = __ldg(reinterpret_cast<const float4*>(g + (r + 4) * ldg + c));
+                s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
+                s1.x += b.x; s1.y += b.y; s1.z += b.z; s1.w += b.w;
+            }
+            if (r < r1) {
+                const float4 a = __ldg(reinterpret_cast<const float4*>(g + r * ldg + c));
+                s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
+            }
         }
-        for (; r < r1; ++r) s0 += __ldg(g + r * ldg + c);
-        part[(int64_t)blockIdx.x * n + c] = (s0 + s1) + (s2 + s3);
+        sh[rl][cu] = make_float4(s0.x + s1.x, s0.y + s1.y, s0.z + s1.z, s0.w + s1.w);
+        __syncthreads();
+        if (rl == 0 && c < n) {
+            const float4 a = sh[0][cu], b = sh[1][cu], d = sh[2][cu], e = sh[3][cu];
+            float* o = part + (int64_t)blockIdx.x * n + c;
+            o[0] = (a.x + b.x) + (d.x + e.x); o[1] = (a.y + b.y) + (d.y + e.y);
+            o[2] = (a.z + b.z) + (d.z + e.z); o[3] = (a.w + b.w) + (d.w + e.w);
+        }
+        __syncthreads();
     }
 }
 __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ part, int blocks, int n,
@@ -428,8 +483,8 @@ extern "C" int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* a, void* wo
         const bool on = s < a->n_src;
         r.k[s] = on ? (int)a->k[s] : 0; r.gw[s] = on ? a->gw[s] : nullptr; r.ldgw[s] = on ? a->ldgw[s] : 0;
     }
-    const int64_t units = (int64_t)pl.combos * (wgrad::BT * wgrad::BT / 4);
-    SG_LAUNCH(wgrad::wgrad_reduce_kernel<<<(unsigned)((units + 255) / 256), 256, 0, stream>>>(r));
+    const int64_t rblocks = (int64_t)pl.combos * (wgrad::BT * wgrad::BT / 128);
+    SG_LAUNCH(wgrad::wgrad_reduce_kernel<<<(unsigned)rblocks, 256, 0, stream>>>(r));
     SG_CHECK_LAUNCH();
 
     if (a->gbias) {

@@ -147,5 +147,21 @@ __device__ __forceinline__ uint32_t f32_to_tf32(float x) {   // round to nearest
     return r;
 }
 
+// 3xTF32 operand split without the (multi-instruction) cvt.rna.tf32: hi = x rounded to 10 mantissa
+// bits (add half an ulp to the bit pattern, clear the low 13 bits: round-to-nearest, ties away --
+// exactly a tf32 value), lo = x - hi (exact in fp32, symmetric around 0).  lo is stored raw: the
+// tensor core reads the tf32 part of a 32-bit container, which bounds the dropped tail by 2^-21 |x|.
+__device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
+    hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+    lo = x - hi;
+}
+__device__ __forceinline__ void tf32_split4(const float4 v, float4& hi, float4& lo) {
+    tf32_split(v.x, hi.x, lo.x); tf32_split(v.y, hi.y, lo.y);
+    tf32_split(v.z, hi.z, lo.z); tf32_split(v.w, hi.w, lo.w);
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 }  // namespace tcptx
 }  // namespace stemgnn
