@@ -119,7 +119,7 @@ def build_models(w, device, S):
                     dropout=0.15).to(device).train()
     vq = S.VectorQuantize(dim=w["hid"], codebook_size=w["codes"], decay=0.8,
                           commitment_weight=1.0).to(device).train()
-    opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
+    opt = torch.optim.AdamW(enc.parameters(), lr=1e-4, capturable=True)   # graph-capturable: same math
     return enc, vq, opt
 
 
@@ -172,13 +172,21 @@ def summarize_trace(trace, steps, pk, n_feat_bytes_l2):
     return out
 
 
-def roofline_of(kern, name, pk, x_fits_l2):
+def roofline_of(kern, name, pk, x_fits_l2=None):
     k = kern[name]
     if name == "vq_assign" and k.get("tflops") is not None:
         # K >= ~508 with fp32 inputs sits right of the ridge: tensor-bound
         return dict(kernel=name, bound="tensor", achieved=k["tflops"], peak=pk["tc_sus"] or pk["tc"],
                     unit="TFLOP/s", frac=k["tflops"] / (pk["tc_sus"] or pk["tc"]), traffic=None,
                     peak_source=pk["src"] + " (sustained: kernel timed inside a long step)")
+    if name in ("linear", "linear_wgrad") and k.get("tflops") is not None:
+        # fp32-accurate GEMM as 3xTF32: the tensor pipe executes 3x the algorithmic 2MNK flops at
+        # the tf32 rate (half the measured dense bf16 rate), so frac tops out at 1/3
+        peak = (pk["tc_sus"] or pk["tc"]) / 2
+        return dict(kernel=name, bound="tensor", achieved=k["tflops"], peak=peak, unit="TFLOP/s",
+                    frac=k["tflops"] / peak, executed_tflops=3 * k["tflops"], traffic=None,
+                    peak_source=pk["src"] + " bf16 dense / 2 = tf32 rate (sustained)",
+                    flops_model="algorithmic 2*M*N*K per call; 3 tf32 MMAs per product are executed")
     a = k["gbps_alg"]
     return dict(kernel=name, bound="hbm", achieved=a, peak=pk["hbm"], unit="GB/s", frac=a / pk["hbm"],
                 traffic=None, peak_source=pk["src"], alg_bytes_per_launch=k["alg_bytes_per_call"],
@@ -288,50 +296,106 @@ def run_ours(args, w):
             dist.barrier()
             torch.cuda.synchronize()
 
-    # ---------------- resident-input timing (value)
+    # ---------------- one CUDA graph of the whole step (forward, backward, optimizer)
+    # ~170 kernels of 5-200 us each: launched one by one the step is bound by the host's launch
+    # rate.  The step reads static input buffers (x_in, ei_in) and writes loss_out; replaying the
+    # graph does exactly the work of the eager step (CSR rebuild included).
+    x_in, ei_in = x_d.clone(), ei_d.clone()
     for _ in range(max(args.warmup, 3)):
-        step(x_d, ei_d)
+        step(x_in, ei_in)
     sync_all()
+    graph, loss_out, graph_err = None, None, None
+    if not args.no_graph and world == 1:
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                loss_out = step(x_in, ei_in)
+            graph = g
+        except Exception as e:                                     # fall back to eager launches
+            graph_err = f"{type(e).__name__}: {e}".splitlines()[0][:200]
+            torch.cuda.synchronize()
+
+    def run_step():
+        if graph is not None:
+            graph.replay()
+            return loss_out
+        return step(x_in, ei_in)
+
+    for _ in range(3):
+        run_step()
+    sync_all()
+
+    # ---------------- resident-input timing (value)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    _lib.TRACE = []
-    l0 = _lib.launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(args.steps)]
     for a, b in ev:
         flush.fill_(1)                      # L2 flush between timed steps (256 MB > 126 MB L2)
         a.record()
-        step(x_d, ei_d)
+        run_step()
         b.record()
     sync_all()
-    launches = (_lib.launch_count() - l0) / args.steps
-    trace, _lib.TRACE = _lib.TRACE, None
     ms = sum(a.elapsed_time(b) for a, b in ev)
 
     # ---------------- end-to-end timing (host buffers in, loss out)
-    x_s, ei_s = torch.empty_like(x_d), torch.empty_like(ei_d)
+    # Inputs come from pinned host memory every step.  Double-buffered: the copy of step i+1 runs
+    # on a side stream while step i computes; step i waits for its own copy only.
     loss_h = torch.empty(1, dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream()
+    stage = [(torch.empty_like(x_d), torch.empty_like(ei_d)) for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
 
-    def e2e_step():
-        x_s.copy_(x_h, non_blocking=True)
-        ei_s.copy_(ei_h, non_blocking=True)
-        loss = step(x_s, ei_s)
+    def issue_copy(i):
+        b = i & 1
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[b])
+            stage[b][0].copy_(x_h, non_blocking=True)
+            stage[b][1].copy_(ei_h, non_blocking=True)
+            ready[b].record(copy_stream)
+
+    def e2e_step(i, last):
+        b = i & 1
+        cur = torch.cuda.current_stream()
+        cur.wait_event(ready[b])
+        x_in.copy_(stage[b][0], non_blocking=True)        # device-to-device into the graph's inputs
+        ei_in.copy_(stage[b][1], non_blocking=True)
+        consumed[b].record(cur)
+        if not last:
+            issue_copy(i + 1)
+        loss = run_step()
         loss_h.copy_(loss.detach().reshape(1), non_blocking=True)
 
-    for _ in range(2):
-        e2e_step()
+    for b in range(2):
+        consumed[b].record(torch.cuda.current_stream())
+    issue_copy(0)
+    e2e_step(0, False); e2e_step(1, True)
     sync_all()
-    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-           for _ in range(args.steps)]
-    for a, b in ev2:
+    ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    for i in range(args.steps):
         flush.fill_(1)
-        a.record()
-        e2e_step()
-        b.record()
+        if i == 0:
+            ev2[0].record()
+            issue_copy(0)                   # the first step's copy is inside the timed region, exposed
+        e2e_step(i, i == args.steps - 1)
+        ev2[i + 1].record()
     sync_all()
-    ms_e2e = sum(a.elapsed_time(b) for a, b in ev2)
+    # the L2 flushes sit inside this region (they overlap the prefetch copies); per-step times come
+    # from consecutive events
+    ms_e2e = ev2[0].elapsed_time(ev2[-1])
     clocks = sampler.stop() if rank == 0 else None
+
+    # ---------------- per-kernel device times (eager, traced): roofline of each kernel family
+    _lib.TRACE = []
+    l0 = _lib.launch_count()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        step(x_in, ei_in)
+    sync_all()
+    launches = (_lib.launch_count() - l0) / args.steps
+    trace, _lib.TRACE = _lib.TRACE, None
 
     t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
     if world > 1:
@@ -344,28 +408,37 @@ def run_ours(args, w):
     units = w["layers"] * w["e"] * world
     value = units * args.steps / (ms / 1e3)
     e2e_v = units * args.steps / (ms_e2e / 1e3)
-    x_fits_l2 = w["n"] * max(w["f"], w["hid"]) * 4 <= 126e6
-    kern = summarize_trace(trace, args.steps, pk, x_fits_l2)
-    mine = {k: v for k, v in kern.items()}
-    top = max(mine, key=lambda k: mine[k]["ms_per_step"])
-    roof = roofline_of(kern, top, pk, x_fits_l2)
+    kern = summarize_trace(trace, args.steps, pk, None)
+    top = max(kern, key=lambda k: kern[k]["ms_per_step"])
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(traffic_file):
-        tr = json.load(open(traffic_file)).get(args.workload, {}).get(top)
-        if tr:
-            roof["traffic"] = tr["bytes_per_launch"]
-            roof["traffic_source"] = tr["source"]
+    traffic = json.load(open(traffic_file)).get(args.workload, {}) if os.path.exists(traffic_file) else {}
+    rooflines = {}
+    for name in kern:
+        if "gbps_alg" not in kern[name]:
+            continue
+        r = roofline_of(kern, name, pk)
+        if name in traffic:
+            r["traffic"] = traffic[name]["bytes_per_launch"]
+            r["traffic_source"] = traffic[name]["source"]
+        rooflines[name] = r
+    roof = rooflines[top]
     line = dict(metric=METRIC, value=value, unit="edges/s", n_gpus=world, steps=args.steps,
                 warmup=max(args.warmup, 3), ms_per_step=ms / args.steps, higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                 vq_nodes_per_s=w["n"] * world * args.steps / (ms / 1e3),
                 config=dict(workload=w["desc"], layers=w["layers"], nodes=w["n"], edges=w["e"],
                             l2="flushed between timed steps (256 MB write)",
+                            cuda_graph=graph is not None, cuda_graph_error=graph_err,
+                            e2e_pipeline="pinned host -> device copy of step i+1 on a side stream during "
+                                         "step i (double-buffered); every step's copy and loss read-back "
+                                         "are inside the timed region",
+                            kernel_times="CUDA events around every C-ABI call in an eager pass of the same "
+                                         "step right after the timed region",
                             parallelism=f"replicas x{world}: EMA statistics + dense grads all-reduced"
                             if world > 1 else "single GPU"),
                 e2e=dict(value=e2e_v, unit="edges/s", ms_per_step=ms_e2e / args.steps,
                          h2d_bytes_per_step=x_h.numel() * 4 + ei_h.numel() * 8, d2h_bytes_per_step=4),
-                gpu_launches=launches, roofline=roof, kernels=kern, clocks=clocks)
+                gpu_launches=launches, roofline=roof, rooflines=rooflines, kernels=kern, clocks=clocks)
     if world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         ws, sample = cpu_sample(w, args.cpu_frac)
@@ -513,6 +586,7 @@ def main():
     ap.add_argument("--cpu-frac", type=float, default=1.0,
                     help="fraction of the graph the CPU arm runs per step (bounded sample)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--partition", action="store_true",
                     help="1-D destination partition across the ranks (strong scaling, static graph)")
     args = ap.parse_args()

@@ -45,6 +45,7 @@ class _Codebook(nn.Module):
             if self.cosine:
                 embed = _l2norm(embed)
         self.register_buffer("initted", torch.Tensor([not kmeans_init]))
+        self._initted_host = None
         self.register_buffer("cluster_size", torch.zeros(num_codebooks, codebook_size))
         self.register_buffer("embed_avg", embed.clone())
         if learnable_codebook:
@@ -67,7 +68,12 @@ class _Codebook(nn.Module):
     def init_embed_(self, x, heads):
         """k-means initialisation (model/vq.py:182-222,320-342) on the first batch, with the
         assignment and the per-cluster sums done by K3 / K4."""
-        if bool(self.initted.item()):
+        # `initted` is a device buffer (it travels in the state_dict like the reference's); reading it
+        # every forward would stall the launch queue, so its value is cached on the host and re-read
+        # only after a state_dict load
+        if self._initted_host is None:
+            self._initted_host = bool(self.initted.item())
+        if self._initted_host:
             return
         Hc, K, D = self.embed.shape
         rows = x.view(x.size(0), heads, D).permute(1, 0, 2) if Hc == heads else x.reshape(1, -1, D)
@@ -92,6 +98,11 @@ class _Codebook(nn.Module):
         self.embed_avg.data.copy_(means * counts.unsqueeze(-1))
         self.cluster_size.data.copy_(counts)
         self.initted.data.fill_(1.0)
+        self._initted_host = True
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self._initted_host = None
+        return super()._load_from_state_dict(*args, **kwargs)
 
     def forward(self, x, heads, training, freeze_codebook, commit_to_embed):
         """x [M, heads*D] fp32 (already l2-normalised for cosine).  Returns (quantize with the
