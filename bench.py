@@ -305,7 +305,7 @@ def run_ours(args, w):
         step(x_in, ei_in)
     sync_all()
     graph, loss_out, graph_err = None, None, None
-    if not args.no_graph and world == 1:
+    if not args.no_graph and world == 1:     # (capturing the NCCL all-reduces of N > 1 ranks hung: not attempted)
         try:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
