@@ -196,6 +196,32 @@ int stemgnn_linear_wgrad_workspace(const stemgnn_linear_wgrad_args* args_host, s
 int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* args_host, void* workspace,
                          size_t workspace_bytes, stemgnn_stream_t stream);
 
+/* ------------------------------------------------------------------ K7: BatchNorm + ReLU + dropout
+ * Replaces `z = self.norms[i](z)` and `z = self.dropout(self.activation(z))` (reference
+ * STEM-GNN/model/encoder.py:313-317) and their autograd with three passes over [rows, feat] fp32
+ * (feat % 4 == 0, 16-byte aligned rows):
+ *   stemgnn_bn_stats        mean[c], biased var[c] of column c (what nn.BatchNorm1d uses in training);
+ *                           running-statistics updates and invstd = rsqrt(var + eps) are the caller's
+ *                           ([feat]-sized torch ops in the drop-in module)
+ *   stemgnn_bn_act_forward  out = dropout(relu((x - mean) * invstd * gamma + beta), p)
+ *   stemgnn_bn_act_backward sum_g[c] = sum_r g, sum_gx[c] = sum_r g * xhat (= grad of beta, gamma) with
+ *                           g = g_y * mask/(1-p) * [pre > 0];  gx = gamma * invstd * (g - sum_g/N -
+ *                           xhat * sum_gx/N) when batch_stats, gamma * invstd * g otherwise
+ * The dropout mask is Philox4x32-10 keyed by *seed (a uint64 in DEVICE memory, read at kernel time,
+ * so a captured CUDA graph sees a fresh seed on every replay) and the element index: it is recomputed
+ * in the backward, never stored.  relu / p = 0 switch the activation / dropout off. */
+int stemgnn_bn_workspace(int64_t rows, int64_t feat, size_t* bytes_host);
+int stemgnn_bn_stats(int64_t rows, int64_t feat, const float* x, int64_t ldx, float* mean, float* var,
+                     void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+int stemgnn_bn_act_forward(int64_t rows, int64_t feat, const float* x, int64_t ldx, const float* mean,
+                           const float* invstd, const float* gamma, const float* beta, int relu, float p,
+                           const uint64_t* seed, float* out, int64_t ldo, stemgnn_stream_t stream);
+int stemgnn_bn_act_backward(int64_t rows, int64_t feat, const float* x, int64_t ldx, const float* gy,
+                            int64_t ldg, const float* mean, const float* invstd, const float* gamma,
+                            const float* beta, int relu, float p, const uint64_t* seed, int batch_stats,
+                            float* sum_g, float* sum_gx, float* gx, int64_t ldgx, void* workspace,
+                            size_t workspace_bytes, stemgnn_stream_t stream);
+
 /* ------------------------------------------------------------------ K4: EMA statistics
  * Replaces onehot.sum(1) and einsum('h n d, h n c -> h c d') (model/vq.py:492,497 / 665,670):
  * counts [embed_heads,K] fp32 and sums [embed_heads,K,D] fp32.  Deterministic: rows are

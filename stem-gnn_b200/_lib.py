@@ -62,6 +62,11 @@ SIGNATURES = {
     "stemgnn_linear": (_i32, [C.POINTER(LinearArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_linear_wgrad_workspace": (_i32, [C.POINTER(LinearWgradArgs), C.POINTER(C.c_size_t)]),
     "stemgnn_linear_wgrad": (_i32, [C.POINTER(LinearWgradArgs), _vp, C.c_size_t, _vp]),
+    "stemgnn_bn_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
+    "stemgnn_bn_stats": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "stemgnn_bn_act_forward": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp, _vp, _i64, _vp]),
+    "stemgnn_bn_act_backward": (_i32, [_i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp, _i32,
+                                       _vp, _vp, _vp, _i64, _vp, C.c_size_t, _vp]),
     "stemgnn_vq_assign_workspace": (_i32, [C.POINTER(VqAssignArgs), C.POINTER(C.c_size_t)]),
     "stemgnn_vq_assign": (_i32, [C.POINTER(VqAssignArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_vq_backward": (_i32, [_vp, _vp, _vp, _vp, _f32, _i64, _vp, _vp]),

@@ -9,6 +9,7 @@ import torch.nn.functional as F
 from torch import Tensor
 
 from .conv import GCNConv, GINConv, MixtureSageLayer, MySAGEConv
+from . import norm_act
 from .graph import structure_of
 
 
@@ -136,10 +137,17 @@ class Encoder(nn.Module):
                 slot += 1
             else:
                 z = layer(z, graph, edge_attr)
-            if self.normalize != "none":
-                z = self.norms[i](z)
-            if i < self.num_layers - 1:
-                z = self.dropout(self.activation(z))
+            act_here = i < self.num_layers - 1
+            if (self.normalize != "none" and self.dropout.p < 1.0
+                    and norm_act.supported(z, self.norms[i], self.activation if act_here else None)):
+                # BatchNorm (+ ReLU + dropout) in three passes over z (K7) on the same norms[i] module
+                z = norm_act.bn_act_drop(z, self.norms[i], relu=act_here,
+                                         p=self.dropout.p if act_here else 0.0, training=self.dropout.training)
+            else:
+                if self.normalize != "none":
+                    z = self.norms[i](z)
+                if act_here:
+                    z = self.dropout(self.activation(z))
         self._last_env_reg = reg_sum / reg_n if (reg_sum is not None and reg_n > 0) else z.new_zeros(1)
         return z
 

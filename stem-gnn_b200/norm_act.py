@@ -1,0 +1,128 @@
+"""BatchNorm1d + ReLU + dropout of the encoder layers as one fused op (K7).
+
+`bn_act_drop(z, bn, relu, p, training)` computes what the reference's encode loop does with three
+torch modules -- `z = self.norms[i](z); z = self.dropout(self.activation(z))`
+(STEM-GNN/model/encoder.py:313-317) -- on the SAME `nn.BatchNorm1d` module (its parameters, running
+statistics and `num_batches_tracked` are read and updated exactly like `F.batch_norm` does), so
+`state_dict` keys and eval behaviour are unchanged.  Dropout uses the library's own counter-based
+Philox stream (not torch's generator): same distribution, different masks.  No CPU path.
+"""
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+_seeds = {}          # device index -> uint64-as-int64 device tensor: the dropout stream position
+_GOLDEN = 0x9E3779B97F4A7C15 - (1 << 64)      # odd increment of the seed (as a signed int64)
+
+
+def _seed_tensor(device):
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    t = _seeds.get(key)
+    if t is None:
+        t = torch.tensor([torch.initial_seed() & 0x7FFFFFFFFFFFFFFF], dtype=torch.int64, device=device)
+        _seeds[key] = t
+    return t
+
+
+def manual_seed(seed: int, device=None):
+    """Re-seed the dropout stream of `device` (default: current)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    _seed_tensor(device).fill_(int(seed) & 0x7FFFFFFFFFFFFFFF)
+
+
+def supported(z, bn, activation) -> bool:
+    return (z.is_cuda and z.dim() == 2 and z.dtype == torch.float32 and z.size(1) % 4 == 0 and z.size(0) > 0
+            and isinstance(bn, nn.BatchNorm1d) and (activation is None or isinstance(activation, nn.ReLU)))
+
+
+def _ws(rows, feat, device):
+    need = C.c_size_t(0)
+    _lib.check(_lib.lib().stemgnn_bn_workspace(rows, feat, C.byref(need)))
+    return _lib.workspace(need.value, device)
+
+
+def _rows16(t):
+    if t.stride(1) != 1 or t.stride(0) % 4 or t.data_ptr() % 16 or t.stride(0) < t.size(1):
+        t = t.contiguous()
+    return t
+
+
+def batch_stats(x):
+    """(mean [F], biased variance [F]) of the columns of x (K7 statistics pass)."""
+    x = _rows16(x)
+    n, f = x.shape
+    mean = torch.empty(f, dtype=torch.float32, device=x.device)
+    var = torch.empty_like(mean)
+    ws = _ws(n, f, x.device)
+    with _lib.traced("bn_stats", n * f * 4, 0, 2):
+        _lib.check(_lib.lib().stemgnn_bn_stats(n, f, x.data_ptr(), x.stride(0), mean.data_ptr(), var.data_ptr(),
+                                               ws.data_ptr(), ws.numel(), _lib.stream()))
+    return mean, var
+
+
+class _BnActDrop(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, mean, invstd, use_batch_stats, relu, p, seed):
+        x = _rows16(x)
+        n, f = x.shape
+        out = torch.empty((n, f), dtype=torch.float32, device=x.device)
+        with _lib.traced("bn_act_forward", 2 * n * f * 4, 0, 1):
+            _lib.check(_lib.lib().stemgnn_bn_act_forward(
+                n, f, x.data_ptr(), x.stride(0), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                beta.data_ptr(), int(relu), float(p), _lib.ptr(seed), out.data_ptr(), out.stride(0), _lib.stream()))
+        ctx.save_for_backward(x, gamma, beta, mean, invstd, seed)
+        ctx.cfg = (bool(use_batch_stats), bool(relu), float(p))
+        return out
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, gamma, beta, mean, invstd, seed = ctx.saved_tensors
+        use_batch_stats, relu, p = ctx.cfg
+        gy = _rows16(gy)
+        n, f = x.shape
+        sum_g = torch.empty(f, dtype=torch.float32, device=x.device)
+        sum_gx = torch.empty_like(sum_g)
+        gx = torch.empty((n, f), dtype=torch.float32, device=x.device) if ctx.needs_input_grad[0] else None
+        ws = _ws(n, f, x.device)
+        with _lib.traced("bn_act_backward", (5 if gx is not None else 2) * n * f * 4, 0, 3):
+            _lib.check(_lib.lib().stemgnn_bn_act_backward(
+                n, f, x.data_ptr(), x.stride(0), gy.data_ptr(), gy.stride(0), mean.data_ptr(), invstd.data_ptr(),
+                gamma.data_ptr(), beta.data_ptr(), int(relu), p, _lib.ptr(seed), int(use_batch_stats),
+                sum_g.data_ptr(), sum_gx.data_ptr(), _lib.ptr(gx), gx.stride(0) if gx is not None else 0,
+                ws.data_ptr(), ws.numel(), _lib.stream()))
+        return (gx, sum_gx if ctx.needs_input_grad[1] else None, sum_g if ctx.needs_input_grad[2] else None,
+                None, None, None, None, None, None)
+
+
+def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool):
+    """dropout(relu(bn(z))) with bn's own parameters / buffers; `relu=False`, `p=0` give plain BatchNorm."""
+    use_batch = bn.training or bn.running_mean is None
+    f = z.size(1)
+    if use_batch:
+        with torch.no_grad():
+            mean, var = batch_stats(z.detach())
+            if bn.training and bn.track_running_stats and bn.running_mean is not None:
+                bn.num_batches_tracked.add_(1)
+                if bn.momentum is None:
+                    m = 1.0 / bn.num_batches_tracked.to(torch.float32)        # cumulative moving average
+                else:
+                    m = bn.momentum
+                n = z.size(0)
+                bn.running_mean.mul_(1 - m).add_(mean * m)
+                bn.running_var.mul_(1 - m).add_(var * (n / max(n - 1, 1)) * m)
+    else:
+        mean, var = bn.running_mean, bn.running_var
+    with torch.no_grad():
+        invstd = torch.rsqrt(var + bn.eps)
+    gamma = bn.weight if bn.weight is not None else torch.ones(f, device=z.device)
+    beta = bn.bias if bn.bias is not None else torch.zeros(f, device=z.device)
+    p_eff = float(p) if training else 0.0
+    seed = None
+    if p_eff > 0.0:
+        st = _seed_tensor(z.device)
+        seed = st.clone()                 # this call's key, kept for the backward
+        st.add_(_GOLDEN)                  # device-side advance: a replayed CUDA graph draws new masks
+    return _BnActDrop.apply(z, gamma, beta, mean, invstd, use_batch, relu, p_eff, seed)

@@ -1,0 +1,108 @@
+"""K7 (fused BatchNorm1d + ReLU + dropout) against torch's own modules on the same nn.BatchNorm1d."""
+import copy
+
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+import stemgnn_b200 as S
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close(a, b, tol=1e-5):
+    scale = b.abs().max().clamp_min(1e-30)
+    assert ((a - b).abs().max() / scale).item() < tol, ((a - b).abs().max() / scale).item()
+
+
+@pytest.mark.parametrize("n,f", [(1000, 256), (777, 36), (5, 4), (40000, 128), (3000, 520)])
+@pytest.mark.parametrize("relu", [True, False])
+def test_training_forward_backward_and_running_stats_match_torch(n, f, relu):
+    g = torch.Generator().manual_seed(n + f)
+    x = (torch.randn(n, f, generator=g) * 3 + 5).to(DEV)       # mean far from 0: the shifted sums matter
+    go = torch.randn(n, f, generator=g).to(DEV)
+    bn_a = nn.BatchNorm1d(f).to(DEV).train()
+    with torch.no_grad():
+        bn_a.weight.copy_(torch.rand(f, generator=g) + 0.5); bn_a.bias.copy_(torch.randn(f, generator=g))
+    bn_b = copy.deepcopy(bn_a)
+    xa = x.clone().requires_grad_(True); xb = x.clone().requires_grad_(True)
+    ya = S.bn_act_drop(xa, bn_a, relu=relu, p=0.0, training=True)
+    yb = bn_b(xb)
+    yb = F.relu(yb) if relu else yb
+    ya.backward(go); yb.backward(go)
+    _close(ya.detach(), yb.detach())
+    _close(xa.grad, xb.grad)
+    _close(bn_a.weight.grad, bn_b.weight.grad); _close(bn_a.bias.grad, bn_b.bias.grad)
+    _close(bn_a.running_mean, bn_b.running_mean); _close(bn_a.running_var, bn_b.running_var)
+    assert int(bn_a.num_batches_tracked) == int(bn_b.num_batches_tracked) == 1
+
+
+def test_eval_mode_uses_running_statistics():
+    g = torch.Generator().manual_seed(1)
+    n, f = 500, 64
+    x = torch.randn(n, f, generator=g).to(DEV)
+    bn = nn.BatchNorm1d(f).to(DEV)
+    with torch.no_grad():
+        bn.running_mean.copy_(torch.randn(f, generator=g)); bn.running_var.copy_(torch.rand(f, generator=g) + 0.3)
+    bn.eval()
+    xa = x.clone().requires_grad_(True); xb = x.clone().requires_grad_(True)
+    ya = S.bn_act_drop(xa, bn, relu=True, p=0.5, training=False)     # dropout is off in eval
+    yb = F.relu(bn(xb))
+    _close(ya.detach(), yb.detach())
+    ya.sum().backward(); yb.sum().backward()
+    _close(xa.grad, xb.grad)
+    assert int(bn.num_batches_tracked) == 0
+
+
+def test_dropout_mask_statistics_and_backward_consistency():
+    n, f, p = 4096, 256, 0.15
+    x = torch.randn(n, f, device=DEV)
+    bn = nn.BatchNorm1d(f).to(DEV).train()
+    S.norm_act.manual_seed(1234)
+    xa = x.clone().requires_grad_(True)
+    y = S.bn_act_drop(xa, bn, relu=False, p=p, training=True)
+    ref = F.batch_norm(x, None, None, bn.weight, bn.bias, True, 0.0, bn.eps)
+    kept = y != 0
+    frac = kept.float().mean().item()
+    assert abs(frac - (1 - p)) < 0.005, frac
+    _close(y[kept], ref[kept] / (1 - p))                      # kept entries are scaled by 1/(1-p)
+    # rows and columns are hit evenly
+    assert (kept.float().mean(0) - (1 - p)).abs().max().item() < 0.03
+    assert (kept.float().mean(1) - (1 - p)).abs().max().item() < 0.12
+    # the backward recomputes the SAME mask: d sum(y) / dx is zero through the dropped entries
+    go = torch.randn(n, f, device=DEV)
+    y.backward(go)
+    xb = x.clone().requires_grad_(True)
+    yb = F.batch_norm(xb, None, None, bn.weight, bn.bias, True, 0.0, bn.eps)
+    yb.backward(go * kept / (1 - p))
+    _close(xa.grad, xb.grad)
+    # a second call draws a different mask; re-seeding reproduces the first
+    y2 = S.bn_act_drop(x, bn, relu=False, p=p, training=True)
+    assert not torch.equal(y2 != 0, kept)
+    S.norm_act.manual_seed(1234)
+    y3 = S.bn_act_drop(x, bn, relu=False, p=p, training=True)
+    assert torch.equal(y3 != 0, kept)
+
+
+def test_encoder_uses_fused_norm_and_matches_unfused_modules():
+    g = torch.Generator().manual_seed(8)
+    n, e, fin, hid = 2000, 12000, 64, 128
+    ei = torch.randint(0, n, (2, e), generator=g).to(DEV)
+    x = torch.randn(n, fin, generator=g).to(DEV)
+    torch.manual_seed(0)
+    enc = S.Encoder(fin, hid, nn.ReLU, 2, backbone="sage", normalize="batch", dropout=0.0).to(DEV).train()
+    ref = copy.deepcopy(enc)
+    S._lib.TRACE = []
+    try:
+        z = enc(x, ei)
+        names = [r[0] for r in S._lib.TRACE]
+    finally:
+        S._lib.TRACE = None
+    assert names.count("bn_act_forward") == 2
+    # unfused: the same layers, torch BatchNorm / ReLU
+    with torch.no_grad():
+        h = ref.layers[0](x, ei); h = F.relu(ref.norms[0](h)); h = ref.norms[1](ref.layers[1](h, ei))
+    _close(z.detach(), h, 2e-5)
+    _close(enc.norms[0].running_var, ref.norms[0].running_var)
