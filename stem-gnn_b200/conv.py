@@ -119,7 +119,11 @@ class GCNConv(nn.Module):
             raise NotImplementedError("GCNConv on a partitioned graph (symmetric normalisation needs "
                                       "the degrees of remote sources) is not built yet")
         g_sl, w = g.gcn()
-        out = aggregate(self.lin(x), g_sl, reduce="sum", edge_weight=w)
+        if x.is_cuda and dense.supported(self.in_channels, self.out_channels):
+            h = dense.linear_sum([x], [self.lin.weight], None)        # K5/K6 (tcgen05, fp32 accuracy)
+        else:
+            h = self.lin(x)
+        out = aggregate(h, g_sl, reduce="sum", edge_weight=w)
         return out + self.bias if self.bias is not None else out
 
 
@@ -170,8 +174,15 @@ class MixtureSageLayer(nn.Module):
 
     def forward(self, x: Tensor, edge_index, edge_attr: Optional[Tensor] = None) -> Tensor:
         agg = aggregate(x, _graph(edge_index, x.size(0)), to_row=0, reduce="mean")
-        combined = torch.cat([agg, x], dim=-1)
-        outputs = torch.einsum("nd,kdo->nko", combined, self.weights)
+        if x.is_cuda and dense.supported(self.in_dim, self.out_dim):
+            # einsum('nd,kdo->nko', [agg|x], W) for all experts as ONE two-source GEMM (K5/K6): the
+            # experts are stacked along the output dimension, [agg|x] is never concatenated
+            w_all = self.weights.permute(0, 2, 1).reshape(self.num_experts * self.out_dim, 2 * self.in_dim)
+            outputs = dense.linear_sum([agg, x], [w_all[:, :self.in_dim], w_all[:, self.in_dim:]], None)
+            outputs = outputs.view(x.size(0), self.num_experts, self.out_dim)
+        else:
+            combined = torch.cat([agg, x], dim=-1)
+            outputs = torch.einsum("nd,kdo->nko", combined, self.weights)
         if self.residual:
             outputs = outputs + x.unsqueeze(1)
         return outputs

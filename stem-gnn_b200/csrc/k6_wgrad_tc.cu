@@ -49,6 +49,7 @@ struct WgParams {
     int n, nb, kbt;          // n blocks, k blocks over the CONCATENATED sources [A_0 | A_1]
     int slots;               // partial tiles per CTA (a multiple of nb*kbt)
     int64_t slabs;
+    int slab;                // rows per work item (<= SLAB, multiple of KM)
     float* partial;          // [grid][slots][256*256]: local item i of a CTA lands in slot i % slots
 };
 
@@ -129,9 +130,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
             const int combo = (int)(item - slab * combos);
             const int nbi = combo / p.kbt, kbi = combo - nbi * p.kbt;
             const int kblk = kbi * BT, nblk = nbi * BT;      // kblk: column of the concatenated [A_0 | A_1]
-            const int64_t m0 = slab * SLAB;
+            const int64_t m0 = slab * p.slab;
             int64_t rows = p.m - m0;
-            rows = rows > SLAB ? SLAB : rows;
+            rows = rows > p.slab ? p.slab : rows;
             const int n_st = (int)((rows + KM - 1) / KM);
             const int64_t ldg = p.ldg;
             const float* gbase = p.g + nblk;
@@ -214,8 +215,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
                 if (lane == 0) {
                     // ---- MMA issue for this item (the previous epilogue has drained TMEM)
                     const int64_t slab = item / combos;
-                    int64_t rows = p.m - slab * SLAB;
-                    rows = rows > SLAB ? SLAB : rows;
+                    int64_t rows = p.m - slab * p.slab;
+                    rows = rows > p.slab ? p.slab : rows;
                     const int n_st = (int)((rows + KM - 1) / KM);
                     mbar_wait(smem_u32(acc_empty), (item_it & 1u) ^ 1u);
                     tc_fence_after();
@@ -406,7 +407,7 @@ __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restri
 using namespace stemgnn;
 
 namespace {
-struct WgPlan { int nb, kbt, combos, grid, slots, cs_blocks; int64_t slabs, items; size_t partial_bytes, cs_bytes; };
+struct WgPlan { int nb, kbt, combos, grid, slots, slab, cs_blocks; int64_t slabs, items; size_t partial_bytes, cs_bytes; };
 
 int wg_plan(const stemgnn_linear_wgrad_args* a, WgPlan& pl) {
     SG_CHECK_ARG(a != nullptr, "args is NULL");
@@ -424,9 +425,22 @@ int wg_plan(const stemgnn_linear_wgrad_args* a, WgPlan& pl) {
     pl.kbt = (int)((kcat + wgrad::BT - 1) / wgrad::BT);
     pl.combos = pl.nb * pl.kbt;
     SG_CHECK_ARG(pl.combos <= wgrad::MAX_COMBOS, "weight matrix too large: more than 64 tiles of 256 x 256");
-    pl.slabs = (a->m + wgrad::SLAB - 1) / wgrad::SLAB;
-    pl.items = pl.slabs * pl.combos;
+    // Rows per item: at most SLAB (accuracy), shrunk so that the items fill whole rounds of the grid
+    // (169,343 rows: 331 slabs of 512 x 2 tiles = 4.47 rounds of 148 CTAs -> 365 slabs of 464 = 4.93)
     const int sms = sm_count();
+    {
+        const int64_t slabs0 = (a->m + wgrad::SLAB - 1) / wgrad::SLAB;
+        const int64_t rounds = (slabs0 * pl.combos + sms - 1) / sms;
+        int64_t slabs_t = rounds * sms / pl.combos;
+        if (slabs_t < slabs0) slabs_t = slabs0;
+        int64_t slab = a->m > 0 ? (a->m + slabs_t - 1) / slabs_t : wgrad::SLAB;
+        slab = (slab + wgrad::KM - 1) / wgrad::KM * wgrad::KM;
+        if (slab > wgrad::SLAB) slab = wgrad::SLAB;
+        if (slab < wgrad::KM) slab = wgrad::KM;
+        pl.slab = (int)slab;
+    }
+    pl.slabs = (a->m + pl.slab - 1) / pl.slab;
+    pl.items = pl.slabs * pl.combos;
     pl.grid = (int)(pl.items < sms ? (pl.items > 0 ? pl.items : 1) : sms);
     // one partial tile per local item while that stays under ~256 MB; beyond, slots are reused and
     // the epilogue adds into them (read-modify-write through L2)
@@ -481,7 +495,7 @@ extern "C" int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* a, void* wo
         const bool on = s < a->n_src;
         p.a[s] = on ? a->a[s] : nullptr; p.lda[s] = on ? a->lda[s] : 0; p.k[s] = on ? (int)a->k[s] : 0;
     }
-    p.m = a->m; p.n = (int)a->n; p.nb = pl.nb; p.kbt = pl.kbt; p.slabs = pl.slabs; p.partial = partial; p.slots = pl.slots;
+    p.m = a->m; p.n = (int)a->n; p.nb = pl.nb; p.kbt = pl.kbt; p.slabs = pl.slabs; p.slab = pl.slab; p.partial = partial; p.slots = pl.slots;
     cudaError_t e = cudaFuncSetAttribute(wgrad::wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wgrad::SMEM_BYTES);
     if (e != cudaSuccess) {
         set_error("stemgnn_linear_wgrad: cudaFuncSetAttribute(%d B smem): %s", wgrad::SMEM_BYTES, cudaGetErrorString(e));

@@ -68,7 +68,7 @@ col_reduce_kernel(const float* __restrict__ x, int64_t ldx, const float* __restr
             float4 k = make_float4(0.f, 0.f, 0.f, 0.f), mu = k, is = k, ga = k, be = k;
             if (MODE == 0) k = ld4(x + c);
             else { mu = ld4(cc.mean + c); is = ld4(cc.invstd + c); ga = ld4(cc.gamma + c); be = ld4(cc.beta + c); }
-#pragma unroll 2
+#pragma unroll 4
             for (int64_t r = r0 + rl; r < r1; r += 4) {
                 const float4 v = ld4(x + r * ldx + c);
                 if (MODE == 0) {
@@ -113,8 +113,10 @@ col_final_kernel(const float* __restrict__ part, int blocks, int feat, int64_t r
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
     float a = 0.f, b = 0.f;
-    if (c < feat)
+    if (c < feat) {
+#pragma unroll 8
         for (int i = w; i < blocks; i += 8) { a += part[((int64_t)i * 2) * feat + c]; b += part[((int64_t)i * 2 + 1) * feat + c]; }
+    }
     sh[0][w][lane] = a; sh[1][w][lane] = b;
     __syncthreads();
     if (w == 0 && c < feat) {
