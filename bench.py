@@ -305,10 +305,10 @@ def run_ours(args, w):
         step(x_in, ei_in)
     sync_all()
     graph, loss_out, graph_err = None, None, None
-    if not args.no_graph and world == 1:     # (capturing the NCCL all-reduces of N > 1 ranks hung: not attempted)
+    if not args.no_graph and (world == 1 or os.environ.get("STEMGNN_BENCH_GRAPH_MULTI", "1") == "1"):
         try:
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 loss_out = step(x_in, ei_in)
             graph = g
         except Exception as e:                                     # fall back to eager launches
@@ -401,9 +401,18 @@ def run_ours(args, w):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
-    if rank != 0:
+    def finish():
         if world > 1:
+            torch.cuda.synchronize()
+            if graph is not None:
+                # tearing NCCL down while a captured graph still holds its collectives hangs
+                # (torch 2.11 / NCCL 2.28): the work is done, leave without the teardown
+                sys.stdout.flush(); sys.stderr.flush()
+                os._exit(0)
             dist.destroy_process_group()
+
+    if rank != 0:
+        finish()
         return
     units = w["layers"] * w["e"] * world
     value = units * args.steps / (ms / 1e3)
@@ -453,8 +462,7 @@ def run_ours(args, w):
                                     cores=threads, kind="port",
                                     sample=f"{n} steps of {sample}; oracle/ restatement, torch CPU fp32")
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    finish()
 
 
 def run_partitioned(args, w):
