@@ -149,3 +149,34 @@ def test_sage_conv_uses_tensor_core_linear_and_matches_torch_layers():
     ref = F.linear(agg.double(), conv.lin_l.weight.double(), conv.lin_l.bias.double()) + \
         F.linear(x.double(), conv.lin_r.weight.double())
     assert _rel_err(out, ref) < 1e-5
+
+
+def test_wgrad_large_m_reuses_partial_slots():
+    """More work items per CTA than partial-tile slots (the read-modify-write epilogue path):
+    620k rows = 1,211+ slabs over 148 CTAs against 6 slots."""
+    g_ = torch.Generator().manual_seed(21)
+    m, n, k = 620_000, 256, 128
+    g = torch.randn(m, n, generator=g_).to(DEV)
+    a = torch.randn(m, k, generator=g_).to(DEV)
+    (gw,), gb = S.linear_wgrad_raw(g, [a], want_bias=True)
+    ref = torch.zeros(n, k, dtype=torch.float64, device=DEV)
+    for lo in range(0, m, 100_000):                      # fp64 reference in chunks (memory)
+        ref += g[lo:lo + 100_000].double().t() @ a[lo:lo + 100_000].double()
+    t32 = g.t() @ a
+    err, err32 = _rel_err(gw, ref), _rel_err(t32, ref)
+    assert err < 1e-5, (err, err32)
+    assert ((gb.double() - g.double().sum(0)).abs().max() / g.double().sum(0).abs().max()).item() < 1e-5
+    (gw2,), _ = S.linear_wgrad_raw(g, [a])
+    assert torch.equal(gw, gw2)
+
+
+def test_linear_large_m():
+    g_ = torch.Generator().manual_seed(22)
+    m, n, k = 1_300_000, 128, 64
+    a = torch.randn(m, k, generator=g_).to(DEV)
+    w = (torch.randn(n, k, generator=g_) / 8).to(DEV)
+    out = S.linear_raw([a], [w])
+    idx = torch.randint(0, m, (4096,), generator=g_).to(DEV)
+    ref = a[idx].double() @ w.double().t()
+    assert _rel_err(out[idx], ref) < 1e-5
+    assert _rel_err(out[-300:], a[-300:].double() @ w.double().t()) < 1e-5

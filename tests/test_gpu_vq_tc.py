@@ -143,8 +143,10 @@ def test_matches_oracle_formula_on_cpu():
     # (relative) of the fp64 optimum -- the CPU's own fp32 argmax is held to the same bound
     for m in bad.tolist():
         assert best64[m] - s64[m, ind[m]] <= 1e-6 * abs(best64[m]), (m, best64[m], s64[m, ind[m]], s64[m, ref[m]])
+    # the CPU restatement's own fp32 argmax (host BLAS, summation order varies by machine) sits
+    # within a few fp32 ulps of the intermediate x2 + e2 ~ 256 of the optimum
     ref_gap = best64 - s64[torch.arange(rows), ref]
-    assert (ref_gap <= 1e-6 * best64.abs()).all(), "CPU oracle itself is outside the 1e-6 gap"
+    assert (ref_gap <= 4e-6 * best64.abs()).all(), "CPU oracle far outside the near-tie gap"
     assert bad.numel() <= 8
     same = ind == ref
     assert torch.equal(q.cpu()[same], embed[0][ref][same])
