@@ -90,6 +90,8 @@ typedef struct {
     int act;                 /* STEMGNN_ACT_* */
     int backward;            /* 0 fwd, 1 bwd */
     float* out;              /* [n_rows,F] */
+    int64_t out_ld;          /* row stride of out in floats; 0 = feat (contiguous).  ABI 2 */
+    int64_t row_x_ld;        /* row stride of row_x in floats; 0 = feat */
 } stemgnn_aggregate_args;
 
 int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t stream);

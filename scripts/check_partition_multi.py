@@ -36,9 +36,33 @@ def main():
     for _ in range(10): step()
     e1.record(); torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda"); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    slices = len(pg.feature_slices(f))
+    # the same exchange unsliced (one blocking all-gather per direction) and on a bf16 wire
+    def timed(pgx):
+        def st():
+            xl.grad = None
+            o = S.aggregate(xl, pgx, reduce="mean", act="relu"); o.backward(go[lo:hi])
+        for _ in range(3): st()
+        torch.cuda.synchronize(); dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(10): st()
+        b.record(); torch.cuda.synchronize()
+        m = torch.tensor([a.elapsed_time(b) / 10], device="cuda"); dist.all_reduce(m, op=dist.ReduceOp.MAX)
+        return m.item()
+    pg1 = S.PartitionedGraph(ei, n, halo_slices=1)
+    ms1 = timed(pg1)
+    pgb = S.PartitionedGraph(ei, n, halo_dtype=torch.bfloat16)
+    xl.grad = None
+    ob = S.aggregate(xl, pgb, reduce="mean", act="relu"); ob.backward(go[lo:hi])
+    errb = ((ob.detach() - ref.detach()[lo:hi]).abs().max() / ref.detach().abs().max()).item()
+    errg = ((xl.grad - xs.grad[lo:hi]).abs().max() / xs.grad.abs().max()).item()
+    msb = timed(pgb)
     if rank == 0:
         print(f"partition check world={world} N={n} E={e} F={f}: bit_exact={bool(t.item())} "
-              f"fwd+bwd {ms.item():.3f} ms  {2 * e / ms.item() / 1e6:.1f} Medges/s (both directions)", flush=True)
+              f"fwd+bwd {ms.item():.3f} ms ({slices} feature slices)  unsliced {ms1:.3f} ms  "
+              f"bf16 wire {msb:.3f} ms (max err fwd {errb:.1e} bwd {errg:.1e})  "
+              f"{2 * e / ms.item() / 1e6:.1f} Medges/s (both directions)", flush=True)
     dist.destroy_process_group()
     sys.exit(0 if t.item() else 1)
 

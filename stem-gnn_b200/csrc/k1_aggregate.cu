@@ -41,6 +41,7 @@ struct AggParams {
     const float* edge_feat; const float* type_table; const int32_t* edge_type;
     const float* edge_weight; const float* row_x;
     int relu; float* out;
+    int64_t out_ld, row_x_ld;   // row strides (floats) of out / row_x: column slices of wider matrices
 };
 
 // One group of U edges of one row.  FULL (all U edges exist, every chunk of the lane inside F) drops
@@ -151,7 +152,7 @@ aggregate_kernel(const AggParams a) {
         for (int c = 0; c < CH; ++c) {
 #pragma unroll
             for (int k = 0; k < VEC; ++k) { acc[c].v[k] = 0.f; rx[c].v[k] = 0.f; }
-            if (BWD && MODE != MODE_W && RELU && fok[c]) rx[c].load(a.row_x + row * F + foff[c]);
+            if (BWD && MODE != MODE_W && RELU && fok[c]) rx[c].load(a.row_x + row * a.row_x_ld + foff[c]);
         }
 
         for (int p = beg; p < end; p += U)
@@ -169,7 +170,7 @@ aggregate_kernel(const AggParams a) {
                 if (BWD && MODE == MODE_PLAIN && RELU) r = rx[c].v[k] > 0.f ? r : 0.f;
                 acc[c].v[k] = r;
             }
-            acc[c].store(a.out + row * F + foff[c]);
+            acc[c].store(a.out + row * a.out_ld + foff[c]);
         }
     }
 }
@@ -246,9 +247,13 @@ extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream
     p.edge_feat = a->edge_feat; p.type_table = a->type_table; p.edge_type = a->edge_type;
     p.edge_weight = a->edge_weight; p.row_x = a->row_x;
     p.relu = a->act == STEMGNN_ACT_RELU; p.out = a->out;
+    p.out_ld = a->out_ld ? a->out_ld : a->feat;
+    p.row_x_ld = a->row_x_ld ? a->row_x_ld : a->feat;
+    SG_CHECK_ARG(p.out_ld >= a->feat && p.row_x_ld >= a->feat, "out_ld / row_x_ld smaller than feat");
 
     bool vec4 = (a->feat % 4 == 0) && aligned16(a->gathered) && aligned16(a->out) &&
-                aligned16(a->edge_feat) && aligned16(a->type_table) && aligned16(a->row_x);
+                aligned16(a->edge_feat) && aligned16(a->type_table) && aligned16(a->row_x) &&
+                p.out_ld % 4 == 0 && p.row_x_ld % 4 == 0;
     const int mode = has_w ? MODE_W : (has_xe ? MODE_XE : MODE_PLAIN);
     // a backward pass with neither a per-edge division nor a relu mask is the plain sum over the
     // transposed structure: the forward kernel

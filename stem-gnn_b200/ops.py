@@ -25,7 +25,9 @@ def _f32c(t, name):
 
 def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_cnt=None,
                     edge_feat=None, type_table=None, edge_type=None, edge_weight=None, row_x=None,
-                    act=ACT_NONE, backward=False):
+                    act=ACT_NONE, backward=False, out_cols=None, gathered_rows=None):
+    """One stemgnn_aggregate call.  `out_cols=(lo, hi)` writes columns [lo, hi) of the wider `out`
+    (and reads the same columns of `row_x`): the feature-sliced halo pipeline."""
     per_edge = edge_feat is not None or edge_type is not None or edge_weight is not None
     a = _lib.AggregateArgs(
         rowptr=_lib.ptr(csr.rowptr), col=_lib.ptr(csr.col),
@@ -35,6 +37,15 @@ def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_c
         edge_feat=_lib.ptr(edge_feat), type_table=_lib.ptr(type_table),
         edge_type=_lib.ptr(edge_type), edge_weight=_lib.ptr(edge_weight), row_x=_lib.ptr(row_x),
         act=act, backward=int(backward), out=_lib.ptr(out))
+    if out_cols is not None:
+        lo, hi = out_cols
+        if hi - lo != gathered.size(1) or lo % 4:
+            raise ValueError("column slice must match the gathered width and start on a 16-byte boundary")
+        a.out = out.data_ptr() + 4 * lo
+        a.out_ld = out.stride(0)
+        if row_x is not None:
+            a.row_x = row_x.data_ptr() + 4 * lo
+            a.row_x_ld = row_x.stride(0)
     # algorithmic bytes: every row read once (X fits the 126 MB L2) or one source
     # row per edge (it does not); index, count and per-edge streams once
     n_g, F, E = n_gather_rows, gathered.size(1), csr.e
@@ -98,7 +109,24 @@ class _Aggregate(torch.autograd.Function):
 class _PartAggregate(torch.autograd.Function):
     """The same aggregation on a 1-D destination-partitioned graph: x holds this rank's rows;
     the forward all-gathers the row blocks (halo exchange) and runs K1 on the owned destination
-    rows, the backward all-gathers the g_out blocks and runs K2 on the owned source rows."""
+    rows, the backward all-gathers the (pre-scaled) g_out blocks and runs K2 on the owned source
+    rows.  The exchange is pipelined by FEATURE slices: all slices are issued asynchronously, the
+    aggregation of slice k runs while slices k+1.. are still on the wire.  A row's sum still walks
+    the same edges in the same order, so the result stays bit-identical to one GPU."""
+
+    @staticmethod
+    def _run(pg, csr, local, out, row_cnt, row_x, act, backward):
+        F = local.size(1)
+        slices = pg.feature_slices(F)
+        if len(slices) == 1:
+            full = pg.gather_rows(local)
+            _aggregate_call(csr, full.size(0), full, out, row_cnt=row_cnt, row_x=row_x, act=act, backward=backward)
+            return
+        pending = [pg.gather_cols_async(local, lo, hi) for lo, hi in slices]      # all on the wire
+        for (lo, hi), fin in zip(slices, pending):
+            full = fin()                                                           # wait for this slice only
+            _aggregate_call(csr, full.size(0), full, out, row_cnt=row_cnt, row_x=row_x, act=act,
+                            backward=backward, out_cols=(lo, hi))
 
     @staticmethod
     def forward(ctx, x, pg, reduce, act):
@@ -106,10 +134,8 @@ class _PartAggregate(torch.autograd.Function):
         if x.dim() != 2 or x.size(0) != pg.num_nodes:
             raise ValueError(f"x must hold this rank's {pg.num_nodes} rows")
         fwd = pg.fwd_csr()
-        x_full = pg.gather_rows(x)
         out = torch.empty_like(x)
-        _aggregate_call(fwd, x_full.size(0), x_full, out,
-                        row_cnt=fwd.cnt if reduce == REDUCE_MEAN else None, act=act)
+        _PartAggregate._run(pg, fwd, x, out, fwd.cnt if reduce == REDUCE_MEAN else None, None, act, False)
         ctx.pg, ctx.reduce, ctx.act = pg, reduce, act
         ctx.save_for_backward(x)
         return out
@@ -121,10 +147,8 @@ class _PartAggregate(torch.autograd.Function):
         g_out = _f32c(g_out, "grad")
         if ctx.reduce == REDUCE_MEAN:       # own rows, own counts: no count exchange
             g_out = _row_scale(g_out, pg.fwd_csr().cnt)
-        g_full = pg.gather_rows(g_out)
         g_x = torch.empty_like(x)
-        _aggregate_call(pg.bwd_csr(), g_full.size(0), g_full, g_x,
-                        row_x=x if ctx.act == ACT_RELU else None, act=ctx.act, backward=True)
+        _PartAggregate._run(pg, pg.bwd_csr(), g_out, g_x, None, x if ctx.act == ACT_RELU else None, ctx.act, True)
         return g_x, None, None, None
 
 

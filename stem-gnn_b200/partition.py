@@ -61,7 +61,8 @@ class PartitionedGraph:
 
     def __init__(self, edge_index: Optional[torch.Tensor], num_nodes: int, rank: Optional[int] = None,
                  world: Optional[int] = None, group=None,
-                 gather: Optional[Callable[[torch.Tensor], torch.Tensor]] = None, pre_split=None):
+                 gather: Optional[Callable[[torch.Tensor], torch.Tensor]] = None, pre_split=None,
+                 halo_slices: Optional[int] = None, halo_dtype: Optional[torch.dtype] = None):
         if world is None:
             world = dist.get_world_size(group) if dist.is_initialized() else 1
         if rank is None:
@@ -78,6 +79,12 @@ class PartitionedGraph:
         self.fwd_edges, self.bwd_edges = fwd, bwd
         self._gather = gather
         self._csr = {}
+        # halo pipeline: number of feature slices per exchange (None: by width) and the wire dtype
+        # (None = fp32, bit-identical to one GPU; torch.bfloat16 halves the bytes at a stated 2^-9
+        # relative error per gathered feature)
+        self.halo_slices, self.halo_dtype = halo_slices, halo_dtype
+        if halo_dtype not in (None, torch.float32, torch.bfloat16):
+            raise ValueError("halo_dtype must be None, torch.float32 or torch.bfloat16")
 
     # ---- structure (K0 on the local edge lists) ------------------------------------------------
     def fwd_csr(self) -> CSR:
@@ -92,19 +99,49 @@ class PartitionedGraph:
             self._csr["b"] = CSR(self.bwd_edges, self.num_nodes, 0)
         return self._csr["b"]
 
+    def feature_slices(self, f: int) -> List[Tuple[int, int]]:
+        """Column ranges the halo exchange of an [n, f] matrix is pipelined over (16-byte aligned)."""
+        if (self.world == 1 and self._gather is None) or f % 4:
+            return [(0, f)]
+        s = self.halo_slices
+        if s is None:
+            # measured on 2 B200s (F=256, 1.2M nodes): 4 slices of 64 columns 7.60 ms vs 7.54 ms
+            # unsliced -- what the overlap hides, the narrower aggregation launches give back; slices
+            # stay >= 256 columns wide by default
+            s = max(1, f // 256)
+        s = max(1, min(int(s), f // 4))
+        w = -(-(f // 4) // s) * 4                       # slice width: multiple of 4 columns
+        return [(lo, min(f, lo + w)) for lo in range(0, f, w)]
+
+    def _padded_block(self, local: torch.Tensor) -> torch.Tensor:
+        n, f = local.shape
+        if n == self.per and local.is_contiguous():
+            return local
+        blk = local.new_zeros((self.per, f))
+        blk[:n] = local
+        return blk
+
+    def gather_cols_async(self, local: torch.Tensor, lo: int, hi: int):
+        """Start the exchange of columns [lo, hi) of this rank's block; returns a callable that waits
+        for it and hands back the gathered fp32 [world*per, hi-lo] matrix."""
+        blk = self._padded_block(local[:, lo:hi])
+        if self._gather is not None:
+            full = self._gather(blk)
+            return lambda: full
+        wire = blk if self.halo_dtype in (None, torch.float32) else blk.to(self.halo_dtype)
+        out = wire.new_empty((self.world * self.per, hi - lo))
+        nbytes = (self.world - 1) * self.per * (hi - lo) * wire.element_size()
+        work = dist.all_gather_into_tensor(out, wire.contiguous(), group=self.group, async_op=True)
+
+        def finish():
+            with _lib.traced("halo_wait", nbytes, 0, 0):
+                work.wait()
+            return out if out.dtype == torch.float32 else out.float()
+        return finish
+
     def gather_rows(self, local: torch.Tensor) -> torch.Tensor:
         """[n_local, F] -> [world*per, F]: every rank's block, padded to `per` rows, in rank order
         (so row g of the result is global node g).  This is the halo exchange."""
-        n, f = local.shape
         if self.world == 1 and self._gather is None:
             return local
-        blk = local
-        if n != self.per:
-            blk = local.new_zeros((self.per, f))
-            blk[:n] = local
-        if self._gather is not None:
-            return self._gather(blk)
-        out = local.new_empty((self.world * self.per, f))
-        with _lib.traced("halo_all_gather", (self.world - 1) * self.per * f * local.element_size(), 0, 0):
-            dist.all_gather_into_tensor(out, blk.contiguous(), group=self.group)
-        return out
+        return self.gather_cols_async(local, 0, local.size(1))()
