@@ -14,15 +14,19 @@
 // are 2^-22 relative: the result sits within ~1e-6 of the fp32 product (tests hold 1e-5, the
 // north_star bound) with the full fp32 exponent range -- no scaling pass, no overflow cases.
 //
-// A persistent CTA owns a 256-row tile: two M=128 accumulators (2 x 256 TMEM columns) share every
-// W stage, which halves the L2 traffic of the weight stream against a 128-row tile.  Eight
+// A persistent CTA owns a 128-row tile with a double-buffered 2 x 256-column TMEM accumulator (the
+// epilogue of tile t overlaps the MMAs of tile t+1), or -- for wide layers whose split weight
+// image is several MB -- a 256-row tile whose two M=128 accumulators share every W stage, which
+// halves the L2 traffic of the weight stream (Shape<MH>, chosen per call).  Eight
 // producer warps read the fp32 rows of A once from HBM, split them and store the hi / lo images
-// K-major with the 64-byte swizzle (16 tf32 per row: a 64 KB stage holds A hi/lo + W hi/lo, three
-// stages fit).  W is split once per call into the same swizzled stage images in global memory and
+// K-major with the 64-byte swizzle (16 tf32 per row: a 48 or 64 KB stage holds A hi/lo + W hi/lo,
+// four or three stages fit).  W is split once per call into the same swizzled stage images in global memory and
 // streamed by one elected thread with 1-D bulk async copies.  One elected thread issues the MMAs;
 // eight epilogue warps drain TMEM through a padded shared-memory transpose so that every global
 // store instruction writes full 128-byte lines.
 // FLOPs: 3 * 2*M*N*K on the tensor pipe (tf32); HBM: M*K*4 (A) + M*N*4 (out).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -31,17 +35,26 @@ namespace lin {
 
 using namespace tcptx;
 
-constexpr int BM = 256;                  // rows per tile: two UMMA M=128 halves
 constexpr int BN = 256;                  // output columns per accumulator = max UMMA N
 constexpr int BK = 16;                   // tf32 per smem row (64 B, SWIZZLE_64B)
 constexpr int IMG_BYTES = 256 * 64;      // one 256-row operand image of a stage: 16 KB
-constexpr int STAGE_BYTES = 4 * IMG_BYTES;   // A hi, A lo, W hi, W lo
 constexpr int W_STAGE_BYTES = 2 * IMG_BYTES;
-constexpr int NS = 3;                    // stages
+// Tile shape: MH = UMMA M=128 halves per tile.
+//   MH = 2: 256-row tiles, both halves share every W stage (half the L2 traffic of the weight
+//           stream), accumulators use all 512 TMEM columns -> the epilogue is NOT overlapped;
+//   MH = 1: 128-row tiles, 2 x 256-column accumulators double-buffered -> the epilogue of tile t
+//           overlaps the MMAs of tile t+1, twice as many tiles (finer tail), W streamed twice as often.
+template <int MH> struct Shape {
+    static constexpr int BM = 128 * MH;
+    static constexpr int A_IMG = BM * 64;                        // hi or lo image of the A rows of a stage
+    static constexpr int STAGE_BYTES = 2 * A_IMG + W_STAGE_BYTES;   // A hi, A lo, W hi, W lo
+    static constexpr int NS = MH == 2 ? 3 : 4;                   // stages
+    static constexpr int NBUF = MH == 2 ? 1 : 2;                 // accumulator buffers
+    static constexpr int SMEM_BYTES = NS * STAGE_BYTES + 8 * (32 * 33) * 4 + 24 * 8 + 16;
+};
 constexpr int EPI_WARPS = 8, PROD_WARP0 = 8, LOAD_WARP = 16, MMA_WARP = 17;
 constexpr int NUM_THREADS = 576;
 constexpr int STAGING_WORDS = 32 * 33;   // per epilogue warp: 32 rows x 32 columns, padded
-constexpr int SMEM_BYTES = NS * STAGE_BYTES + EPI_WARPS * STAGING_WORDS * 4 + 16 * 8 + 16;
 
 struct LinParams {
     const float* a[2];
@@ -97,7 +110,11 @@ __global__ void __launch_bounds__(256) lin_w_image_kernel(const WPrep p) {
 }
 
 // ---- the GEMM ------------------------------------------------------------------------------------
+template <int MH>
 __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams p) {
+    using SH = Shape<MH>;
+    constexpr int BM = SH::BM, NS = SH::NS, NBUF = SH::NBUF, STAGE_BYTES = SH::STAGE_BYTES, A_IMG = SH::A_IMG;
+    constexpr int W_OFF = 2 * A_IMG;      // W hi image inside a stage; W lo follows
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* stages = smem;
     float* s_stage = reinterpret_cast<float*>(smem + NS * STAGE_BYTES);      // [8][32 x 33]
@@ -105,9 +122,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
     uint64_t* a_full = bars;              // [NS] 128 producer arrivals
     uint64_t* w_full = bars + NS;         // [NS] loader expect_tx
     uint64_t* empty = bars + 2 * NS;      // [NS] tcgen05.commit
-    uint64_t* acc_full = bars + 3 * NS;   // tcgen05.commit after the last chunk of a tile
-    uint64_t* acc_empty = acc_full + 1;   // 256 epilogue arrivals
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    uint64_t* acc_full = bars + 3 * NS;   // [NBUF] tcgen05.commit after the last chunk of a tile
+    uint64_t* acc_empty = acc_full + 2;   // [NBUF] 256 epilogue arrivals
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row_tiles = (p.m + BM - 1) / BM;
@@ -119,8 +136,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
             mbar_init(smem_u32(w_full + i), 1);
             mbar_init(smem_u32(empty + i), 1);
         }
-        mbar_init(smem_u32(acc_full), 1);
-        mbar_init(smem_u32(acc_empty), EPI_WARPS * 32);
+        for (int i = 0; i < NBUF; ++i) {
+            mbar_init(smem_u32(acc_full + i), 1);
+            mbar_init(smem_u32(acc_empty + i), EPI_WARPS * 32);
+        }
         fence_barrier_init();
     }
     if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -140,7 +159,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     const uint32_t slot = seq % NS;
                     mbar_wait(smem_u32(empty + slot), ((seq / NS) & 1u) ^ 1u);
                     mbar_expect_tx(smem_u32(w_full + slot), W_STAGE_BYTES);
-                    bulk_g2s(smem_u32(stages + slot * STAGE_BYTES + 2 * IMG_BYTES), src + (int64_t)c * W_STAGE_BYTES,
+                    bulk_g2s(smem_u32(stages + slot * STAGE_BYTES + W_OFF), src + (int64_t)c * W_STAGE_BYTES,
                              W_STAGE_BYTES, smem_u32(w_full + slot));
                 }
             }
@@ -155,7 +174,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                 ncols = ncols > BN ? BN : ncols;
                 const int n_mma = ncols < 16 ? 16 : ((ncols + 15) & ~15);
                 const uint32_t idesc = make_idesc_tf32(128, n_mma, 0, 0);
-                mbar_wait(smem_u32(acc_empty), (item_it & 1u) ^ 1u);
+                const uint32_t buf = item_it % NBUF;
+                mbar_wait(smem_u32(acc_empty + buf), ((item_it / NBUF) & 1u) ^ 1u);
                 tc_fence_after();
                 for (int c = 0; c < p.kct; ++c, ++seq) {
                     const uint32_t slot = seq % NS, ph = (seq / NS) & 1u;
@@ -164,14 +184,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     tc_fence_after();
                     const uint32_t base = smem_u32(stages + slot * STAGE_BYTES);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
+                    for (int h = 0; h < MH; ++h) {
 #pragma unroll
                         for (int ks = 0; ks < 2; ++ks) {
-                            const uint64_t a_hi = smem_desc_sw64(base + h * (IMG_BYTES / 2) + ks * 32);
-                            const uint64_t a_lo = smem_desc_sw64(base + IMG_BYTES + h * (IMG_BYTES / 2) + ks * 32);
-                            const uint64_t w_hi = smem_desc_sw64(base + 2 * IMG_BYTES + ks * 32);
-                            const uint64_t w_lo = smem_desc_sw64(base + 3 * IMG_BYTES + ks * 32);
-                            const uint32_t d = tmem_base + (uint32_t)h * BN;
+                            const uint64_t a_hi = smem_desc_sw64(base + h * 8192 + ks * 32);
+                            const uint64_t a_lo = smem_desc_sw64(base + A_IMG + h * 8192 + ks * 32);
+                            const uint64_t w_hi = smem_desc_sw64(base + W_OFF + ks * 32);
+                            const uint64_t w_lo = smem_desc_sw64(base + W_OFF + IMG_BYTES + ks * 32);
+                            const uint32_t d = tmem_base + (uint32_t)(MH == 2 ? h : buf) * BN;
                             umma_tf32(d, a_lo, w_hi, idesc, (c > 0 || ks > 0) ? 1u : 0u);
                             umma_tf32(d, a_hi, w_lo, idesc, 1u);
                             umma_tf32(d, a_hi, w_hi, idesc, 1u);
@@ -179,13 +199,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     }
                     umma_commit(smem_u32(empty + slot));
                 }
-                umma_commit(smem_u32(acc_full));
+                umma_commit(smem_u32(acc_full + buf));
             }
         }
     } else if (warp >= PROD_WARP0 && warp < LOAD_WARP) {
         // ================= producers: fp32 rows -> tf32 hi / lo images =================
         // Two groups of 128 threads take alternate chunks.  Thread (j, rr) of a group owns the
-        // 16 B unit j of rows rr, rr+32, ..., rr+224: a quad reads 64 contiguous bytes per row.
+        // 16 B unit j of rows rr, rr+32, ... of the tile: a quad reads 64 contiguous bytes per row.
+        constexpr int RPT = 4 * MH;       // rows per thread and chunk
         const int pt = (threadIdx.x - PROD_WARP0 * 32) & 127;
         const int grp = (threadIdx.x - PROD_WARP0 * 32) >> 7;
         const int j = pt & 3, rr = pt >> 2;
@@ -202,9 +223,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                 const bool col_ok = kcol < (s ? p.k[1] : p.k[0]);
                 const float* ap = (s ? p.a[1] : p.a[0]) + kcol;
                 const int64_t lda = (s ? p.lda[1] : p.lda[0]);
-                float4 v[8];
+                float4 v[RPT];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
+                for (int i = 0; i < RPT; ++i) {
                     const int64_t r = row0 + rr + 32 * i;
                     v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (col_ok && r < p.m) v[i] = __ldg(reinterpret_cast<const float4*>(ap + r * lda));
@@ -216,7 +237,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     const int kcol2 = (s2 == 0 ? c2 : c2 - p.kc[0]) * BK + 4 * j;
                     if (kcol2 < (s2 ? p.k[1] : p.k[0])) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) {
+                        for (int i = 0; i < RPT; ++i) {
                             const int64_t r = row0 + rr + 32 * i;
                             if (r < p.m) prefetch_l2((s2 ? p.a[1] : p.a[0]) + kcol2 + r * (s2 ? p.lda[1] : p.lda[0]));
                         }
@@ -225,11 +246,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                 mbar_wait(smem_u32(empty + slot), ((seq / NS) & 1u) ^ 1u);
                 uint8_t* dst = stages + slot * STAGE_BYTES + soff;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
+                for (int i = 0; i < RPT; ++i) {
                     float4 hi, lo;
                     tf32_split4(v[i], hi, lo);
                     *reinterpret_cast<float4*>(dst + i * 2048) = hi;
-                    *reinterpret_cast<float4*>(dst + IMG_BYTES + i * 2048) = lo;
+                    *reinterpret_cast<float4*>(dst + A_IMG + i * 2048) = lo;
                 }
                 fence_async_smem();
                 mbar_arrive(smem_u32(a_full + slot));
@@ -237,6 +258,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
         }
     } else {
         // ================= epilogue: TMEM -> padded smem transpose -> full-line global stores =====
+        // MH = 2: warp (q, h) drains lane quarter q of M half h, all column chunks.
+        // MH = 1: warps w and w+4 share lane quarter q and take alternate 32-column chunks.
         const int q = warp & 3, h = warp >> 2;
         float* st = s_stage + warp * STAGING_WORDS;
         uint32_t item_it = 0;
@@ -245,13 +268,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
             const int nt = (int)(item - rt * p.n_tiles);
             int ncols = p.n - nt * BN;
             ncols = ncols > BN ? BN : ncols;
-            const int64_t row_base = rt * BM + h * 128 + q * 32;
-            mbar_wait(smem_u32(acc_full), item_it & 1u);
+            const uint32_t buf = item_it % NBUF;
+            const int64_t row_base = rt * BM + (MH == 2 ? h * 128 : 0) + q * 32;
+            mbar_wait(smem_u32(acc_full + buf), (item_it / NBUF) & 1u);
             tc_fence_after();
-            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)h * BN;
+            const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(MH == 2 ? h : buf) * BN;
             if (row_base < p.m) {
 #pragma unroll 1
-                for (int c0 = 0; c0 < ncols; c0 += 32) {
+                for (int c0 = (MH == 2 ? 0 : h * 32); c0 < ncols; c0 += (MH == 2 ? 32 : 64)) {
                     float v[32];
                     tmem_ld32(t_addr + (uint32_t)c0, v);
                     tmem_ld_wait();
@@ -271,7 +295,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                 }
             }
             tc_fence_before();
-            mbar_arrive(smem_u32(acc_empty));
+            mbar_arrive(smem_u32(acc_empty + buf));
         }
     }
     tc_fence_before();
@@ -347,15 +371,26 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
 
     p.kct = kct; p.m = a->m; p.n = (int)a->n; p.n_tiles = n_tiles; p.wimg = img; p.bias = a->bias;
     p.out = a->out; p.ldo = a->ldo;
-    cudaError_t e = cudaFuncSetAttribute(lin::lin_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, lin::SMEM_BYTES);
+    // Tile shape (measured, scripts/lin_bench.py, M = 169,343): 128-row tiles with the double-buffered
+    // accumulator win 10-17 % while the split weight image is small (N=256, K<=512: 114 / 196 us
+    // against 136 / 218 us); once it reaches a few MB (N=512, K=1024: 4 MB) streaming it twice as
+    // often costs more than the exposed epilogue (730 vs 687 us).  STEMGNN_LIN_BM=128|256 forces one.
+    static const int forced = [] { const char* e = getenv("STEMGNN_LIN_BM"); return e ? atoi(e) : 0; }();
+    const int mh = forced == 256 ? 2 : (forced == 128 ? 1 : ((size_t)n_tiles * kct * lin::W_STAGE_BYTES >= (2u << 20) ? 2 : 1));
+    const int smem_bytes = mh == 2 ? lin::Shape<2>::SMEM_BYTES : lin::Shape<1>::SMEM_BYTES;
+    cudaError_t e = mh == 2
+        ? cudaFuncSetAttribute(lin::lin_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes)
+        : cudaFuncSetAttribute(lin::lin_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     if (e != cudaSuccess) {
-        set_error("stemgnn_linear: cudaFuncSetAttribute(%d B smem): %s", lin::SMEM_BYTES, cudaGetErrorString(e));
+        set_error("stemgnn_linear: cudaFuncSetAttribute(%d B smem): %s", smem_bytes, cudaGetErrorString(e));
         return STEMGNN_ECUDA;
     }
     const int sms = sm_count();
-    const int64_t items = ((a->m + lin::BM - 1) / lin::BM) * n_tiles;
+    const int bm = 128 * mh;
+    const int64_t items = ((a->m + bm - 1) / bm) * n_tiles;
     const unsigned grid = (unsigned)(items < sms ? items : sms);
-    SG_LAUNCH(lin::lin_tc_kernel<<<grid, lin::NUM_THREADS, lin::SMEM_BYTES, stream>>>(p));
+    if (mh == 2) SG_LAUNCH(lin::lin_tc_kernel<2><<<grid, lin::NUM_THREADS, smem_bytes, stream>>>(p));
+    else SG_LAUNCH(lin::lin_tc_kernel<1><<<grid, lin::NUM_THREADS, smem_bytes, stream>>>(p));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

@@ -356,13 +356,17 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __rest
         float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
         if (c < n) {
             int64_t r = r0 + rl;
-            for (; r + 4 < r1; r += 8) {
-                const float4 a = __ldg(reinterpret_cast<const float4*>(g + r * ldg + c));
-                const float4 b = __ldg(reinterpret_cast<const float4*>(g + (r + 4) * ldg + c));
-                s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
-                s1.x += b.x; s1.y += b.y; s1.z += b.z; s1.w += b.w;
+            for (; r + 28 < r1; r += 32) {          // 8 independent 16 B loads in flight per thread
+                float4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(g + (r + 4 * u) * ldg + c));
+#pragma unroll
+                for (int u = 0; u < 8; u += 2) {
+                    s0.x += v[u].x; s0.y += v[u].y; s0.z += v[u].z; s0.w += v[u].w;
+                    s1.x += v[u + 1].x; s1.y += v[u + 1].y; s1.z += v[u + 1].z; s1.w += v[u + 1].w;
+                }
             }
-            if (r < r1) {
+            for (; r < r1; r += 4) {
                 const float4 a = __ldg(reinterpret_cast<const float4*>(g + r * ldg + c));
                 s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
             }
