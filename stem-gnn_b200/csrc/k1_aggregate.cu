@@ -117,13 +117,7 @@ __device__ __forceinline__ void edge_group(const AggParams& a, const int F, cons
 // against 3 everywhere, 4 blocks (64 registers) gain 10 % for one 16 B chunk per lane across a full
 // warp (F = 100..128) and lose 5-10 % elsewhere (spills, L2 thrash), 5 blocks always lose.
 template <int LANES, int CH>
-struct AggOcc {
-#ifdef AGG_OCC_ALT   // A/B builds only
-    static constexpr int min_blocks = CH <= 2 ? 4 : (CH <= 6 ? 3 : 2);
-#else
-    static constexpr int min_blocks = (LANES == 32 && CH == 1) ? 4 : (CH <= 6 ? 3 : 2);
-#endif
-};
+struct AggOcc { static constexpr int min_blocks = (LANES == 32 && CH == 1) ? 4 : (CH <= 6 ? 3 : 2); };
 
 template <int VEC, int LANES, int CH, int MODE, bool BWD, bool RELU>
 __global__ void __launch_bounds__(256, AggOcc<LANES, CH>::min_blocks)
