@@ -152,6 +152,9 @@ int stemgnn_vq_backward(const float* g_q, const float* x, const float* q, const 
  * layers, and -- with w_transposed = 1, W_s given as [k, n] -- any A @ W product such as the
  * backward-data term g_out @ lin.weight.  Runs on the tcgen05 tensor cores as 3xTF32 (operands
  * split hi + lo, three MMAs, fp32 accumulate): within 1e-5 of torch's fp32 result, full fp32 range.
+ * The tensor-core accumulator truncates (about 7.5e-9 of the output scale per accumulated column), so
+ * a caller that needs 1e-5 beyond sum(k) ~ 1024 splits K into slabs and chains calls with accumulate = 1
+ * (the drop-in host op does: stem-gnn_b200/dense.py).
  * k[s], lda[s] must be multiples of 4 and a[s] 16-byte aligned (row segments are read as float4). */
 typedef struct {
     int64_t m;            /* rows */
@@ -166,6 +169,8 @@ typedef struct {
     const float* bias;    /* [n] or NULL */
     float* out;           /* [m, n], row stride ldo floats */
     int64_t ldo;
+    int32_t accumulate;   /* 1: out += product (round-to-nearest add in the epilogue) instead of out = */
+    int32_t reserved;
 } stemgnn_linear_args;
 
 int stemgnn_linear_workspace(const stemgnn_linear_args* args_host, size_t* bytes_host);

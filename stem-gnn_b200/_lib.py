@@ -39,7 +39,7 @@ class VqCodeStatsArgs(C.Structure):
 class LinearArgs(C.Structure):
     _fields_ = [("m", _i64), ("n", _i64), ("n_src", _i32), ("w_transposed", _i32), ("a", _vp * 2),
                 ("lda", _i64 * 2), ("k", _i64 * 2), ("w", _vp * 2), ("ldw", _i64 * 2), ("bias", _vp),
-                ("out", _vp), ("ldo", _i64)]
+                ("out", _vp), ("ldo", _i64), ("accumulate", _i32), ("reserved", _i32)]
 
 
 class LinearWgradArgs(C.Structure):

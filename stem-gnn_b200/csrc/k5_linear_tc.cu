@@ -68,6 +68,7 @@ struct LinParams {
     const float* bias;
     float* out;
     int64_t ldo;
+    int accumulate;         // out += instead of out =
 };
 
 // byte offset of the 16 B unit j of row r in a 256-row SWIZZLE_64B image
@@ -289,8 +290,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     float* op = p.out + row_base * p.ldo + col;
                     const int nrow = (int)(p.m - row_base < 32 ? p.m - row_base : 32);
                     if (col_ok) {
+                        if (!p.accumulate) {
 #pragma unroll 4
-                        for (int i = 0; i < nrow; ++i) op[(int64_t)i * p.ldo] = st[i * 33 + lane] + b;
+                            for (int i = 0; i < nrow; ++i) op[(int64_t)i * p.ldo] = st[i * 33 + lane] + b;
+                        } else {
+#pragma unroll 4
+                            for (int i = 0; i < nrow; ++i) op[(int64_t)i * p.ldo] += st[i * 33 + lane] + b;
+                        }
                     }
                 }
             }
@@ -370,7 +376,7 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
     SG_CHECK_LAUNCH();
 
     p.kct = kct; p.m = a->m; p.n = (int)a->n; p.n_tiles = n_tiles; p.wimg = img; p.bias = a->bias;
-    p.out = a->out; p.ldo = a->ldo;
+    p.out = a->out; p.ldo = a->ldo; p.accumulate = a->accumulate != 0;
     // Tile shape (measured, scripts/lin_bench.py, M = 169,343): 128-row tiles with the double-buffered
     // accumulator win 10-17 % while the split weight image is small (N=256, K<=512: 114 / 196 us
     // against 136 / 218 us); once it reaches a few MB (N=512, K=1024: 4 MB) streaming it twice as

@@ -29,11 +29,34 @@ def _rowmajor(t):
     return t
 
 
+K_SLAB = 512       # columns accumulated in TMEM per call once a product is cut into slabs
+K_SINGLE = 768     # widest product done in one call (measured max error 7.5e-9 * K of the output scale)
+
+
 def linear_raw(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
                bias: Optional[torch.Tensor] = None, w_transposed: bool = False,
-               out: Optional[torch.Tensor] = None) -> torch.Tensor:
+               out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
     """out[m, n] = sum_s srcs[s][m, :] . weights[s][n, :] (+ bias[n]); with w_transposed the
-    weights are [k, n] and the product is srcs[s] @ weights[s].  One stemgnn_linear call."""
+    weights are [k, n] and the product is srcs[s] @ weights[s].  One stemgnn_linear call while
+    sum(k) <= K_SINGLE; wider products are cut into column slabs of K_SLAB whose partial products are
+    added round-to-nearest by the epilogue (accumulate), keeping the 1e-5 bound."""
+    if sum(int(a.size(1)) for a in srcs) > K_SINGLE:
+        pieces = []
+        for a, w in zip(srcs, weights):
+            for lo in range(0, a.size(1), K_SLAB):
+                hi = min(a.size(1), lo + K_SLAB)
+                pieces.append((a[:, lo:hi], w[lo:hi] if w_transposed else w[:, lo:hi]))
+        calls, cur, cur_k = [], [], 0
+        for pc in pieces:                       # at most two sources and K_SLAB columns per call
+            k = pc[0].size(1)
+            if cur and (len(cur) == 2 or cur_k + k > K_SLAB):
+                calls.append(cur); cur, cur_k = [], 0
+            cur.append(pc); cur_k += k
+        calls.append(cur)
+        for i, grp in enumerate(calls):
+            out = linear_raw([g[0] for g in grp], [g[1] for g in grp], bias if i == 0 else None,
+                             w_transposed, out, accumulate or i > 0)
+        return out
     ns = len(srcs)
     if ns not in (1, 2) or len(weights) != ns:
         raise ValueError("one or two (source, weight) pairs")
@@ -57,6 +80,7 @@ def linear_raw(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
         a.w[s], a.ldw[s] = weights[s].data_ptr(), weights[s].stride(0)
     a.bias = _lib.ptr(_check(bias, "bias").contiguous()) if bias is not None else None
     a.out, a.ldo = out.data_ptr(), out.stride(0)
+    a.accumulate = int(accumulate)
     L = _lib.lib()
     need = C.c_size_t(0)
     _lib.check(L.stemgnn_linear_workspace(C.byref(a), C.byref(need)))

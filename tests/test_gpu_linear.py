@@ -180,3 +180,24 @@ def test_linear_large_m():
     ref = a[idx].double() @ w.double().t()
     assert _rel_err(out[idx], ref) < 1e-5
     assert _rel_err(out[-300:], a[-300:].double() @ w.double().t()) < 1e-5
+
+
+@pytest.mark.parametrize("ks", [(4096,), (1024, 1024), (768, 520)])
+def test_wide_products_are_slabbed_and_hold_the_bound(ks):
+    g = torch.Generator().manual_seed(sum(ks))
+    m, n = 3000, 256
+    srcs = [torch.randn(m, k, generator=g).to(DEV) for k in ks]
+    ws = [(torch.randn(n, k, generator=g) / k ** 0.5).to(DEV) for k in ks]
+    bias = torch.randn(n, generator=g).to(DEV)
+    out = S.linear_raw(srcs, ws, bias)
+    ref = sum(a.double() @ w.double().t() for a, w in zip(srcs, ws)) + bias.double()
+    assert _rel_err(out, ref) < 1e-5
+    # positive operands: the truncation bias adds up coherently -- the hard case
+    srcs = [t.abs() for t in srcs]; ws = [t.abs() for t in ws]
+    out = S.linear_raw(srcs, ws, None)
+    ref = sum(a.double() @ w.double().t() for a, w in zip(srcs, ws))
+    assert ((out.double() - ref) / ref).abs().max().item() < 1e-5
+    # transposed weights take the same path
+    wt = [w.t().contiguous() for w in ws]
+    out_t = S.linear_raw(srcs, wt, None, w_transposed=True)
+    assert torch.equal(out_t, out)
