@@ -214,7 +214,7 @@ int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* args_host, void* works
  *   stemgnn_bn_act_backward sum_g[c] = sum_r g, sum_gx[c] = sum_r g * xhat (= grad of beta, gamma) with
  *                           g = g_y * mask/(1-p) * [pre > 0];  gx = gamma * invstd * (g - sum_g/N -
  *                           xhat * sum_gx/N) when batch_stats, gamma * invstd * g otherwise
- * The dropout mask is Philox4x32-10 keyed by *seed (a uint64 in DEVICE memory, read at kernel time,
+ * The dropout mask is Philox4x32-7 keyed by *seed (a uint64 in DEVICE memory, read at kernel time,
  * so a captured CUDA graph sees a fresh seed on every replay) and the element index: it is recomputed
  * in the backward, never stored.  relu / p = 0 switch the activation / dropout off. */
 int stemgnn_bn_workspace(int64_t rows, int64_t feat, size_t* bytes_host);

@@ -29,8 +29,12 @@ __global__ void vq_sqnorm_kernel(const float* v, int64_t rows, int64_t heads, in
                                  int64_t row_stride, int64_t head_stride, float* out);
 __global__ void vq_scan_kernel(VqView q, const float* x2, const float* e2, const int32_t* row_list,
                                const int32_t* row_count, int32_t* best_out);
-__global__ void vq_gather_kernel(VqView q, const int32_t* best, const int32_t* cand, const float* e2,
-                                 double* partials, unsigned long long* stats);
+__global__ void vq_gather_kernel(VqView q, int32_t* best, const int32_t* cand, const float* e2,
+                                 double* partials, int32_t* open_list, int32_t* open_count,
+                                 unsigned long long* stats);
+__global__ void vq_rescan_kernel(VqView q, int32_t* best, const float* e2, double* partials, int nblk,
+                                 const int32_t* open_list, const int32_t* open_count,
+                                 unsigned long long* stats);
 constexpr int VQ_CAND_CAP = 8;   // candidate slots per row written by the tcgen05 path
 __global__ void vq_sqerr_reduce_kernel(const double* partials, int nblk, double* sq_err);
 

@@ -44,6 +44,8 @@ size_t base_bytes(const VqView& q, const VqPlan& p) {
     b += align_up((size_t)q.embed_heads * q.K * 4, 256);             // e2
     b += align_up((size_t)p.items * 4, 256);                         // best
     b += align_up((size_t)q.heads * (size_t)(p.nblk > 0 ? p.nblk : 1) * 8, 256);  // partials
+    b += align_up((size_t)q.heads * (size_t)(p.nblk > 0 ? p.nblk : 1) * 4, 256);  // open_list
+    b += 256;                                                                      // open_count
     return b;
 }
 }  // namespace
@@ -89,6 +91,9 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
     float* e2 = ws.take<float>((size_t)q.embed_heads * q.K);
     int32_t* best = ws.take<int32_t>(p.items);
     double* partials = ws.take<double>((size_t)q.heads * p.nblk);
+    int32_t* open_list = ws.take<int32_t>((size_t)q.heads * p.nblk);
+    int32_t* open_count = ws.take<int32_t>(1);
+    cudaMemsetAsync(open_count, 0, 4, stream);
 
     const int64_t ek = q.embed_heads * (int64_t)q.K;
     SG_LAUNCH(vq_sqnorm_kernel<<<(unsigned)((ek * 32 + 255) / 256), 256, 0, stream>>>(
@@ -106,8 +111,12 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
     }
     dim3 ggrid((unsigned)p.nblk, (unsigned)q.heads);
     SG_LAUNCH(vq_gather_kernel<<<ggrid, 256, 0, stream>>>(
-        q, best, cand, e2, a->sq_err ? partials : nullptr,
+        q, best, cand, e2, a->sq_err ? partials : nullptr, open_list, open_count,
         reinterpret_cast<unsigned long long*>(a->stats)));
+    if (p.path == 2)      // rows the tensor-core search left to the exact scan (normally a handful)
+        SG_LAUNCH(vq_rescan_kernel<<<(unsigned)sm_count(), 1024, 0, stream>>>(
+            q, best, e2, a->sq_err ? partials : nullptr, (int)p.nblk, open_list, open_count,
+            reinterpret_cast<unsigned long long*>(a->stats)));
     if (a->sq_err)
         SG_LAUNCH(vq_sqerr_reduce_kernel<<<(unsigned)q.heads, 256, 0, stream>>>(partials, (int)p.nblk, a->sq_err));
     SG_CHECK_LAUNCH();

@@ -133,9 +133,12 @@ vq_scan_kernel(VqView q, const float* __restrict__ x2, const float* __restrict__
 // ---- gather + commitment partial: one warp per (head,row) --------------------------------------
 // quantize(h,m,:) = embed[eh, best, :]; ind(h,m) = best; partials[h*nblk + blockIdx.x] = sum (q-x)^2
 // over this CTA's rows, reduced in a fixed order (shuffle tree, then warps in index order).
-// Rows the tcgen05 path left open are settled here first, while the warp holds the row anyway:
+// Rows the tcgen05 path left open are settled first, while the warp holds the row anyway:
 // best == -1: re-score the row's candidate list (cand[flat][0..CAP), -1 padded) with the
-// reference's fp32 formula; best == -2: exact scan over all K codes.  First index wins ties.
+// reference's fp32 formula, first index winning ties.  Rows that need the exact scan over all K
+// codes (best == -2) are NOT scanned here -- one such row would hold its CTA for K dot products
+// (430 us at K=16384, D=256: the kernel's tail) -- the CTA appends itself to open_list and
+// vq_rescan_kernel spreads those rows over the whole GPU.
 __device__ __forceinline__ float warp_dot(const float* __restrict__ a, const float* __restrict__ b,
                                           int D, bool vec4, int lane) {
     float s = 0.f;
@@ -153,14 +156,90 @@ __device__ __forceinline__ float warp_dot(const float* __restrict__ a, const flo
     return s;
 }
 
+// G dot products of one row against G consecutive codes, each summed in warp_dot's order (so a
+// (row, code) pair scores the same wherever it is evaluated); x is loaded once, the G code rows
+// are G independent loads in flight.
+template <int G>
+__device__ __forceinline__ void warp_dot_group(const float* __restrict__ a, const float* __restrict__ b,
+                                               int D, int ncodes, bool vec4, int lane, float (&out)[G]) {
+    float s[G];
+#pragma unroll
+    for (int i = 0; i < G; ++i) s[i] = 0.f;
+    if (vec4) {
+        for (int d = lane * 4; d < D; d += 128) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(a + d));
+            float4 w[G];
+#pragma unroll
+            for (int i = 0; i < G; ++i)
+                w[i] = i < ncodes ? __ldg(reinterpret_cast<const float4*>(b + (int64_t)i * D + d))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < G; ++i) {
+                s[i] = fmaf(u.x, w[i].x, s[i]); s[i] = fmaf(u.y, w[i].y, s[i]);
+                s[i] = fmaf(u.z, w[i].z, s[i]); s[i] = fmaf(u.w, w[i].w, s[i]);
+            }
+        }
+    } else {
+        for (int d = lane; d < D; d += 32) {
+            const float u = __ldg(a + d);
+#pragma unroll
+            for (int i = 0; i < G; ++i)
+                if (i < ncodes) s[i] = fmaf(u, __ldg(b + (int64_t)i * D + d), s[i]);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < G; ++i) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s[i] += __shfl_xor_sync(0xffffffffu, s[i], o);
+        out[i] = s[i];
+    }
+}
+
+// quantize row <- code row, returns this lane's share of |code - x|^2 (the warp sums it)
+__device__ __forceinline__ float gather_row(const float* __restrict__ xp, const float* __restrict__ e,
+                                            float* __restrict__ qp, int D, int lane) {
+    float s = 0.f;
+    const bool vec4 = (D & 3) == 0 &&
+                      ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(e) |
+                        reinterpret_cast<uintptr_t>(qp)) & 15) == 0;
+    if (vec4) {
+        // two 16-byte loads of each operand in flight per lane (D = 256: the whole row)
+        for (int d = lane * 4; d < D; d += 256) {
+            const bool two = d + 128 < D;
+            const float4 e0 = __ldg(reinterpret_cast<const float4*>(e + d));
+            const float4 x0 = __ldg(reinterpret_cast<const float4*>(xp + d));
+            float4 e1 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = e1;
+            if (two) {
+                e1 = __ldg(reinterpret_cast<const float4*>(e + d + 128));
+                x1 = __ldg(reinterpret_cast<const float4*>(xp + d + 128));
+            }
+            float df;
+            df = e0.x - x0.x; s = fmaf(df, df, s); df = e0.y - x0.y; s = fmaf(df, df, s);
+            df = e0.z - x0.z; s = fmaf(df, df, s); df = e0.w - x0.w; s = fmaf(df, df, s);
+            df = e1.x - x1.x; s = fmaf(df, df, s); df = e1.y - x1.y; s = fmaf(df, df, s);
+            df = e1.z - x1.z; s = fmaf(df, df, s); df = e1.w - x1.w; s = fmaf(df, df, s);
+            if (qp) {
+                *reinterpret_cast<float4*>(qp + d) = e0;
+                if (two) *reinterpret_cast<float4*>(qp + d + 128) = e1;
+            }
+        }
+    } else {
+        for (int d = lane; d < D; d += 32) {
+            const float ev = __ldg(e + d);
+            const float df = ev - __ldg(xp + d);
+            s = fmaf(df, df, s);
+            if (qp) qp[d] = ev;
+        }
+    }
+    return s;
+}
+
 __global__ void __launch_bounds__(256)
-vq_gather_kernel(VqView q, const int32_t* __restrict__ best, const int32_t* __restrict__ cand,
+vq_gather_kernel(VqView q, int32_t* __restrict__ best, const int32_t* __restrict__ cand,
                  const float* __restrict__ e2, double* __restrict__ partials,
+                 int32_t* __restrict__ open_list, int32_t* __restrict__ open_count,
                  unsigned long long* __restrict__ stats) {
     __shared__ double wsum[8];
-    __shared__ int s_b[8];          // per-warp decision: code, or -2 = needs the exact scan
-    __shared__ float s_bs[8];
-    __shared__ int s_bi[8];
     const int w = threadIdx.x >> 5, lane = lane_id();
     const int64_t h = blockIdx.y;
     const int64_t m = (int64_t)blockIdx.x * 8 + w;
@@ -168,11 +247,12 @@ vq_gather_kernel(VqView q, const int32_t* __restrict__ best, const int32_t* __re
     const float* E = q.embed + eh * (int64_t)q.K * q.D;
     const float* e2h = e2 + eh * (int64_t)q.K;
     int b = 0;
+    double part = 0.0;
     if (m < q.rows) {
         const int64_t flat = h * q.rows + m;
+        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
         b = best[flat];
         if (b == -1) {
-            const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
             const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
             const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
             float bs = -INFINITY;
@@ -185,52 +265,17 @@ vq_gather_kernel(VqView q, const int32_t* __restrict__ best, const int32_t* __re
             }
             if (lane == 0 && stats) atomicAdd(stats + 0, 1ull);
             b = bi < q.K ? bi : -2;
+            if (b == -2 && lane == 0) best[flat] = -2;      // NaN scores: the exact scan decides
+        }
+        if (b >= 0) {
+            float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
+            part = (double)gather_row(xp, E + (int64_t)b * q.D, qp, q.D, lane);
+            if (lane == 0 && q.ind) q.ind[m * q.ind_row_stride + h * q.ind_head_stride] = (int64_t)b;
         }
     }
-    if (lane == 0) s_b[w] = b;
-    __syncthreads();
-    // exact scan of the rows left open (-2), the whole CTA on one row at a time: warp w takes the
-    // codes w, w+8, ...; first index wins ties.  Normally no row gets here.
-    for (int r = 0; r < 8; ++r) {
-        if (s_b[r] != -2) continue;                       // CTA-uniform
-        const int64_t mr = (int64_t)blockIdx.x * 8 + r;
-        const float* xp = q.x + mr * q.x_row_stride + h * q.x_head_stride;
-        const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
-        const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
-        float bs = -INFINITY;
-        int bi = 0x7fffffff;
-        for (int c = w; c < q.K; c += 8) {
-            const float s = vq_score(q.metric, x2, e2h[c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
-            if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
-        }
-        if (lane == 0) { s_bs[w] = bs; s_bi[w] = bi; }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            float fs = s_bs[0];
-            int fi = s_bi[0];
-            for (int k = 1; k < 8; ++k)
-                if (s_bs[k] > fs || (s_bs[k] == fs && s_bi[k] < fi)) { fs = s_bs[k]; fi = s_bi[k]; }
-            s_b[r] = fi < q.K ? fi : 0;                   // all-NaN rows: argmax of NaNs is index 0
-            if (stats) atomicAdd(stats + 1, 1ull);
-        }
-        __syncthreads();
-    }
-    double part = 0.0;
-    if (m < q.rows) {
-        b = s_b[w];
-        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
-        const float* e = E + (int64_t)b * q.D;
-        float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
-        float s = 0.f;
-        for (int d = lane; d < q.D; d += 32) {
-            float ev = __ldg(e + d);
-            float df = ev - __ldg(xp + d);
-            s = fmaf(df, df, s);
-            if (qp) qp[d] = ev;
-        }
-        part = (double)s;
-        if (lane == 0 && q.ind) q.ind[m * q.ind_row_stride + h * q.ind_head_stride] = (int64_t)b;
-    }
+    const int any_open = __syncthreads_or(b == -2);
+    if (any_open && threadIdx.x == 0)
+        open_list[atomicAdd(open_count, 1)] = (int32_t)(h * gridDim.x + blockIdx.x);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
     if (lane == 0) wsum[w] = part;
@@ -240,6 +285,79 @@ vq_gather_kernel(VqView q, const int32_t* __restrict__ best, const int32_t* __re
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += wsum[i];
         partials[h * gridDim.x + blockIdx.x] = t;
+    }
+}
+
+// ---- exact scan of the rows left open: one CTA per row at a time, over the whole GPU ----------
+// An entry of open_list is a gather CTA (8 consecutive rows of one head) with at least one row at
+// best == -2.  A CTA of 32 warps scans all K codes for each such row (warp w takes the groups of
+// eight codes w, w+32, ...: the scan is bound by L2 latency, so 256 code rows are in flight per
+// SM; first index wins ties; an all-NaN row takes index 0 like argmax does), writes the row's
+// index / quantize row and adds its squared error to the gather CTA's partial -- rows in index
+// order, no atomics, so the commitment sum stays deterministic.
+constexpr int RS_WARPS = 32, RS_GROUP = 8;
+
+__global__ void __launch_bounds__(RS_WARPS * 32)
+vq_rescan_kernel(VqView q, int32_t* __restrict__ best, const float* __restrict__ e2,
+                 double* __restrict__ partials, int nblk, const int32_t* __restrict__ open_list,
+                 const int32_t* __restrict__ open_count, unsigned long long* __restrict__ stats) {
+    __shared__ float s_bs[RS_WARPS];
+    __shared__ int s_bi[RS_WARPS];
+    __shared__ int s_pick;
+    const int w = threadIdx.x >> 5, lane = lane_id();
+    const int n_open = *open_count;
+    for (int entry = blockIdx.x; entry < n_open; entry += gridDim.x) {
+        const int blk = open_list[entry];
+        const int64_t h = blk / nblk, bx = blk - h * nblk;
+        const int64_t eh = q.embed_heads == 1 ? 0 : h;
+        const float* E = q.embed + eh * (int64_t)q.K * q.D;
+        const float* e2h = e2 + eh * (int64_t)q.K;
+        double extra = 0.0;
+        for (int r = 0; r < 8; ++r) {
+            const int64_t m = bx * 8 + r;
+            if (m >= q.rows) break;
+            const int64_t flat = h * q.rows + m;
+            if (best[flat] != -2) continue;                   // CTA-uniform
+            const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
+            const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
+            const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
+            float bs = -INFINITY;
+            int bi = 0x7fffffff;
+            for (int c0 = w * RS_GROUP; c0 < q.K; c0 += RS_WARPS * RS_GROUP) {
+                const int nc = q.K - c0 < RS_GROUP ? q.K - c0 : RS_GROUP;
+                float dot[RS_GROUP];
+                warp_dot_group<RS_GROUP>(xp, E + (int64_t)c0 * q.D, q.D, nc, vec4, lane, dot);
+#pragma unroll
+                for (int i = 0; i < RS_GROUP; ++i) {
+                    if (i >= nc) break;
+                    const float s = vq_score(q.metric, x2, e2h[c0 + i], dot[i]);
+                    if (s > bs || (s == bs && c0 + i < bi)) { bs = s; bi = c0 + i; }
+                }
+            }
+            if (lane == 0) { s_bs[w] = bs; s_bi[w] = bi; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                float fs = s_bs[0];
+                int fi = s_bi[0];
+                for (int k = 1; k < RS_WARPS; ++k)
+                    if (s_bs[k] > fs || (s_bs[k] == fs && s_bi[k] < fi)) { fs = s_bs[k]; fi = s_bi[k]; }
+                s_pick = fi < q.K ? fi : 0;
+                best[flat] = s_pick;
+                if (stats) atomicAdd(stats + 1, 1ull);
+            }
+            __syncthreads();
+            if (w == 0) {
+                const int pick = s_pick;
+                float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
+                double part = (double)gather_row(xp, E + (int64_t)pick * q.D, qp, q.D, lane);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+                extra += part;
+                if (lane == 0 && q.ind) q.ind[m * q.ind_row_stride + h * q.ind_head_stride] = (int64_t)pick;
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0 && partials) partials[blk] += extra;
     }
 }
 

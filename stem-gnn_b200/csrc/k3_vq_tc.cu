@@ -31,6 +31,8 @@
 // FLOPs: 2*N*K*D on the tensor pipe; HBM: N*D*4 B (x) + N*4 B (best).
 #include <cuda_fp16.h>
 
+#include <cstdlib>
+
 #include "k3_vq_common.cuh"
 #include "tc_ptx.cuh"
 
@@ -49,9 +51,9 @@ constexpr int PROD_WARP0 = 8, LOAD_WARP = 16, MMA_WARP = 17;
 constexpr int MAX_AS = 20;                 // A chunk slots (resident: kcn * 1|2 buffers; ring: 4)
 constexpr int MAX_SB = 6;
 constexpr int MERGE_WORDS = 8;             // per-row state handed from the odd-chunk warp to its partner
-// ne2 slices [8][256] f32, band ring [4][128] f32, group-1 partials [128] float2, merge [128][12],
+// ne2 ring [4][256] f32, band ring [4][128] f32, group-1 partials [128] float2, merge [128][12],
 // barriers, tmem slot
-constexpr int SMEM_EXTRA = EPI_WARPS * BN * 4 + 4 * BM * 4 + BM * 8 + BM * MERGE_WORDS * 4 + 80 * 8 + 16;
+constexpr int SMEM_EXTRA = 4 * BN * 4 + 4 * BM * 4 + BM * 8 + BM * MERGE_WORDS * 4 + 80 * 8 + 16;
 constexpr int SMEM_MAX = 232448;           // 227 KB opt-in limit per CTA
 
 using namespace tcptx;
@@ -63,7 +65,8 @@ struct TcParams {
     int K, D;
     int n_tiles, kcn;                // code tiles of 256, 64-column chunks
     int sb;                          // B ring stages
-    int a_slots;                     // A chunk slots: kcn * buffers (resident) or ring stages
+    int a_slots;                     // A chunk slots: kcn << a_dbl (resident) or a ring of 4
+    int a_dbl;                       // resident mode: 1 = two A buffers (row tiles alternate)
     const __half* img;               // [embed_heads][n_tiles][kcn][256 x 64] swizzled tile images
     const float* ne2;                // [embed_heads][n_tiles*256]: -e2/2 | 0, padded with -inf
     const uint32_t* head_stats;      // [embed_heads][4] float bits: max|e|, max e2, max |e - e~|^2, S
@@ -90,12 +93,20 @@ __device__ __forceinline__ float transpose_reduce4(const float (&a)[4], int j) {
 }
 
 // ---------------------------------------------------------------------------------- kernel
-// A chunk sequence number: resident mode fills every chunk once per row tile, ring mode once per
-// (row tile, code tile).  slot = seq % a_slots, phase = (seq / a_slots) & 1.
+// Slot and mbarrier phase of an A chunk.  Resident mode fills every chunk once per row tile
+// (slots kcn << a_dbl, row tiles alternate between the two buffers); ring mode once per (row tile,
+// code tile) through 4 slots, ring_seq counting this CTA's chunks.  No divisions: these run once
+// per chunk in the single-thread MMA loop.
 template <bool RESIDENT>
-__device__ __forceinline__ uint32_t a_seq(const TcParams& p, uint32_t tile_it, int n, int kc) {
-    return RESIDENT ? tile_it * (uint32_t)p.kcn + (uint32_t)kc
-                    : (tile_it * (uint32_t)p.n_tiles + (uint32_t)n) * (uint32_t)p.kcn + (uint32_t)kc;
+__device__ __forceinline__ void a_slot(const TcParams& p, uint32_t tile_it, uint32_t ring_seq, int kc,
+                                       uint32_t& slot, uint32_t& phase) {
+    if (RESIDENT) {
+        slot = (tile_it & (uint32_t)p.a_dbl) * (uint32_t)p.kcn + (uint32_t)kc;
+        phase = (tile_it >> p.a_dbl) & 1u;
+    } else {
+        slot = ring_seq & 3u;
+        phase = (ring_seq >> 2) & 1u;
+    }
 }
 
 template <bool RESIDENT>
@@ -103,8 +114,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sA = smem;
     uint8_t* sB = sA + (size_t)p.a_slots * A_CHUNK_BYTES;
-    float* s_ne2 = reinterpret_cast<float*>(sB + (size_t)p.sb * B_STAGE_BYTES);   // [8][256]
-    float* s_band = s_ne2 + EPI_WARPS * BN;                                        // [4][128]
+    float* s_ne2 = reinterpret_cast<float*>(sB + (size_t)p.sb * B_STAGE_BYTES);   // [4][256]
+    float* s_band = s_ne2 + 4 * BN;                                        // [4][128]
     float2* s_part = reinterpret_cast<float2*>(s_band + 4 * BM);                   // [128]
     float* s_merge = reinterpret_cast<float*>(s_part + BM);                        // [128][12]
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_merge + BM * MERGE_WORDS);
@@ -119,7 +130,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     uint64_t* part_empty = part_full + 1;    // [1]
     uint64_t* merge_full = part_empty + 1;   // [1]
     uint64_t* merge_empty = merge_full + 1;  // [1]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(merge_empty + 1);
+    uint64_t* ne2_full = merge_empty + 1;    // [4]
+    uint64_t* ne2_empty = ne2_full + 4;      // [4]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(ne2_empty + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t row_tiles = (p.rows + BM - 1) / BM;
@@ -131,6 +144,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
         for (int i = 0; i < MAX_SB; ++i) { mbar_init(smem_u32(b_full + i), 1); mbar_init(smem_u32(b_empty + i), 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(t_full + i), 1); mbar_init(smem_u32(t_empty + i), EPI_WARPS * 32); }
         for (int i = 0; i < 4; ++i) mbar_init(smem_u32(band_full + i), BM);
+        for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(ne2_full + i), 1); mbar_init(smem_u32(ne2_empty + i), EPI_WARPS * 32); }
         mbar_init(smem_u32(part_full), BM);
         mbar_init(smem_u32(part_empty), BM);
         mbar_init(smem_u32(merge_full), BM);
@@ -146,55 +160,71 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     if (warp == LOAD_WARP) {
         // ================= codebook loader: bulk async copies into the B ring =================
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t s = 0, ph = 0, acc = 0;      // B ring stage / phase carried, not recomputed
             for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
                 const int64_t h = item / row_tiles;
                 const int64_t eh = p.embed_heads == 1 ? 0 : h;
-                for (int n = 0; n < p.n_tiles; ++n) {
+                for (int n = 0; n < p.n_tiles; ++n, ++acc) {
+                    // the tile's -e2/2 slice for the epilogue: a ring of 4, two tiles ahead of TMEM
+                    const uint32_t ns = acc & 3u;
+                    mbar_wait(smem_u32(ne2_empty + ns), ((acc >> 2) & 1u) ^ 1u);
+                    mbar_expect_tx(smem_u32(ne2_full + ns), BN * 4);
+                    bulk_g2s(smem_u32(s_ne2 + ns * BN), p.ne2 + (eh * p.n_tiles + n) * (int64_t)BN, BN * 4,
+                             smem_u32(ne2_full + ns));
                     const uint32_t bytes = (uint32_t)tile_codes32(p, n) * 128u;
                     const uint8_t* src = reinterpret_cast<const uint8_t*>(p.img) +
                                          ((eh * p.n_tiles + n) * (int64_t)p.kcn) * B_STAGE_BYTES;
-                    for (int kc = 0; kc < p.kcn; ++kc, ++it) {
-                        const uint32_t s = it % (uint32_t)p.sb, ph = (it / (uint32_t)p.sb) & 1u;
+                    for (int kc = 0; kc < p.kcn; ++kc) {
                         mbar_wait(smem_u32(b_empty + s), ph ^ 1u);
                         mbar_expect_tx(smem_u32(b_full + s), bytes);
                         bulk_g2s(smem_u32(sB + (size_t)s * B_STAGE_BYTES), src + (size_t)kc * B_STAGE_BYTES,
                                  bytes, smem_u32(b_full + s));
+                        if (++s == (uint32_t)p.sb) { s = 0; ph ^= 1u; }
                     }
                 }
             }
         }
     } else if (warp == MMA_WARP) {
         // ================= MMA issuer: one thread drives the tensor core =================
-        if (lane == 0) {
-            uint32_t it_b = 0, acc_it = 0, tile_it = 0;
-            const int last_ksteps = ((p.D - (p.kcn - 1) * BK) + 15) / 16;
-            for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
-                for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
-                    const uint32_t idesc = make_idesc(BM, tile_codes32(p, n));
-                    const uint32_t st = acc_it & 1u;
-                    mbar_wait(smem_u32(t_empty + st), ((acc_it >> 1) & 1u) ^ 1u);
+        // The whole warp walks the loop -- warp-uniform control flow keeps descriptors and barrier
+        // addresses in uniform registers -- and one elected lane issues.  Ring positions are
+        // carried, not recomputed.  (The first version ran the loop in lane 0 only, with three
+        // integer divisions per chunk and a predicate loop around every UTCHMMA: 430 ns per
+        // 64-column chunk with the MMAs taken out, more than the 276 ns the four MMAs need, so the
+        // tensor pipe idled 59 % of the time whatever the ring depth or the epilogue did.)
+        uint32_t sb = 0, sb_ph = 0, acc_it = 0, tile_it = 0, ring_seq = 0;
+        const int last_ksteps = ((p.D - (p.kcn - 1) * BK) + 15) / 16;
+        const uint64_t a_desc0 = smem_desc_sw128(smem_u32(sA)), b_desc0 = smem_desc_sw128(smem_u32(sB));
+        for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
+            for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
+                const uint32_t idesc = make_idesc(BM, tile_codes32(p, n));
+                const uint32_t st = acc_it & 1u;
+                mbar_wait(smem_u32(t_empty + st), ((acc_it >> 1) & 1u) ^ 1u);
+                const uint32_t d_tmem = tmem_base + st * BN;
+                const bool last_n = n == p.n_tiles - 1;
+                for (int kc = 0; kc < p.kcn; ++kc, ++ring_seq) {
+                    uint32_t sa, a_ph;
+                    a_slot<RESIDENT>(p, tile_it, ring_seq, kc, sa, a_ph);
+                    if (!RESIDENT || n == 0) mbar_wait(smem_u32(a_full + sa), a_ph);
+                    mbar_wait(smem_u32(b_full + sb), sb_ph);
                     tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + st * BN;
-                    for (int kc = 0; kc < p.kcn; ++kc, ++it_b) {
-                        const uint32_t sb = it_b % (uint32_t)p.sb;
-                        const uint32_t seq = a_seq<RESIDENT>(p, tile_it, n, kc);
-                        const uint32_t sa = seq % (uint32_t)p.a_slots;
-                        if (!RESIDENT || n == 0)
-                            mbar_wait(smem_u32(a_full + sa), (seq / (uint32_t)p.a_slots) & 1u);
-                        mbar_wait(smem_u32(b_full + sb), (it_b / (uint32_t)p.sb) & 1u);
-                        tc_fence_after();
-                        const uint64_t a_desc = smem_desc_sw128(smem_u32(sA + (size_t)sa * A_CHUNK_BYTES));
-                        const uint64_t b_desc = smem_desc_sw128(smem_u32(sB + (size_t)sb * B_STAGE_BYTES));
-                        const int ksteps = kc == p.kcn - 1 ? last_ksteps : BK / 16;
-                        for (int k = 0; k < ksteps; ++k)   // +32 B along K inside the swizzle row
-                            umma_f16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                                     (uint32_t)((kc | k) != 0));
+                    // the start-address field holds addr >> 4 (14 bits, no carry below 256 KB)
+                    const uint64_t a_desc = a_desc0 + (uint64_t)(sa * (uint32_t)(A_CHUNK_BYTES >> 4));
+                    const uint64_t b_desc = b_desc0 + (uint64_t)(sb * (uint32_t)(B_STAGE_BYTES >> 4));
+                    const int ksteps = kc == p.kcn - 1 ? last_ksteps : BK / 16;
+                    if (elect_one()) {
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k)   // +32 B along K inside the swizzle row
+                            if (k < ksteps)
+                                umma_f16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                         (uint32_t)((kc | k) != 0));
                         umma_commit(smem_u32(b_empty + sb));
                         // the A chunk is free once the last code tile that reads it has consumed it
-                        if (!RESIDENT || n == p.n_tiles - 1) umma_commit(smem_u32(a_empty + sa));
+                        if (!RESIDENT || last_n) umma_commit(smem_u32(a_empty + sa));
+                        if (kc == p.kcn - 1) umma_commit(smem_u32(t_full + st));
                     }
-                    umma_commit(smem_u32(t_full + st));
+                    __syncwarp();
+                    if (++sb == (uint32_t)p.sb) { sb = 0; sb_ph ^= 1u; }
                 }
             }
         }
@@ -211,7 +241,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
 #pragma unroll
         for (int k = 0; k < 4; ++k)
             soff[k] = (uint32_t)((rr >> 3) * 1024 + (rr & 7) * 128 + (((((j + 4 * k) >> 1)) ^ (rr & 7)) << 4) + (j & 1) * 8);
-        uint32_t tile_it = 0;
+        uint32_t tile_it = 0, ring_base = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int64_t h = item / row_tiles, mt = item - h * row_tiles;
             const int64_t eh = p.embed_heads == 1 ? 0 : h;
@@ -225,9 +255,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
             for (int n = 0; n < n_pass; ++n) {
 #pragma unroll 1
                 for (int kc = grp; kc < p.kcn; kc += 2) {
-                    const uint32_t seq = a_seq<RESIDENT>(p, tile_it, n, kc);
-                    const uint32_t slot = seq % (uint32_t)p.a_slots;
-                    mbar_wait(smem_u32(a_empty + slot), ((seq / (uint32_t)p.a_slots) & 1u) ^ 1u);
+                    uint32_t slot, a_ph;
+                    a_slot<RESIDENT>(p, tile_it, ring_base + (uint32_t)kc, kc, slot, a_ph);
+                    mbar_wait(smem_u32(a_empty + slot), a_ph ^ 1u);
                     float4 v[4][4];
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
@@ -266,6 +296,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
                     fence_async_smem();
                     mbar_arrive(smem_u32(a_full + slot));
                 }
+                ring_base += (uint32_t)p.kcn;
                 if (n == 0) {
                     // lane j of the quad gets the totals of row rr + 32j over this group's chunks
                     const float s_g = transpose_reduce4(sq, j), r_g = transpose_reduce4(rq, j);
@@ -298,86 +329,90 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) vq_tc_kernel(const TcParams p)
     } else if (warp < EPI_WARPS) {
         // ================= epilogue: TMEM -> registers, running best + candidate band =================
         // One row per thread; warps w and w+4 share TMEM lane quarter w&3 and take alternate
-        // 32-column chunks (two warps per scheduler hide each other's latencies).  Every code tile
-        // is swept twice while it sits in TMEM: sweep 1 is a pure max (FFMA + FMNMX tree), sweep 2
-        // records -- branch-free, three index slots + a count -- the codes with score >= max - band.
-        // No values are kept: when a later tile beats the old best by more than the band the list
-        // is simply cleared, otherwise it stays a superset of the in-band codes, which is all the
-        // fp32 re-scoring needs.  More than three in-band codes -> exact re-scan of the row.
+        // 32-column chunks (two warps per scheduler hide each other's latencies).  Every chunk is
+        // read from TMEM once: FFMA + FMNMX tree for its max, then -- only when some row of the warp
+        // has a score within the band of its running best -- a branch-free pass that records the
+        // codes with score >= best - band in three index slots + a count.  No values are kept:
+        // when a later chunk beats the old best by more than the band the list is simply cleared,
+        // otherwise it stays a superset of the in-band codes, which is all the fp32 re-scoring
+        // needs.  More than three recorded codes -> exact re-scan of the row.  (The first version
+        // swept every tile twice with the TMEM load latency exposed: 3.6 us per 256-code tile
+        // whatever D was, i.e. the epilogue, not the tensor pipe, set the rate.)
         const int quarter = warp & 3, half = warp >> 2;
         const int row_in_tile = quarter * 32 + lane;
-        const uint32_t ne2s = smem_u32(s_ne2 + warp * BN);
         uint32_t acc_it = 0, tile_it = 0;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++tile_it) {
             const int64_t h = item / row_tiles, mt = item - h * row_tiles;
             const int64_t eh = p.embed_heads == 1 ? 0 : h;
             const int64_t m = mt * BM + row_in_tile;
-            const float* ne2g = p.ne2 + eh * (int64_t)p.n_tiles * BN;
             const float scale = __uint_as_float(__ldg(p.head_stats + eh * 4 + 3));
-            float rb = -INFINITY, thr = -INFINITY, band = 0.f;
+            float rb = -INFINITY, band = 0.f;
             int cnt = 0, p0 = -1, p1 = -1, p2 = -1;
+            // one 32-column chunk, already in registers: running best, and the codes within the
+            // band of it.  thr uses the best INCLUDING this chunk, so a code inside the final band
+            // is always recorded (the final best is >= every running best); the list is cleared
+            // when a chunk beats everything before it by more than the band.
+            auto sweep = [&](float (&v)[32], uint32_t ne2s, int c0, int n) {
+                float cm = -INFINITY;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const float4 na = lds128(ne2s + (uint32_t)(c0 + g * 8) * 4u);
+                    const float4 nb = lds128(ne2s + (uint32_t)(c0 + g * 8 + 4) * 4u);
+                    float* w = v + g * 8;
+                    w[0] = fmaf(w[0], scale, na.x); w[1] = fmaf(w[1], scale, na.y);
+                    w[2] = fmaf(w[2], scale, na.z); w[3] = fmaf(w[3], scale, na.w);
+                    w[4] = fmaf(w[4], scale, nb.x); w[5] = fmaf(w[5], scale, nb.y);
+                    w[6] = fmaf(w[6], scale, nb.z); w[7] = fmaf(w[7], scale, nb.w);
+                    cm = fmaxf(cm, fmaxf(fmaxf(fmaxf(w[0], w[1]), fmaxf(w[2], w[3])),
+                                         fmaxf(fmaxf(w[4], w[5]), fmaxf(w[6], w[7]))));
+                }
+                if (cm - band > rb) { cnt = 0; p0 = -1; p1 = -1; p2 = -1; }
+                rb = fmaxf(rb, cm);
+                const float thr = rb - band;
+                if (__any_sync(0xffffffffu, cm >= thr)) {
+                    const int base = n * BN + c0;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const bool hit = v[i] >= thr;
+                        p2 = hit ? p1 : p2;
+                        p1 = hit ? p0 : p1;
+                        p0 = hit ? base + i : p0;
+                        cnt += hit ? 1 : 0;
+                    }
+                }
+            };
 #pragma unroll 1
             for (int n = 0; n < p.n_tiles; ++n, ++acc_it) {
                 const int ncols = tile_codes32(p, n);
-                __syncwarp();
-#pragma unroll
-                for (int j = 0; j < BN / 32; ++j)
-                    s_ne2[warp * BN + j * 32 + lane] = __ldg(ne2g + n * BN + j * 32 + lane);
-                __syncwarp();
-                const uint32_t st = acc_it & 1u;
+                const uint32_t st = acc_it & 1u, ns = acc_it & 3u;
                 if (n == 0) {
                     mbar_wait(smem_u32(band_full + (tile_it & 3u)), (tile_it >> 2) & 1u);
                     band = s_band[(tile_it & 3u) * BM + row_in_tile];
                 }
+                mbar_wait(smem_u32(ne2_full + ns), (acc_it >> 2) & 1u);
+                const uint32_t ne2s = smem_u32(s_ne2 + ns * BN);
                 mbar_wait(smem_u32(t_full + st), (acc_it >> 1) & 1u);
                 tc_fence_after();
-                const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + st * BN;
-                float tmax = -INFINITY;
-                bool any_hit = true;
+                const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + st * BN + (uint32_t)(half * 32);
+                // this warp's chunks are columns half*32 + 64 i; the TMEM load of chunk i+1 is in
+                // flight while chunk i is swept (two register buffers)
+                const int nch = (ncols - half * 32 + 63) >> 6;
+                float va[32], vb[32];
+                if (nch > 0) tmem_ld32(t_addr, va);
 #pragma unroll 1
-                for (int pass = 0; pass < 2 && any_hit; ++pass) {
-#pragma unroll 1
-                    for (int c0 = half * 32; c0 < ncols; c0 += 64) {
-                        float v[32];
-                        tmem_ld32(t_addr + (uint32_t)c0, v);
+                for (int i = 0; i < nch; i += 2) {
+                    tmem_ld_wait();
+                    if (i + 1 < nch) tmem_ld32(t_addr + (uint32_t)((i + 1) * 64), vb);
+                    sweep(va, ne2s, half * 32 + i * 64, n);
+                    if (i + 1 < nch) {
                         tmem_ld_wait();
-                        float cm = -INFINITY;
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            const float4 na = lds128(ne2s + (uint32_t)(c0 + g * 8) * 4u);
-                            const float4 nb = lds128(ne2s + (uint32_t)(c0 + g * 8 + 4) * 4u);
-                            float* w = v + g * 8;
-                            w[0] = fmaf(w[0], scale, na.x); w[1] = fmaf(w[1], scale, na.y);
-                            w[2] = fmaf(w[2], scale, na.z); w[3] = fmaf(w[3], scale, na.w);
-                            w[4] = fmaf(w[4], scale, nb.x); w[5] = fmaf(w[5], scale, nb.y);
-                            w[6] = fmaf(w[6], scale, nb.z); w[7] = fmaf(w[7], scale, nb.w);
-                            cm = fmaxf(cm, fmaxf(fmaxf(fmaxf(w[0], w[1]), fmaxf(w[2], w[3])),
-                                                 fmaxf(fmaxf(w[4], w[5]), fmaxf(w[6], w[7]))));
-                        }
-                        if (pass == 0) {
-                            tmax = fmaxf(tmax, cm);
-                        } else if (__any_sync(0xffffffffu, cm >= thr)) {
-                            const int base = n * BN + c0;
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) {
-                                const bool hit = v[i] >= thr;
-                                p2 = hit ? p1 : p2;
-                                p1 = hit ? p0 : p1;
-                                p0 = hit ? base + i : p0;
-                                cnt += hit ? 1 : 0;
-                            }
-                        }
-                    }
-                    if (pass == 0) {
-                        // everything recorded so far drops out of the band when this tile wins clearly
-                        if (tmax - band > rb) { cnt = 0; p0 = -1; p1 = -1; p2 = -1; }
-                        rb = fmaxf(rb, tmax);
-                        thr = rb - band;
-                        any_hit = __any_sync(0xffffffffu, tmax >= thr);
+                        if (i + 2 < nch) tmem_ld32(t_addr + (uint32_t)((i + 2) * 64), va);
+                        sweep(vb, ne2s, half * 32 + (i + 1) * 64, n);
                     }
                 }
                 tc_fence_before();
                 mbar_arrive(smem_u32(t_empty + st));
+                mbar_arrive(smem_u32(ne2_empty + ns));
             }
             // ---- merge the two column halves of the row and publish
             float* mg = s_merge + row_in_tile * MERGE_WORDS;
@@ -516,7 +551,7 @@ __global__ void vq_tc_ne2_kernel(const float* __restrict__ embed, const float* _
 }
 
 struct Plan {
-    int n_tiles, kcn, sb, a_slots;
+    int n_tiles, kcn, sb, a_slots, a_dbl;
     bool resident;
     size_t smem, img_bytes, ne2_bytes;
 };
@@ -526,18 +561,26 @@ static bool make_plan(const VqView& q, Plan& pl) {
     pl.kcn = (q.D + BK - 1) / BK;
     const size_t avail = SMEM_MAX - SMEM_EXTRA;
     const size_t a_res = (size_t)pl.kcn * A_CHUNK_BYTES;
-    // the B ring needs as many stages as one code tile has chunks to keep a whole tile in
-    // flight, but never more than 4; at least 2
-    const size_t sb_want = pl.kcn >= 4 ? 4 : (pl.kcn >= 2 ? (size_t)pl.kcn : 2);
+    // The codebook stream is latency-bound: every 32 KB stage is a bulk copy out of L2 (~1-2 us
+    // under load) that feeds 4 MMAs (~0.3 us), so the ring wants as many stages as fit.  Measured at
+    // 1M x 16384: D=128 with 2 stages 568 TFLOP/s, D=256 with 2 stages + double-buffered A 735.
     pl.resident = a_res + 2 * (size_t)B_STAGE_BYTES <= avail;
     if (pl.resident) {
-        // second A buffer (next row tile loads under this tile's MMAs) when it still leaves >= 2 stages
-        const bool dbl = 2 * a_res + 2 * (size_t)B_STAGE_BYTES <= avail && 2 * pl.kcn <= MAX_AS;
+        const size_t sb1 = (avail - a_res) / B_STAGE_BYTES;
+        const size_t sb2 = 2 * a_res + 2 * (size_t)B_STAGE_BYTES <= avail && 2 * pl.kcn <= MAX_AS
+                               ? (avail - 2 * a_res) / B_STAGE_BYTES : 0;
+        // second A buffer (next row tile loads under this tile's MMAs): always when it still leaves
+        // 4 stages; with few code tiles per row tile (the reload is a large share) down to 2 stages
+        bool dbl = sb2 >= 4 || (sb2 >= 2 && pl.n_tiles < 8);
+        if (const char* ev = getenv("STEMGNN_VQ_DOUBLE_A")) dbl = sb2 >= 2 && atoi(ev) != 0;   // tuning knob
         pl.a_slots = pl.kcn * (dbl ? 2 : 1);
-        size_t sb = (avail - (size_t)pl.a_slots * A_CHUNK_BYTES) / B_STAGE_BYTES;
-        pl.sb = (int)(sb > sb_want ? sb_want : sb);
+        pl.a_dbl = dbl ? 1 : 0;
+        const size_t sb = dbl ? sb2 : sb1;
+        pl.sb = (int)(sb > (size_t)MAX_SB ? (size_t)MAX_SB : sb);
+        if (const char* ev = getenv("STEMGNN_VQ_STAGES")) pl.sb = atoi(ev) >= 2 && atoi(ev) < pl.sb ? atoi(ev) : pl.sb;
     } else {
         pl.a_slots = 4;
+        pl.a_dbl = 0;
         pl.sb = 4;
     }
     if (pl.a_slots > MAX_AS || pl.sb > MAX_SB || pl.sb < 2) return false;
@@ -609,7 +652,7 @@ int vq_assign_tc(const VqView& q, const float* e2, int32_t* best, int32_t** cand
     TcParams p;
     p.x = q.x; p.x_row_stride = q.x_row_stride; p.x_head_stride = q.x_head_stride;
     p.heads = q.heads; p.embed_heads = q.embed_heads; p.rows = q.rows;
-    p.K = q.K; p.D = q.D; p.n_tiles = pl.n_tiles; p.kcn = pl.kcn; p.sb = pl.sb; p.a_slots = pl.a_slots;
+    p.K = q.K; p.D = q.D; p.n_tiles = pl.n_tiles; p.kcn = pl.kcn; p.sb = pl.sb; p.a_slots = pl.a_slots; p.a_dbl = pl.a_dbl;
     p.img = img; p.ne2 = ne2; p.head_stats = head_stats;
     // fp32 accumulation of D exact fp16 x fp16 products (tensor core) and of the fp32 re-score
     // chain: <= D 2^-22 |x||e| together.  The Euclidean score adds the fp32 roundings of

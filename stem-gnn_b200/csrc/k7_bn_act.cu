@@ -5,7 +5,7 @@
 // STEM-GNN/model/encoder.py:313-317) and its autograd:
 //
 //   forward : column statistics (one read)  ->  y = drop(relu((x - mean) * invstd * gamma + beta))
-//             (one read, one write; the dropout mask is a counter-based Philox4x32-10 stream keyed
+//             (one read, one write; the dropout mask is a counter-based Philox4x32-7 stream keyed
 //              by a device-resident seed and the element index, so it is never stored)
 //   backward: g = g_y * mask/(1-p) * [pre > 0];  sums of g and g * xhat per column (reads g_y, x)
 //             ->  g_x = gamma * invstd * (g - sum_g/N - xhat * sum_gxhat/N)  (reads g_y, x, writes g_x)
@@ -21,9 +21,11 @@ struct Cols {                 // per-column constants, all [F]
     const float* mean; const float* invstd; const float* gamma; const float* beta;
 };
 
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+// Philox4x32 with 7 rounds (Random123's "crush-resistant" minimum; curand's default is 10): the
+// forward apply pass with dropout measured 83 us against 65 us without -- the rounds are visible
+__device__ __forceinline__ uint4 philox4x32_7(uint4 c, uint2 k) {
 #pragma unroll
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < 7; ++r) {
         const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
         const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
         c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
@@ -34,7 +36,7 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 
 // keep-mask scale factors of the 4 elements of float4 number `idx4`: 1/(1-p) or 0
 __device__ __forceinline__ float4 drop_scale4(uint64_t seed, int64_t idx4, float p, float inv_keep) {
-    const uint4 r = philox4x32_10(make_uint4((uint32_t)idx4, (uint32_t)((uint64_t)idx4 >> 32), 0u, 0u),
+    const uint4 r = philox4x32_7(make_uint4((uint32_t)idx4, (uint32_t)((uint64_t)idx4 >> 32), 0u, 0u),
                                   make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
     const float s = 1.f / 16777216.f;
     float4 m;
