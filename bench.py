@@ -580,6 +580,25 @@ def run_partitioned(args, w):
                              h2d_bytes_per_step=x_h.numel() * 4 * world, d2h_bytes_per_step=4 * world),
                     gpu_launches=launches, roofline=roof, kernels=kern, clocks=clocks)
         print(json.dumps(line), flush=True)
+    # optional A/B of the halo exchange on the same graph: STEMGNN_HALO_SWEEP="2:f32,4:f32,1:bf16"
+    # (feature slices : wire dtype); results go to stderr, the JSON line above stays the only stdout line
+    for item in filter(None, os.environ.get("STEMGNN_HALO_SWEEP", "").split(",")):
+        sl, dt = item.split(":")
+        pg.halo_slices, pg.halo_dtype = int(sl), (torch.bfloat16 if dt == "bf16" else None)
+        for _ in range(2):
+            step(x_d)
+        sync_all()
+        e0.record()
+        for _ in range(args.steps):
+            step(x_d)
+        e1.record()
+        sync_all()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(json.dumps(dict(sweep=item, n_gpus=world, ms_per_step=float(t[0]) / args.steps)),
+                  file=sys.stderr, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

@@ -166,8 +166,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
             }
         }
     } else if (warp == MMA_WARP) {
-        // ================= MMA issue: one elected thread =================
-        if (lane == 0) {
+        // ================= MMA issue =================
+        // The whole warp walks the loop (warp-uniform control flow: descriptors and barrier
+        // addresses stay in uniform registers, no per-instruction predicate loops); one elected
+        // lane issues the MMAs and commits.
+        {
             uint32_t seq = 0, item_it = 0;
             for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x, ++item_it) {
                 const int nt = (int)(item % p.n_tiles);
@@ -177,30 +180,32 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                 const uint32_t idesc = make_idesc_tf32(128, n_mma, 0, 0);
                 const uint32_t buf = item_it % NBUF;
                 mbar_wait(smem_u32(acc_empty + buf), ((item_it / NBUF) & 1u) ^ 1u);
-                tc_fence_after();
                 for (int c = 0; c < p.kct; ++c, ++seq) {
                     const uint32_t slot = seq % NS, ph = (seq / NS) & 1u;
                     mbar_wait(smem_u32(a_full + slot), ph);
                     mbar_wait(smem_u32(w_full + slot), ph);
                     tc_fence_after();
                     const uint32_t base = smem_u32(stages + slot * STAGE_BYTES);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int h = 0; h < MH; ++h) {
+                        for (int h = 0; h < MH; ++h) {
 #pragma unroll
-                        for (int ks = 0; ks < 2; ++ks) {
-                            const uint64_t a_hi = smem_desc_sw64(base + h * 8192 + ks * 32);
-                            const uint64_t a_lo = smem_desc_sw64(base + A_IMG + h * 8192 + ks * 32);
-                            const uint64_t w_hi = smem_desc_sw64(base + W_OFF + ks * 32);
-                            const uint64_t w_lo = smem_desc_sw64(base + W_OFF + IMG_BYTES + ks * 32);
-                            const uint32_t d = tmem_base + (uint32_t)(MH == 2 ? h : buf) * BN;
-                            umma_tf32(d, a_lo, w_hi, idesc, (c > 0 || ks > 0) ? 1u : 0u);
-                            umma_tf32(d, a_hi, w_lo, idesc, 1u);
-                            umma_tf32(d, a_hi, w_hi, idesc, 1u);
+                            for (int ks = 0; ks < 2; ++ks) {
+                                const uint64_t a_hi = smem_desc_sw64(base + h * 8192 + ks * 32);
+                                const uint64_t a_lo = smem_desc_sw64(base + A_IMG + h * 8192 + ks * 32);
+                                const uint64_t w_hi = smem_desc_sw64(base + W_OFF + ks * 32);
+                                const uint64_t w_lo = smem_desc_sw64(base + W_OFF + IMG_BYTES + ks * 32);
+                                const uint32_t d = tmem_base + (uint32_t)(MH == 2 ? h : buf) * BN;
+                                umma_tf32(d, a_lo, w_hi, idesc, (c > 0 || ks > 0) ? 1u : 0u);
+                                umma_tf32(d, a_hi, w_lo, idesc, 1u);
+                                umma_tf32(d, a_hi, w_hi, idesc, 1u);
+                            }
                         }
+                        umma_commit(smem_u32(empty + slot));
+                        if (c == p.kct - 1) umma_commit(smem_u32(acc_full + buf));
                     }
-                    umma_commit(smem_u32(empty + slot));
+                    __syncwarp();
                 }
-                umma_commit(smem_u32(acc_full + buf));
             }
         }
     } else if (warp >= PROD_WARP0 && warp < LOAD_WARP) {

@@ -212,8 +212,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(tile + (int64_t)(row_base + lane) * BT + i * 32));
             }
             if (warp == MMA_WARP) {
-                if (lane == 0) {
-                    // ---- MMA issue for this item (the previous epilogue has drained TMEM)
+                {
+                    // ---- MMA issue for this item (the previous epilogue has drained TMEM): the
+                    // whole warp walks the loop, one elected lane issues (uniform registers, no
+                    // per-instruction predicate loops)
                     const int64_t slab = item / combos;
                     int64_t rows = p.m - slab * p.slab;
                     rows = rows > p.slab ? p.slab : rows;
@@ -225,6 +227,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
                         mbar_wait(smem_u32(full + slot), (mma_seq / NS) & 1u);
                         tc_fence_after();
                         const uint32_t base = smem_u32(stages + slot * STAGE_BYTES);
+                        if (elect_one()) {
 #pragma unroll
                         for (int hh = 0; hh < 2; ++hh) {
 #pragma unroll
@@ -241,10 +244,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
                             }
                         }
                         umma_commit(smem_u32(empty + slot));
+                        if (c == n_st - 1) umma_commit(smem_u32(acc_full));
+                        }
+                        __syncwarp();
                     }
-                    umma_commit(smem_u32(acc_full));
                 }
-                __syncwarp();
             }
             mbar_wait(smem_u32(acc_full), item_it & 1u);
             tc_fence_after();
