@@ -255,6 +255,19 @@ int stemgnn_vq_ema_apply(const float* counts, const float* sums, int64_t embed_h
                          float* cluster_size, float* embed_avg, float* embed,
                          float* totals_scratch /* [embed_heads] */, stemgnn_stream_t stream);
 
+/* ------------------------------------------------------------------ K8: edge-wise inner product
+ * Replaces InnerProductDecoder.forward (STEM-GNN/model/encoder.py:353-366; called on the positive
+ * and the negative edges by model/pt_model.py:62-63):
+ *     out[e] = sum_d z[edge_index[0][e], d] * z[edge_index[1][e], d]      (then sigmoid if asked)
+ * edge_index is the reference's int64 [2, E] COO tensor (row 0 at edge_index, row 1 at
+ * edge_index + E); z has `feat` columns and row stride `ldz` floats.  The sum over d runs as an
+ * fma chain per lane and a fixed shuffle tree: deterministic, within fp32 rounding of torch's sum.
+ * An index outside [0, num_nodes) gives NaN for that edge (torch raises a device assert).
+ * The backward needs no entry point of its own: it is two stemgnn_aggregate(SUM) calls with
+ * edge_weight = upstream gradient (see stemgnn_b200/decoder.py). */
+int stemgnn_edge_dot(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes, int64_t feat,
+                     const float* z, int64_t ldz, int apply_sigmoid, float* out, stemgnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,6 +8,7 @@ from .partition import PartitionedGraph, block_size, local_edges, partition_1d
 from .ops import (aggregate, vq_assign_raw, vq_code_stats, vq_ema_apply, vq_quantize,
                   METRIC_DOT, METRIC_EUCLID, PATH_AUTO, PATH_EXACT, PATH_TENSOR)
 from .dense import linear_raw, linear_sum, linear_wgrad_raw
+from .decoder import edge_dot
 from .norm_act import bn_act_drop, batch_stats
 from . import norm_act
 from .vq import CosineSimCodebook, EuclideanCodebook, VectorQuantize
@@ -15,6 +16,6 @@ from .vq import CosineSimCodebook, EuclideanCodebook, VectorQuantize
 __all__ = ["StemGnnError", "GCNConv", "GINConv", "MixtureSageLayer", "MySAGEConv", "Encoder",
            "InnerProductDecoder", "CSR", "GraphStructure", "clear_structure_cache", "structure_of",
            "PartitionedGraph", "block_size", "local_edges", "partition_1d",
-           "aggregate", "bn_act_drop", "batch_stats", "norm_act", "linear_raw", "linear_sum", "linear_wgrad_raw", "vq_assign_raw", "vq_code_stats", "vq_ema_apply", "vq_quantize",
+           "aggregate", "edge_dot", "bn_act_drop", "batch_stats", "norm_act", "linear_raw", "linear_sum", "linear_wgrad_raw", "vq_assign_raw", "vq_code_stats", "vq_ema_apply", "vq_quantize",
            "METRIC_DOT", "METRIC_EUCLID", "PATH_AUTO", "PATH_EXACT", "PATH_TENSOR",
            "CosineSimCodebook", "EuclideanCodebook", "VectorQuantize"]

@@ -58,6 +58,7 @@ SIGNATURES = {
     "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "stemgnn_aggregate": (_i32, [C.POINTER(AggregateArgs), _vp]),
     "stemgnn_row_scale": (_i32, [_i64, _i64, _vp, _vp, _vp, _vp]),
+    "stemgnn_edge_dot": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i32, _vp, _vp]),
     "stemgnn_linear_workspace": (_i32, [C.POINTER(LinearArgs), C.POINTER(C.c_size_t)]),
     "stemgnn_linear": (_i32, [C.POINTER(LinearArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_linear_wgrad_workspace": (_i32, [C.POINTER(LinearWgradArgs), C.POINTER(C.c_size_t)]),

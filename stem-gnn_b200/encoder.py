@@ -10,6 +10,7 @@ from torch import Tensor
 
 from .conv import GCNConv, GINConv, MixtureSageLayer, MySAGEConv
 from . import norm_act
+from .decoder import edge_dot
 from .graph import structure_of
 
 
@@ -161,8 +162,9 @@ class Encoder(nn.Module):
 
 
 class InnerProductDecoder(nn.Module):
-    """sigma(<z_i, z_j>) over given node pairs (encoder.py:336-380); a caller of the hot path,
-    kept as plain torch."""
+    """sigma(<z_i, z_j>) over given node pairs (encoder.py:336-380).  The edge-wise decode runs
+    through K8 (`decoder.edge_dot`: no E x F gathered matrices, deterministic backward through
+    K1); `forward_all` is a plain dense product."""
 
     def __init__(self, hidden_dim=None, output_dim=None):
         super().__init__()
@@ -172,8 +174,7 @@ class InnerProductDecoder(nn.Module):
 
     def forward(self, z: Tensor, edge_index: Tensor, sigmoid: bool = True) -> Tensor:
         z = self.lin(z) if self.proj_z else z
-        value = (z[edge_index[0]] * z[edge_index[1]]).sum(dim=1)
-        return torch.sigmoid(value) if sigmoid else value
+        return edge_dot(z, edge_index, sigmoid)
 
     def forward_all(self, z: Tensor, sigmoid: bool = True) -> Tensor:
         z = self.lin(z) if self.proj_z else z

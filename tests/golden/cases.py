@@ -28,3 +28,11 @@ ENC_CASES = {
     "enc_moe": dict(backbone="sage", normalize="none", in_dim=24, hid=24, layers=2, xe=False,
                     moe=True),
 }
+
+
+# InnerProductDecoder (model/encoder.py:336-380): the topology-reconstruction decode on edges
+DEC_CASES = {
+    "dec_inner_sigmoid": dict(n=80, e=300, dim=24, proj=None, sigmoid=True),
+    "dec_inner_raw": dict(n=80, e=300, dim=20, proj=None, sigmoid=False),
+    "dec_inner_proj": dict(n=64, e=257, dim=24, proj=16, sigmoid=True),
+}

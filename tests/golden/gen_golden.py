@@ -2,7 +2,8 @@
 from /root/reference (only available in the build container, never on the GPU box):
 
 * vq_*.npz  -- /root/reference/STEM-GNN/model/vq.py VectorQuantize (imports torch + einops only)
-* enc_*.npz -- /root/reference/STEM-GNN/model/encoder.py Encoder, executed on oracle/pyg_shim
+* enc_*.npz, dec_*.npz -- /root/reference/STEM-GNN/model/encoder.py Encoder / InnerProductDecoder,
+               executed on oracle/pyg_shim
                (torch_geometric / torch_scatter are not installable here; see oracle/__init__.py)
 
 Run:  python tests/golden/gen_golden.py      (CPU, fp32, seeded; a few seconds)
@@ -23,9 +24,9 @@ sys.path.insert(0, "/root/reference/STEM-GNN")
 warnings.filterwarnings("ignore")
 
 from model.vq import VectorQuantize  # noqa: E402  (the reference's own module)
-from model.encoder import Encoder    # noqa: E402  (the reference's own module, on the shim)
+from model.encoder import Encoder, InnerProductDecoder  # noqa: E402  (the reference's own module, on the shim)
 
-from tests.golden.cases import ENC_CASES, VQ_CASES  # noqa: E402
+from tests.golden.cases import DEC_CASES, ENC_CASES, VQ_CASES  # noqa: E402
 
 
 def gen_vq(name, cfg):
@@ -98,8 +99,34 @@ def gen_enc(name, c):
     print(name, z.shape, len(before), "state tensors")
 
 
+def gen_dec(name, c):
+    torch.manual_seed(5)
+    dec = InnerProductDecoder(c["dim"], c["proj"]) if c["proj"] else InnerProductDecoder()
+    z = torch.randn(c["n"], c["dim"], requires_grad=True)
+    ei = torch.randint(0, c["n"], (2, c["e"]))
+    ei[:, :6] = ei[:, 6:12]           # duplicate edges
+    ei[1, 12:18] = ei[0, 12:18]       # self loops
+    out = dec(z, ei, sigmoid=c["sigmoid"])
+    g = torch.randn(out.shape, generator=torch.Generator().manual_seed(6))
+    (out * g).sum().backward()
+    res = dict(z=z.detach().numpy(), edge_index=ei.numpy(), out=out.detach().numpy(), g_out=g.numpy(),
+               g_z=z.grad.numpy())
+    for k, v in dec.state_dict().items():
+        res["state." + k] = v.detach().numpy()
+    for k, p in dec.named_parameters():
+        res["grad." + k] = p.grad.numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **res)
+    print(name, out.shape)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "dec":      # only the decoder fixtures (added later)
+        for k, v in DEC_CASES.items():
+            gen_dec(k, v)
+        sys.exit(0)
     for k, v in VQ_CASES.items():
         gen_vq(k, v)
     for k, v in ENC_CASES.items():
         gen_enc(k, v)
+    for k, v in DEC_CASES.items():
+        gen_dec(k, v)

@@ -12,7 +12,8 @@ from oracle import c_agg, graph_ref
 from oracle import propagate_ref as P
 from oracle.encoder_ref import EncoderRef
 from oracle.vq_ref import vq_forward_ref
-from tests.golden.cases import ENC_CASES, VQ_CASES
+from oracle.decoder_ref import edge_dot_grad_ref, edge_dot_ref
+from tests.golden.cases import DEC_CASES, ENC_CASES, VQ_CASES
 
 
 def _load(golden_dir, name):
@@ -148,3 +149,26 @@ def test_csr_ref_properties():
             seg = perm[rowptr[i]:rowptr[i + 1]]
             assert (ei[by][seg] == i).all() and (np.diff(seg) > 0).all()  # stable
             assert (col[rowptr[i]:rowptr[i + 1]] == ei[1 - by][seg]).all()
+
+
+@pytest.mark.parametrize("name", sorted(DEC_CASES))
+def test_decoder_oracle_matches_reference_golden(golden_dir, name):
+    """oracle/decoder_ref.py against the reference's own InnerProductDecoder (encoder.py:336-380)."""
+    c = DEC_CASES[name]
+    g = _load(golden_dir, name)
+    z = torch.from_numpy(g["z"]).requires_grad_(True)
+    ei = torch.from_numpy(g["edge_index"])
+    h = z
+    if c["proj"]:
+        lin = nn.Linear(c["dim"], c["proj"])
+        with torch.no_grad():
+            lin.weight.copy_(torch.from_numpy(g["state.lin.weight"]))
+            lin.bias.copy_(torch.from_numpy(g["state.lin.bias"]))
+        h = lin(z)
+    out = edge_dot_ref(h, ei, c["sigmoid"])
+    np.testing.assert_array_equal(out.detach().numpy(), g["out"])
+    (out * torch.from_numpy(g["g_out"])).sum().backward()
+    np.testing.assert_array_equal(z.grad.numpy(), g["g_z"])
+    if not c["proj"]:     # the closed form used for the large GPU cases
+        g64 = edge_dot_grad_ref(g["z"], g["edge_index"], g["g_out"], c["sigmoid"])
+        np.testing.assert_allclose(g["g_z"], g64, rtol=1e-5, atol=1e-6)
