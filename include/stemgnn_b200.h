@@ -268,6 +268,80 @@ int stemgnn_vq_ema_apply(const float* counts, const float* sums, int64_t embed_h
 int stemgnn_edge_dot(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes, int64_t feat,
                      const float* z, int64_t ldz, int apply_sigmoid, float* out, stemgnn_stream_t stream);
 
+/* ------------------------------------------------------------------ K9: graph augmentations
+ * The pretrain step augments the sampled subgraph before it reaches the encoder (reference
+ * STEM-GNN/pretrain.py:41-44, torch_geometric.utils 2.3.0 `mask_feature` / `dropout_adj`).
+ *
+ * dropout_adj: edge e survives iff u[e] >= p and (force_undirected ? row[e] <= col[e] : 1), with
+ * u = rand[e] when `rand` is given (the caller's torch.rand(E): same stream as the reference on the
+ * same device and seed) or a Philox draw keyed by (*seed, e) otherwise.  Survivors keep their order;
+ * with force_undirected the output is [row_kept ++ col_kept ; col_kept ++ row_kept] (2*kept columns),
+ * else [row_kept ; col_kept].  edge_id_out (optional, same length as an output row) holds the original
+ * edge id of every output edge, which is how edge_attr / edge types follow (`edge_attr[mask]`,
+ * `cat([edge_attr, edge_attr])`).  The survivor count is data-dependent, so the call is split like the
+ * boolean-mask indexing it replaces: _count leaves the count in device memory (and the tile offsets in
+ * the workspace), the caller reads it, allocates, and calls _write with the same arguments and
+ * workspace contents. */
+int stemgnn_dropout_adj_workspace(int64_t num_edges, size_t* bytes_host);
+int stemgnn_dropout_adj_count(const int64_t* edge_index, int64_t num_edges, const float* rand,
+                              const uint64_t* seed, float p, int force_undirected, int64_t* kept_out,
+                              void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+int stemgnn_dropout_adj_write(const int64_t* edge_index, int64_t num_edges, const float* rand,
+                              const uint64_t* seed, float p, int force_undirected, int64_t kept,
+                              int64_t* edge_index_out, int64_t* edge_id_out, const void* workspace,
+                              size_t workspace_bytes, stemgnn_stream_t stream);
+
+/* mask_feature: out[r, c] = keep ? x[r, c] : fill (masked_fill semantics: a masked NaN becomes fill)
+ * with keep = row_keep[r] & col_keep[c] & (u(r, c) >= p_elem); row_keep / col_keep are torch.bool
+ * vectors (1 byte each) or NULL, p_elem = 0 switches the element-wise Philox mask off.  mask_out
+ * (optional, [rows, feat] bytes) receives the mask (mode 'all' returns it).  The same call with
+ * fill = 0 on the upstream gradient is the backward.  feat % 4 == 0, 16-byte aligned rows. */
+int stemgnn_mask_fill(int64_t rows, int64_t feat, const float* x, int64_t ldx, const uint8_t* row_keep,
+                      const uint8_t* col_keep, float p_elem, const uint64_t* seed, float fill, float* out,
+                      int64_t ldo, uint8_t* mask_out, stemgnn_stream_t stream);
+
+/* out[i, :] = src[ids[i], :] -- `node_text_feat[data.x]`, `edge_text_feat[data.xe]`
+ * (STEM-GNN/pretrain.py:33-38) and `edge_attr[mask]` of dropout_adj.  An id outside [0, n_src) gives
+ * a NaN row.  feat % 4 == 0, 16-byte aligned rows. */
+int stemgnn_gather_rows(const float* src, int64_t lds, int64_t n_src, const int64_t* ids, int64_t n_out,
+                        int64_t feat, float* out, int64_t ldo, stemgnn_stream_t stream);
+
+/* ------------------------------------------------------------------ K10: neighbour sampling
+ * Replaces the sampling step of torch_geometric.loader.NeighborLoader (2.3.0; torch_sparse 0.6.15
+ * `neighbor_sample`, replace=False, directed=True) as driven by STEM-GNN/pretrain.py:151-153 and
+ * utils/loader.py:11-24.  The graph is the K0 CSR grouped by destination (in-edges per node).
+ * nodes = seeds in order (a duplicated seed keeps both positions, the map points at the first);
+ * per hop every frontier node takes min(deg, fanout) distinct in-edges (all, in edge order, when
+ * fanout < 0 or deg <= fanout; a uniform random subset otherwise, Philox keyed by *seed); unseen
+ * sources are appended to n_id in order of first appearance and form the next frontier.
+ * Outputs (caller-allocated at the capacities stemgnn_neighbor_sample_bounds returns):
+ *   n_id [node_cap] global ids; edge_index_out [2, edge_cap] LOCAL ids, row 0 = source, row 1 =
+ *   target (row 1 starts at edge_index_out + edge_cap); e_id [edge_cap] original edge ids;
+ *   counts [3 + 2*num_hops] int64 (device): [0] nodes, [1] edges, [2+2h], [3+2h] cumulative nodes /
+ *   edges after hop h, last word = error bits (1 seed out of range, 2 / 4 capacity exceeded).
+ * No host synchronisation inside the call: stages are launched over host-side bounds, true sizes stay
+ * on the device.  node_map [num_nodes] int32 is scratch that persists across calls: initialise it once
+ * with stemgnn_node_map_init; every call leaves it initialised again.  fan-outs above 64 (other than
+ * -1) return STEMGNN_EUNSUPPORTED. */
+typedef struct {
+    const int32_t* rowptr; const int32_t* col; const int32_t* perm;   /* CSR grouped by destination */
+    int64_t num_nodes, num_edges;
+    const int64_t* seeds; int64_t num_seeds;
+    int32_t num_hops; int32_t reserved;
+    const int32_t* fanout_host;     /* [num_hops] HOST array */
+    const uint64_t* seed;           /* device; may be NULL when every fan-out is < 0 */
+    int32_t* node_map;
+    int64_t node_cap, edge_cap;
+    int64_t* n_id; int64_t* edge_index_out; int64_t* e_id; int64_t* counts;
+} stemgnn_neighbor_sample_args;
+
+int stemgnn_neighbor_sample_bounds(int64_t num_seeds, int64_t num_nodes, int64_t num_edges,
+                                   int32_t num_hops, const int32_t* fanout_host, int64_t* node_cap_host,
+                                   int64_t* edge_cap_host, size_t* workspace_bytes_host);
+int stemgnn_node_map_init(int32_t* node_map, int64_t num_nodes, stemgnn_stream_t stream);
+int stemgnn_neighbor_sample(const stemgnn_neighbor_sample_args* args_host, void* workspace,
+                            size_t workspace_bytes, stemgnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,6 +9,8 @@ from .ops import (aggregate, vq_assign_raw, vq_code_stats, vq_ema_apply, vq_quan
                   METRIC_DOT, METRIC_EUCLID, PATH_AUTO, PATH_EXACT, PATH_TENSOR)
 from .dense import linear_raw, linear_sum, linear_wgrad_raw
 from .decoder import edge_dot
+from .augment import dropout_adj, gather_rows, mask_feature
+from .sampler import NeighborLoader, NeighborSampler, neighbor_sample
 from .norm_act import bn_act_drop, batch_stats
 from . import norm_act
 from .vq import CosineSimCodebook, EuclideanCodebook, VectorQuantize
@@ -18,4 +20,5 @@ __all__ = ["StemGnnError", "GCNConv", "GINConv", "MixtureSageLayer", "MySAGEConv
            "PartitionedGraph", "block_size", "local_edges", "partition_1d",
            "aggregate", "edge_dot", "bn_act_drop", "batch_stats", "norm_act", "linear_raw", "linear_sum", "linear_wgrad_raw", "vq_assign_raw", "vq_code_stats", "vq_ema_apply", "vq_quantize",
            "METRIC_DOT", "METRIC_EUCLID", "PATH_AUTO", "PATH_EXACT", "PATH_TENSOR",
-           "CosineSimCodebook", "EuclideanCodebook", "VectorQuantize"]
+           "CosineSimCodebook", "EuclideanCodebook", "VectorQuantize",
+           "dropout_adj", "gather_rows", "mask_feature", "NeighborLoader", "NeighborSampler", "neighbor_sample"]

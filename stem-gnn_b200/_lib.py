@@ -8,7 +8,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libstemgnn_b200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 _i64, _i32, _vp, _f32, _f64 = C.c_int64, C.c_int, C.c_void_p, C.c_float, C.c_double
 
@@ -48,6 +48,14 @@ class LinearWgradArgs(C.Structure):
                 ("gbias", _vp)]
 
 
+class NeighborSampleArgs(C.Structure):
+    _fields_ = [("rowptr", _vp), ("col", _vp), ("perm", _vp), ("num_nodes", _i64), ("num_edges", _i64),
+                ("seeds", _vp), ("num_seeds", _i64), ("num_hops", _i32), ("reserved", _i32),
+                ("fanout_host", C.POINTER(C.c_int32)), ("seed", _vp), ("node_map", _vp),
+                ("node_cap", _i64), ("edge_cap", _i64), ("n_id", _vp), ("edge_index_out", _vp),
+                ("e_id", _vp), ("counts", _vp)]
+
+
 # name -> (restype, argtypes); every symbol include/stemgnn_b200.h declares
 SIGNATURES = {
     "stemgnn_last_error": (C.c_char_p, []),
@@ -75,6 +83,15 @@ SIGNATURES = {
     "stemgnn_vq_code_stats": (_i32, [C.POINTER(VqCodeStatsArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_vq_ema_apply": (_i32, [_vp, _vp, _i64, _i64, _i64, _f64, _f64, _i32, _vp, _vp, _vp,
                                     _vp, _vp]),
+    "stemgnn_dropout_adj_workspace": (_i32, [_i64, C.POINTER(C.c_size_t)]),
+    "stemgnn_dropout_adj_count": (_i32, [_vp, _i64, _vp, _vp, _f32, _i32, _vp, _vp, C.c_size_t, _vp]),
+    "stemgnn_dropout_adj_write": (_i32, [_vp, _i64, _vp, _vp, _f32, _i32, _i64, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "stemgnn_mask_fill": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _f32, _vp, _f32, _vp, _i64, _vp, _vp]),
+    "stemgnn_gather_rows": (_i32, [_vp, _i64, _i64, _vp, _i64, _i64, _vp, _i64, _vp]),
+    "stemgnn_neighbor_sample_bounds": (_i32, [_i64, _i64, _i64, _i32, C.POINTER(C.c_int32), C.POINTER(_i64),
+                                              C.POINTER(_i64), C.POINTER(C.c_size_t)]),
+    "stemgnn_node_map_init": (_i32, [_vp, _i64, _vp]),
+    "stemgnn_neighbor_sample": (_i32, [C.POINTER(NeighborSampleArgs), _vp, C.c_size_t, _vp]),
 }
 
 _lib = None

@@ -13,6 +13,7 @@
 // Statistics are shifted sums (shift = row 0 of the column) accumulated in a fixed order:
 // deterministic, no atomics.  HBM-bound: N*F*4 B per pass.
 #include "common.cuh"
+#include "philox.cuh"
 
 namespace stemgnn {
 namespace bn {
@@ -20,19 +21,6 @@ namespace bn {
 struct Cols {                 // per-column constants, all [F]
     const float* mean; const float* invstd; const float* gamma; const float* beta;
 };
-
-// Philox4x32 with 7 rounds (Random123's "crush-resistant" minimum; curand's default is 10): the
-// forward apply pass with dropout measured 83 us against 65 us without -- the rounds are visible
-__device__ __forceinline__ uint4 philox4x32_7(uint4 c, uint2 k) {
-#pragma unroll
-    for (int r = 0; r < 7; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
-        k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
-    }
-    return c;
-}
 
 // keep-mask scale factors of the 4 elements of float4 number `idx4`: 1/(1-p) or 0
 __device__ __forceinline__ float4 drop_scale4(uint64_t seed, int64_t idx4, float p, float inv_keep) {
