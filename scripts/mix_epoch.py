@@ -1,0 +1,127 @@
+"""BASELINE configs[2]: one pretrain epoch over the multi-graph mix -- the disjoint
+union of Cora / CiteSeer / PubMed / arxiv-sized synthetic graphs (195,095 nodes, 1,274,551 edges,
+768-wide text features, 237 edge types), weight-5 seeds = 975,475 seeds -> 953 mini-batches of 1,024
+seeds, fan-out [10, 10] (reference STEM-GNN/pretrain.py:28-66,143-154, config/pt_data.yaml).
+
+Every stage of a mini-batch runs on the device through the library: K10 sampler -> K9 row gather of
+the text features -> K9 mask_feature + dropout_adj(force_undirected) -> K0 CSR -> 2-layer SAGE
+768-768 with the edge-type table (K1/K2, K5/K6, K7) -> shipped VQ 4 x 128 x 768 cosine (K3) ->
+backward -> AdamW.  Prints one JSON line (whole-epoch device time, CUDA events).
+    python scripts/mix_epoch.py [--batches B] [--cpu-batches C]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+PARTS = [(2708, 10556), (3327, 9104), (19717, 88648), (169343, 1166243)]
+F, T, HID, LAYERS, BATCH, FANOUT, WEIGHT = 768, 237, 768, 2, 1024, [10, 10], 5
+
+
+def mix_graph(seed):
+    g = torch.Generator().manual_seed(seed)
+    eis, off = [], 0
+    for n, e in PARTS:
+        eis.append(torch.randint(0, n, (2, e), generator=g) + off)
+        off += n
+    ei = torch.cat(eis, 1)
+    return off, ei, torch.randn(off, F, generator=g), torch.randn(T, F, generator=g), \
+        torch.randint(0, T, (ei.size(1),), generator=g)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batches", type=int, default=0, help="0 = the full epoch (953)")
+    ap.add_argument("--cpu-batches", type=int, default=3)
+    args = ap.parse_args()
+    import __graft_entry__ as G
+    G.build()
+    import stemgnn_b200 as S
+    from stemgnn_b200 import _lib
+    dev = torch.device("cuda:0")
+    n, ei, text, etable, etype = mix_graph(0)
+    data = dict(edge_index=ei.to(dev), x=torch.arange(n, device=dev), xe=etype.to(dev), num_nodes=n)
+    text_d, etable_d = text.to(dev), etable.to(dev)
+    seeds = torch.arange(n).repeat(WEIGHT)                            # get_train_node_idx, weight 5
+    loader = S.NeighborLoader(data, num_neighbors=FANOUT, input_nodes=seeds, batch_size=BATCH, shuffle=True, seed=1)
+    torch.manual_seed(0)
+    enc = S.Encoder(F, HID, nn.ReLU, LAYERS, backbone="sage", normalize="batch", dropout=0.15).to(dev).train()
+    vq = S.VectorQuantize(dim=HID, codebook_size=128, codebook_dim=HID, heads=4, separate_codebook_per_head=True,
+                          decay=0.8, commitment_weight=10, use_cosine_sim=True, orthogonal_reg_weight=1,
+                          orthogonal_reg_max_codes=32, orthogonal_reg_active_codes_only=False, kmeans_init=False,
+                          ema_update=False).to(dev).train()
+    opt = torch.optim.AdamW(list(enc.parameters()) + list(vq.parameters()), lr=1e-4, capturable=True)
+
+    def step(batch):
+        x = S.gather_rows(text_d, batch.x)                            # node_text_feat[data.x]
+        aug_x, _ = S.mask_feature(x, p=0.2)
+        aug_ei, aug_t = S.dropout_adj(batch.edge_index, batch.xe, p=0.2, force_undirected=True,
+                                      num_nodes=x.size(0))
+        opt.zero_grad(set_to_none=True)
+        z = enc(aug_x, aug_ei, (etable_d, aug_t))                     # edge_text_feat[data.xe] as a table
+        q, ind, vq_loss, _ = vq(z)
+        loss = q.square().mean() + vq_loss.sum()
+        loss.backward()
+        opt.step()
+        return loss, aug_ei.size(1), x.size(0)
+
+    total = len(loader) if args.batches <= 0 else min(args.batches, len(loader))
+    it = iter(loader)
+    for _ in range(3):                                                # warm-up batches
+        step(next(it))
+    torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    edges = nodes = done = 0
+    kept = []
+    t0 = time.perf_counter()
+    e0.record()
+    for batch in loader:
+        loss, m, nn_ = step(batch)
+        edges += m; nodes += nn_; done += 1
+        if len(kept) < args.cpu_batches:
+            kept.append(batch)
+        if done >= total:
+            break
+    e1.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    ms = e0.elapsed_time(e1)
+    launches = _lib.launch_count() - l0
+    line = dict(metric="edges/sec encoder fwd+bwd & VQ nodes/sec", value=LAYERS * edges / ms * 1e3, unit="edges/s",
+                n_gpus=1, steps=done, ms_per_step=ms / done, epoch_s_extrapolated=ms / done * len(loader) / 1e3,
+                wall_s=wall, vq_nodes_per_s=nodes / ms * 1e3, dtype="f32", data="synthetic",
+                gpu_launches=launches / done, final_loss=float(loss),
+                config=dict(workload="pretrain mix (195,095 nodes, 1,274,551 edges, 768 feats, 237 edge types), "
+                            "mini-batches of 1,024 seeds, fan-out [10,10], 2-layer SAGE 768-768 + shipped VQ 4x128x768",
+                            batches_per_epoch=len(loader), mean_nodes=nodes / done, mean_aug_edges=edges / done))
+    if args.cpu_batches > 0:
+        from oracle.encoder_ref import EncoderRef
+        torch.set_num_threads(os.cpu_count() or 1)
+        ref = EncoderRef(F, HID, nn.ReLU, LAYERS, backbone="sage", normalize="batch", dropout=0.15).train()
+        ropt = torch.optim.AdamW(ref.parameters(), lr=1e-4)
+        t0, ce = time.perf_counter(), 0
+        for b in kept:                                                # encoder part of the step only
+            x = text[b.x.cpu()]
+            bei, bt = b.edge_index.cpu(), b.xe.cpu()
+            ropt.zero_grad()
+            z = ref(x, bei, etable[bt])
+            z.square().mean().backward()
+            ropt.step()
+            ce += bei.size(1)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = dict(value=LAYERS * ce / dt, unit="edges/s", cores=os.cpu_count(), kind="port",
+                                    sample=f"{len(kept)} sampled mini-batches, encoder fwd+bwd+AdamW only "
+                                           "(no sampler, no augmentation, no VQ), oracle/ restatement")
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
