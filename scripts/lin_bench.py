@@ -13,8 +13,14 @@ def timeit(fn, reps=5):
         s.record(); fn(); t.record(); torch.cuda.synchronize()
         if r >= 2: ts.append(s.elapsed_time(t) * 1e3)
     return min(ts)
-for m, n, ks in [(169343, 256, (128, 128)), (169343, 256, (256, 256)), (169343, 256, (256,)), (169343, 128, (256,)),
-                 (2449029 // 4, 256, (256, 256)), (169343, 512, (512, 512))]:
+MIX = len(sys.argv) > 1 and sys.argv[1] == "mix"      # the 768-wide shapes of the pretrain mix (C3) mini-batch
+FWD = [(169343, 256, (128, 128)), (169343, 256, (256, 256)), (169343, 256, (256,)), (169343, 128, (256,)),
+       (2449029 // 4, 256, (256, 256)), (169343, 512, (512, 512))]
+WG = [(169343, 256, (128, 128)), (169343, 256, (256, 256)), (169343, 256, (256,))]
+if MIX:
+    FWD = [(43008, 768, (768, 768)), (43008, 768, (768,)), (43008, 3072, (768,)), (43008, 768, (3072,)), (43008, 768, (512,)), (43008, 768, (256,))]
+    WG = [(43008, 768, (768, 768)), (43008, 3072, (768,)), (43008, 768, (3072,))]
+for m, n, ks in FWD:
     srcs = [torch.randn(m, k, generator=g).to(dev) for k in ks]
     ws = [(torch.randn(n, k, generator=g) / k ** 0.5).to(dev) for k in ks]
     bias = torch.randn(n, generator=g).to(dev)
@@ -30,7 +36,7 @@ for m, n, ks in [(169343, 256, (128, 128)), (169343, 256, (256, 256)), (169343, 
                           tflops_fp32_equiv=round(fl / t_ours / 1e6, 1), tf32_mma_tflops=round(3 * fl / t_ours / 1e6, 1),
                           hbm_GBps=round(by / t_ours / 1e3))), flush=True)
 print("wgrad", flush=True)
-for m, n, ks in [(169343, 256, (128, 128)), (169343, 256, (256, 256)), (169343, 256, (256,))]:
+for m, n, ks in WG:
     gr = torch.randn(m, n, generator=g).to(dev)
     srcs = [torch.randn(m, k, generator=g).to(dev) for k in ks]
     t_ours = timeit(lambda: S.linear_wgrad_raw(gr, srcs, want_bias=False))

@@ -40,6 +40,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batches", type=int, default=0, help="0 = the full epoch (953)")
     ap.add_argument("--cpu-batches", type=int, default=3)
+    ap.add_argument("--trace", type=int, default=5, help="batches traced call by call after the timed loop")
     args = ap.parse_args()
     import __graft_entry__ as G
     G.build()
@@ -98,10 +99,25 @@ def main():
     line = dict(metric="edges/sec encoder fwd+bwd & VQ nodes/sec", value=LAYERS * edges / ms * 1e3, unit="edges/s",
                 n_gpus=1, steps=done, ms_per_step=ms / done, epoch_s_extrapolated=ms / done * len(loader) / 1e3,
                 wall_s=wall, vq_nodes_per_s=nodes / ms * 1e3, dtype="f32", data="synthetic",
-                gpu_launches=launches / done, final_loss=float(loss),
+                gpu_launches=launches / done, final_loss=float(loss.detach()),
                 config=dict(workload="pretrain mix (195,095 nodes, 1,274,551 edges, 768 feats, 237 edge types), "
                             "mini-batches of 1,024 seeds, fan-out [10,10], 2-layer SAGE 768-768 + shipped VQ 4x128x768",
                             batches_per_epoch=len(loader), mean_nodes=nodes / done, mean_aug_edges=edges / done))
+    if args.trace > 0:                                                # per-call device times (CUDA events)
+        _lib.TRACE = []
+        ta, tb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ta.record()
+        for _, batch in zip(range(args.trace), loader):
+            step(batch)
+        tb.record()
+        torch.cuda.synchronize()
+        fam = {}
+        for name, nbytes, flops, launches, a, b in _lib.TRACE:
+            d = fam.setdefault(name, [0.0, 0])
+            d[0] += a.elapsed_time(b); d[1] += 1
+        _lib.TRACE = None
+        line["traced_ms_per_step"] = ta.elapsed_time(tb) / args.trace
+        line["kernels_ms_per_step"] = {k: round(v[0] / args.trace, 4) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])}
     if args.cpu_batches > 0:
         from oracle.encoder_ref import EncoderRef
         torch.set_num_threads(os.cpu_count() or 1)
@@ -117,7 +133,8 @@ def main():
             ropt.step()
             ce += bei.size(1)
         dt = time.perf_counter() - t0
-        line["cpu_baseline"] = dict(value=LAYERS * ce / dt, unit="edges/s", cores=os.cpu_count(), kind="port",
+        line["cpu_baseline"] = dict(value=LAYERS * ce / dt, unit="edges/s", ms_per_step=dt / len(kept) * 1e3,
+                                    cores=os.cpu_count(), kind="port",
                                     sample=f"{len(kept)} sampled mini-batches, encoder fwd+bwd+AdamW only "
                                            "(no sampler, no augmentation, no VQ), oracle/ restatement")
     print(json.dumps(line), flush=True)

@@ -299,8 +299,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
 #pragma unroll 4
                             for (int i = 0; i < nrow; ++i) op[(int64_t)i * p.ldo] = st[i * 33 + lane] + b;
                         } else {
-#pragma unroll 4
-                            for (int i = 0; i < nrow; ++i) op[(int64_t)i * p.ldo] += st[i * 33 + lane] + b;
+                            // 16 reads of the chunk in flight before the first add: as a per-row
+                            // read-modify-write chain (4 in flight) an accumulating call cost 3x a
+                            // plain one (ogbn shapes never chain; the 768-wide mix layers do)
+#pragma unroll 1
+                            for (int i0 = 0; i0 < 32; i0 += 16) {
+                                float old[16];
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) old[i] = i0 + i < nrow ? op[(int64_t)(i0 + i) * p.ldo] : 0.f;
+#pragma unroll
+                                for (int i = 0; i < 16; ++i)
+                                    if (i0 + i < nrow) op[(int64_t)(i0 + i) * p.ldo] = old[i] + (st[(i0 + i) * 33 + lane] + b);
+                            }
                         }
                     }
                 }

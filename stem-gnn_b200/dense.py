@@ -46,6 +46,7 @@ def linear_raw(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
             for lo in range(0, a.size(1), K_SLAB):
                 hi = min(a.size(1), lo + K_SLAB)
                 pieces.append((a[:, lo:hi], w[lo:hi] if w_transposed else w[:, lo:hi]))
+        pieces.sort(key=lambda pc: -pc[0].size(1))   # full slabs first, the remainders pair up
         calls, cur, cur_k = [], [], 0
         for pc in pieces:                       # at most two sources and K_SLAB columns per call
             k = pc[0].size(1)

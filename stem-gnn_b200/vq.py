@@ -11,7 +11,7 @@ import torch.distributed as dist
 import torch.nn as nn
 import torch.nn.functional as F
 
-from . import ops
+from . import dense, ops
 
 
 def _l2norm(t):
@@ -225,7 +225,7 @@ class VectorQuantize(nn.Module):
             raise ValueError("x must be (N, dim) or (B, n, dim)")
         lead = x.shape[:-1]
         heads, cb = self.heads, self._codebook
-        h = self.project_in(x).reshape(-1, heads * cb.dim)         # 'b n (h d)' rows, heads in columns
+        h = self._project(self.project_in, x).reshape(-1, heads * cb.dim)   # 'b n (h d)' rows, heads in columns
         if cb.cosine:                                              # l2norm per head (vq.py:891)
             h = _l2norm(h.view(-1, heads, cb.dim)).view(-1, heads * cb.dim)
         commit_to_embed = self.learnable_codebook and not freeze_codebook
@@ -246,5 +246,19 @@ class VectorQuantize(nn.Module):
                 loss = loss + _orthogonal_loss(codes) * self.orthogonal_reg_weight
         embed_ind = ind.view(*lead, heads) if heads > 1 else ind.view(*lead)
         orig_quantize = q.view(*lead, heads * cb.dim)
-        quantize = self.project_out(orig_quantize)
+        quantize = self._project(self.project_out, orig_quantize)
         return quantize, embed_ind, loss, orig_quantize
+
+    @staticmethod
+    def _project(lin, t):
+        """project_in / project_out (model/vq.py:738-739,881,1041) on the tensor cores at fp32 accuracy
+        (K5/K6): with the shipped 768 <-> 4 x 768 widths the two fp32 SGEMMs and their
+        gradients were 2/3 of a pretrain mini-batch.  Widths the kernels do not take stay on nn.Linear."""
+        if not isinstance(lin, nn.Linear):
+            return lin(t)
+        n, k = lin.weight.shape
+        tiles = -(-n // 256) * -(-k // 256)
+        if not (t.is_cuda and t.dtype == torch.float32 and dense.supported(n, k) and tiles <= 64):
+            return lin(t)
+        out = dense.linear_sum([t.reshape(-1, k)], [lin.weight], lin.bias)
+        return out.view(*t.shape[:-1], n)
