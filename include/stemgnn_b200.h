@@ -342,6 +342,16 @@ int stemgnn_node_map_init(int32_t* node_map, int64_t num_nodes, stemgnn_stream_t
 int stemgnn_neighbor_sample(const stemgnn_neighbor_sample_args* args_host, void* workspace,
                             size_t workspace_bytes, stemgnn_stream_t stream);
 
+/* ------------------------------------------------------------------ K11: row-wise l2 normalisation
+ * y[r, :] = x[r, :] / max(||x[r, :]||_2, eps)  (F.normalize(p=2, dim=-1), the `l2norm` applied per
+ * head in front of the cosine codebook, STEM-GNN/model/vq.py:48-49,891) over `rows` contiguous rows
+ * of `dim` floats (dim % 4 == 0); norm_out [rows] (optional) keeps ||x|| for the backward:
+ * gx = (g - y * <g, y>) / max(||x||, eps), or g / eps where the norm was clamped. */
+int stemgnn_l2norm_forward(int64_t rows, int64_t dim, const float* x, float eps, float* y, float* norm_out,
+                           stemgnn_stream_t stream);
+int stemgnn_l2norm_backward(int64_t rows, int64_t dim, const float* g, const float* y, const float* norm,
+                            float eps, float* gx, stemgnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

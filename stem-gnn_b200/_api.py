@@ -5,7 +5,7 @@ from .conv import GCNConv, GINConv, MixtureSageLayer, MySAGEConv
 from .encoder import Encoder, InnerProductDecoder
 from .graph import CSR, GraphStructure, clear_structure_cache, structure_of
 from .partition import PartitionedGraph, block_size, local_edges, partition_1d
-from .ops import (aggregate, vq_assign_raw, vq_code_stats, vq_ema_apply, vq_quantize,
+from .ops import (aggregate, l2norm_rows, vq_assign_raw, vq_code_stats, vq_ema_apply, vq_quantize,
                   METRIC_DOT, METRIC_EUCLID, PATH_AUTO, PATH_EXACT, PATH_TENSOR)
 from .dense import linear_raw, linear_sum, linear_wgrad_raw
 from .decoder import edge_dot
@@ -18,7 +18,7 @@ from .vq import CosineSimCodebook, EuclideanCodebook, VectorQuantize
 __all__ = ["StemGnnError", "GCNConv", "GINConv", "MixtureSageLayer", "MySAGEConv", "Encoder",
            "InnerProductDecoder", "CSR", "GraphStructure", "clear_structure_cache", "structure_of",
            "PartitionedGraph", "block_size", "local_edges", "partition_1d",
-           "aggregate", "edge_dot", "bn_act_drop", "batch_stats", "norm_act", "linear_raw", "linear_sum", "linear_wgrad_raw", "vq_assign_raw", "vq_code_stats", "vq_ema_apply", "vq_quantize",
+           "aggregate", "l2norm_rows", "edge_dot", "bn_act_drop", "batch_stats", "norm_act", "linear_raw", "linear_sum", "linear_wgrad_raw", "vq_assign_raw", "vq_code_stats", "vq_ema_apply", "vq_quantize",
            "METRIC_DOT", "METRIC_EUCLID", "PATH_AUTO", "PATH_EXACT", "PATH_TENSOR",
            "CosineSimCodebook", "EuclideanCodebook", "VectorQuantize",
            "dropout_adj", "gather_rows", "mask_feature", "NeighborLoader", "NeighborSampler", "neighbor_sample"]

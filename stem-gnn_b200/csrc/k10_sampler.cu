@@ -27,6 +27,7 @@
 namespace stemgnn {
 namespace smp {
 
+constexpr int SCAN_ITEMS = 1;    // one frontier node / edge slot per thread: spreads a 10k-node hop over the SMs
 constexpr int MAX_FANOUT = 64;   // random subsets (deg > k) keep the chosen slots in local memory
 enum { ST_BEGIN = 0, ST_END, ST_EDGE_BASE, ST_HOP_EDGES, ST_NEW_NODES, ST_ERROR, ST_WORDS = 8 };
 enum { ERR_SEED_RANGE = 1, ERR_EDGE_CAP = 2, ERR_NODE_CAP = 4 };
@@ -213,7 +214,7 @@ extern "C" int stemgnn_neighbor_sample_bounds(int64_t num_seeds, int64_t num_nod
     if (node_cap_host) *node_cap_host = b.node_cap;
     if (edge_cap_host) *edge_cap_host = b.edge_cap;
     if (workspace_bytes_host)
-        *workspace_bytes_host = align_up(smp::ST_WORDS * 8, 256) + align_up((size_t)scan::num_tiles(b.max_stage) * 4, 256);
+        *workspace_bytes_host = align_up(smp::ST_WORDS * 8, 256) + align_up((size_t)scan::num_tiles(b.max_stage, smp::SCAN_ITEMS) * 4, 256);
     return STEMGNN_OK;
 }
 
@@ -263,9 +264,9 @@ extern "C" int stemgnn_neighbor_sample(const stemgnn_neighbor_sample_args* a, vo
         const int k = a->fanout_host[h];
         int64_t eb = k < 0 ? a->num_edges : front * (int64_t)k;
         if (h > 0 && eb > a->num_edges) eb = a->num_edges;
-        scan::ordered_emit(smp::CountNbr{g, k}, smp::PickNbr{g, k, h, a->seed}, front, tiles, st + smp::ST_HOP_EDGES, stream);
+        scan::ordered_emit<smp::SCAN_ITEMS>(smp::CountNbr{g, k}, smp::PickNbr{g, k, h, a->seed}, front, tiles, st + smp::ST_HOP_EDGES, stream);
         if (eb > 0) SG_LAUNCH(smp::claim_kernel<<<(unsigned)((eb + T - 1) / T), T, 0, stream>>>(g, eb));
-        scan::ordered_emit(smp::IsFirst{g}, smp::AssignId{g}, eb, tiles, st + smp::ST_NEW_NODES, stream);
+        scan::ordered_emit<smp::SCAN_ITEMS>(smp::IsFirst{g}, smp::AssignId{g}, eb, tiles, st + smp::ST_NEW_NODES, stream);
         if (eb > 0) SG_LAUNCH(smp::relabel_kernel<<<(unsigned)((eb + T - 1) / T), T, 0, stream>>>(g, eb));
         SG_LAUNCH(smp::advance_kernel<<<1, 1, 0, stream>>>(st, a->counts, h));
         front = eb < a->num_nodes ? eb : a->num_nodes;

@@ -19,6 +19,8 @@
 namespace stemgnn {
 namespace aug {
 
+constexpr int SCAN_ITEMS = 8;   // edge-list sized streams
+
 struct KeepEdge {
     const int64_t* ei; int64_t E; const float* rnd; const uint64_t* seed; float p; int undirected;
     __device__ __forceinline__ int operator()(int64_t e) const {
@@ -105,7 +107,7 @@ using namespace stemgnn;
 extern "C" int stemgnn_dropout_adj_workspace(int64_t E, size_t* bytes) {
     SG_CHECK_ARG(bytes != nullptr, "bytes_host is NULL");
     SG_CHECK_ARG(E >= 0 && E < (int64_t)2147483647, "E must be in [0, 2^31)");
-    *bytes = align_up((size_t)scan::num_tiles(E) * 4, 256);
+    *bytes = align_up((size_t)scan::num_tiles(E, aug::SCAN_ITEMS) * 4, 256);
     return STEMGNN_OK;
 }
 
@@ -133,9 +135,9 @@ extern "C" int stemgnn_dropout_adj_count(const int64_t* edge_index, int64_t E, c
     if (rc) return rc;
     SG_CHECK_ARG(kept_out, "kept_out is NULL");
     int32_t* tiles = (int32_t*)workspace;
-    const int nt = (int)scan::num_tiles(E);
+    const int nt = (int)scan::num_tiles(E, aug::SCAN_ITEMS);
     aug::KeepEdge keep{edge_index, E, rnd, seed, p, force_undirected};
-    SG_LAUNCH(scan::tile_count_kernel<<<nt, scan::THREADS, 0, stream>>>(keep, E, tiles));
+    SG_LAUNCH(scan::tile_count_kernel<aug::SCAN_ITEMS><<<nt, scan::THREADS, 0, stream>>>(keep, E, tiles));
     SG_LAUNCH(scan::tile_scan_kernel<<<1, scan::THREADS, 0, stream>>>(tiles, nt, kept_out));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
@@ -152,10 +154,10 @@ extern "C" int stemgnn_dropout_adj_write(const int64_t* edge_index, int64_t E, c
     SG_CHECK_ARG(kept >= 0 && kept <= E, "kept out of range");
     if (kept == 0 || E == 0) return STEMGNN_OK;
     SG_CHECK_ARG(edge_index_out, "edge_index_out is NULL");
-    const int nt = (int)scan::num_tiles(E);
+    const int nt = (int)scan::num_tiles(E, aug::SCAN_ITEMS);
     aug::KeepEdge keep{edge_index, E, rnd, seed, p, force_undirected};
     aug::WriteEdge wr{edge_index, E, kept, force_undirected, edge_index_out, edge_id_out};
-    SG_LAUNCH(scan::tile_emit_kernel<<<nt, scan::THREADS, 0, stream>>>(keep, wr, E, (const int32_t*)workspace));
+    SG_LAUNCH(scan::tile_emit_kernel<aug::SCAN_ITEMS><<<nt, scan::THREADS, 0, stream>>>(keep, wr, E, (const int32_t*)workspace));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

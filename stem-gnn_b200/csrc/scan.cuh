@@ -13,8 +13,9 @@ namespace stemgnn {
 namespace scan {
 
 constexpr int THREADS = 256;
-constexpr int ITEMS = 8;
-constexpr int TILE = THREADS * ITEMS;
+// ITEMS per thread (template parameter): 8 for edge-list sized streams, 1 when the item count is a
+// few thousand and an item is heavy (the sampler's per-node subset draw: 5 CTAs of 2,048 nodes took
+// 137 us), so that the work spreads over the SMs
 
 // exclusive scan of one int per thread over the 256-thread CTA; *total = CTA sum
 __device__ __forceinline__ int block_excl_scan(int v, int* total) {
@@ -40,10 +41,10 @@ __device__ __forceinline__ int block_excl_scan(int v, int* total) {
     return base + inc - v;
 }
 
-template <class Count>
+template <int ITEMS, class Count>
 __global__ void __launch_bounds__(THREADS)
 tile_count_kernel(Count count, int64_t n, int32_t* __restrict__ tile_sums) {
-    const int64_t base = (int64_t)blockIdx.x * TILE;
+    const int64_t base = (int64_t)blockIdx.x * (THREADS * ITEMS);
     int s = 0;
 #pragma unroll
     for (int r = 0; r < ITEMS; ++r) {
@@ -70,10 +71,10 @@ tile_scan_kernel(int32_t* __restrict__ tile_sums, int nt, int64_t* __restrict__ 
     if (threadIdx.x == 0 && total_out) *total_out = carry;
 }
 
-template <class Count, class Emit>
+template <int ITEMS, class Count, class Emit>
 __global__ void __launch_bounds__(THREADS)
 tile_emit_kernel(Count count, Emit emit, int64_t n, const int32_t* __restrict__ tile_offs) {
-    const int64_t base = (int64_t)blockIdx.x * TILE;
+    const int64_t base = (int64_t)blockIdx.x * (THREADS * ITEMS);
     int64_t running = tile_offs[blockIdx.x];
 #pragma unroll 1
     for (int r = 0; r < ITEMS; ++r) {
@@ -86,16 +87,19 @@ tile_emit_kernel(Count count, Emit emit, int64_t n, const int32_t* __restrict__ 
     }
 }
 
-static inline int64_t num_tiles(int64_t n) { return n > 0 ? (n + TILE - 1) / TILE : 1; }
+static inline int64_t num_tiles(int64_t n, int items) {
+    const int64_t tile = (int64_t)THREADS * items;
+    return n > 0 ? (n + tile - 1) / tile : 1;
+}
 
-// tile_offs: num_tiles(n) int32 of scratch; total_out: device int64 or NULL.  n may be 0.
-template <class Count, class Emit>
+// tile_offs: num_tiles(n, ITEMS) int32 of scratch; total_out: device int64 or NULL.  n may be 0.
+template <int ITEMS, class Count, class Emit>
 static inline void ordered_emit(Count count, Emit emit, int64_t n, int32_t* tile_offs,
                                 int64_t* total_out, cudaStream_t stream) {
-    const int nt = (int)num_tiles(n);
-    SG_LAUNCH(tile_count_kernel<<<nt, THREADS, 0, stream>>>(count, n, tile_offs));
+    const int nt = (int)num_tiles(n, ITEMS);
+    SG_LAUNCH(tile_count_kernel<ITEMS><<<nt, THREADS, 0, stream>>>(count, n, tile_offs));
     SG_LAUNCH(tile_scan_kernel<<<1, THREADS, 0, stream>>>(tile_offs, nt, total_out));
-    SG_LAUNCH(tile_emit_kernel<<<nt, THREADS, 0, stream>>>(count, emit, n, tile_offs));
+    SG_LAUNCH(tile_emit_kernel<ITEMS><<<nt, THREADS, 0, stream>>>(count, emit, n, tile_offs));
 }
 
 }  // namespace scan

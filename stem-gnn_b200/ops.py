@@ -188,6 +188,42 @@ def aggregate(x, graph, *, to_row=1, reduce="mean", act="none", edge_attr=None, 
     return _Aggregate.apply(x, graph, to_row, r, a, edge_attr, type_table, edge_type, edge_weight)
 
 
+# ------------------------------------------------------------------------------- l2norm (K11)
+class _L2Norm(torch.autograd.Function):
+    """F.normalize(x, p=2, dim=-1) over the rows of a contiguous [R, D] matrix, one kernel each way."""
+
+    @staticmethod
+    def forward(ctx, x, eps):
+        x = _f32c(x, "x")
+        r, d = x.shape
+        y = torch.empty_like(x)
+        norm = torch.empty(r, dtype=torch.float32, device=x.device)
+        with _lib.traced("l2norm_forward", 2 * r * d * 4 + r * 4, 0, 1):
+            _lib.check(_lib.lib().stemgnn_l2norm_forward(r, d, _lib.ptr(x), eps, _lib.ptr(y), _lib.ptr(norm),
+                                                         _lib.stream()))
+        ctx.save_for_backward(y, norm)
+        ctx.eps = eps
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        y, norm = ctx.saved_tensors
+        g = _f32c(g, "grad")
+        r, d = y.shape
+        gx = torch.empty_like(y)
+        with _lib.traced("l2norm_backward", 3 * r * d * 4 + r * 4, 0, 1):
+            _lib.check(_lib.lib().stemgnn_l2norm_backward(r, d, _lib.ptr(g), _lib.ptr(y), _lib.ptr(norm), ctx.eps,
+                                                          _lib.ptr(gx), _lib.stream()))
+        return gx, None
+
+
+def l2norm_rows(x, eps=1e-12):
+    """x / max(||x||_2, eps) per row of a 2-D fp32 CUDA matrix (model/vq.py:48-49), differentiable."""
+    if x.dim() != 2 or x.size(1) % 4:
+        raise ValueError("l2norm_rows: a 2-D matrix whose width is a multiple of 4")
+    return _L2Norm.apply(x, float(eps))
+
+
 # ------------------------------------------------------------------------------- VQ (K3 / K4)
 METRIC_EUCLID, METRIC_DOT = 0, 1
 PATH_AUTO, PATH_EXACT, PATH_TENSOR = 0, 1, 2

@@ -227,7 +227,10 @@ class VectorQuantize(nn.Module):
         heads, cb = self.heads, self._codebook
         h = self._project(self.project_in, x).reshape(-1, heads * cb.dim)   # 'b n (h d)' rows, heads in columns
         if cb.cosine:                                              # l2norm per head (vq.py:891)
-            h = _l2norm(h.view(-1, heads, cb.dim)).view(-1, heads * cb.dim)
+            if h.is_cuda and h.dtype == torch.float32 and cb.dim % 4 == 0:
+                h = ops.l2norm_rows(h.contiguous().view(-1, cb.dim)).view(-1, heads * cb.dim)     # K11
+            else:
+                h = _l2norm(h.view(-1, heads, cb.dim)).view(-1, heads * cb.dim)
         commit_to_embed = self.learnable_codebook and not freeze_codebook
         q, ind, mse = cb(h, heads, self.training, freeze_codebook, commit_to_embed)
         loss = torch.zeros(1, device=x.device, requires_grad=self.training)    # vq.py:983

@@ -170,3 +170,26 @@ def test_sweep_slice_large_codebook():
     x = torch.randn(rows, D, generator=g, device=DEV)
     embed = torch.randn(1, K, D, generator=g, device=DEV)
     _check_pair(x, embed, 1, S.METRIC_EUCLID)
+
+
+@pytest.mark.parametrize("rows,dim", [(1, 4), (1000, 32), (4097, 768), (333, 1028)])
+def test_l2norm_rows_matches_f_normalize(rows, dim):
+    """K11 against torch's own F.normalize (the reference's l2norm, model/vq.py:48-49) and its autograd."""
+    import torch.nn.functional as F
+    g_ = torch.Generator().manual_seed(rows + dim)
+    x = (torch.randn(rows, dim, generator=g_) * 3).to(DEV)
+    x[0] = 0                                          # zero row: clamped norm, y = 0
+    if rows > 5:
+        x[5] = 1e-20                                  # below eps
+    up = torch.randn(rows, dim, generator=g_).to(DEV)
+    a = x.clone().requires_grad_(True)
+    b = x.clone().requires_grad_(True)
+    ya = S.l2norm_rows(a)
+    yb = F.normalize(b, p=2, dim=-1)
+    torch.testing.assert_close(ya, yb, rtol=1e-6, atol=1e-7)
+    ya.backward(up)
+    yb.backward(up)
+    big = x.norm(dim=-1) > 1e-6
+    torch.testing.assert_close(a.grad[big], b.grad[big], rtol=2e-5, atol=1e-6)
+    assert bool(torch.isfinite(a.grad[0]).all())
+    assert torch.equal(S.l2norm_rows(x), S.l2norm_rows(x))
