@@ -47,7 +47,7 @@ struct WgParams {
     int k[2];
     int64_t m;
     int n, nb, kbt;          // n blocks, k blocks over the CONCATENATED sources [A_0 | A_1]
-    int slots;               // partial tiles per CTA (a multiple of nb*kbt)
+    int slots;               // partial tiles per CTA (the grid is a multiple of nb*kbt: one tile id per CTA)
     int64_t slabs;
     int slab;                // rows per work item (<= SLAB, multiple of KM)
     float* partial;          // [grid][slots][256*256]: local item i of a CTA lands in slot i % slots
@@ -285,8 +285,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) wgrad_tc_kernel(const WgParams
 }
 
 // gw_s[n, k] = sum, in (slot, CTA) order, of the partial tiles of that (n block, k block).  Slot i of
-// CTA c holds the items c + (i + t*slots)*grid, t = 0, 1, ..: all the same combo because slots is a
-// multiple of the combo count.
+// CTA c holds the items c + (i + t*slots)*grid, t = 0, 1, ..: all the same combo because the grid is
+// a multiple of the combo count.
 struct WgReduce {
     const float* partial;
     int grid, nb, kbt, slots;
@@ -438,8 +438,9 @@ int wg_plan(const stemgnn_linear_wgrad_args* a, WgPlan& pl) {
     const int sms = sm_count();
     {
         const int64_t slabs0 = (a->m + wgrad::SLAB - 1) / wgrad::SLAB;
-        const int64_t rounds = (slabs0 * pl.combos + sms - 1) / sms;
-        int64_t slabs_t = rounds * sms / pl.combos;
+        const int64_t geff = (int64_t)(sms / pl.combos) * pl.combos;      // the grid (see below)
+        const int64_t rounds = (slabs0 * pl.combos + geff - 1) / geff;
+        int64_t slabs_t = rounds * geff / pl.combos;
         if (slabs_t < slabs0) slabs_t = slabs0;
         int64_t slab = a->m > 0 ? (a->m + slabs_t - 1) / slabs_t : wgrad::SLAB;
         slab = (slab + wgrad::KM - 1) / wgrad::KM * wgrad::KM;
@@ -449,15 +450,20 @@ int wg_plan(const stemgnn_linear_wgrad_args* a, WgPlan& pl) {
     }
     pl.slabs = (a->m + pl.slab - 1) / pl.slab;
     pl.items = pl.slabs * pl.combos;
-    pl.grid = (int)(pl.items < sms ? (pl.items > 0 ? pl.items : 1) : sms);
-    // one partial tile per local item while that stays under ~256 MB; beyond, slots are reused and
-    // the epilogue adds into them (read-modify-write through L2)
+    // The grid is a multiple of the tile count, so CTA c only ever sees tile c % combos (items are
+    // dealt round-robin, slab-major: the CTAs of one round share their G / A slabs through L2) and any
+    // number of partial slots per CTA is legal.
+    pl.grid = (int)(pl.items < sms ? (pl.items > 0 ? pl.items : 1) : (sms / pl.combos) * pl.combos);
+    // One partial tile per local item while all of them stay under 256 MB (written once, read once by
+    // the reduce).  Beyond that (wide layers: 3072 x 768 weights over 43k rows were 3,024 tiles =
+    // 790 MB written and read back, the reduce alone 430 us) the CTA keeps as few tiles as fit in L2
+    // next to the operands and adds every further item into them (read-modify-write through L2).
     const int64_t per_cta = (pl.items + pl.grid - 1) / pl.grid;
-    int64_t r = (per_cta + pl.combos - 1) / pl.combos;
-    const int64_t r_cap = (256ll << 20) / ((int64_t)pl.grid * pl.combos * wgrad::BT * wgrad::BT * 4);
-    if (r > r_cap) r = r_cap;
-    if (r < 1) r = 1;
-    pl.slots = (int)(r * pl.combos);
+    const int64_t tile_bytes = (int64_t)wgrad::BT * wgrad::BT * 4;
+    int64_t slots = per_cta;
+    if ((int64_t)pl.grid * per_cta * tile_bytes > (256ll << 20)) slots = (64ll << 20) / ((int64_t)pl.grid * tile_bytes);
+    if (slots < 1) slots = 1;
+    pl.slots = (int)slots;
     pl.partial_bytes = (size_t)pl.grid * pl.slots * wgrad::BT * wgrad::BT * 4;
     pl.cs_blocks = sms * 4;
     pl.cs_bytes = a->gbias ? (size_t)pl.cs_blocks * a->n * 4 : 0;
