@@ -29,7 +29,7 @@ def _rowmajor(t):
     return t
 
 
-K_SLAB = 512       # columns accumulated in TMEM per call once a product is cut into slabs
+K_SLAB = 768       # columns accumulated in TMEM per call once a product is cut into slabs (= K_SINGLE: same bound)
 K_SINGLE = 768     # widest product done in one call (measured max error 7.5e-9 * K of the output scale)
 
 
