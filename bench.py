@@ -172,8 +172,17 @@ def summarize_trace(trace, steps, pk, n_feat_bytes_l2):
     return out
 
 
-def roofline_of(kern, name, pk, x_fits_l2=None):
+def roofline_of(kern, name, pk, x_fits_l2=None, codes=None):
     k = kern[name]
+    if name == "vq_assign" and k.get("tflops") is not None and codes is not None and codes <= 512:
+        # with fp32 inputs the distance GEMM's intensity is 2K/4 flop per byte, the ridge
+        # (1,664 TF / 6.55 TB/s = 254 flop/B) is at K ~ 508: K <= 512 is reported against HBM
+        a = k["gbps_alg"]
+        return dict(kernel=name, bound="hbm", achieved=a, peak=pk["hbm"], unit="GB/s", frac=a / pk["hbm"],
+                    traffic=None, peak_source=pk["src"], alg_bytes_per_launch=k["alg_bytes_per_call"],
+                    tflops=k["tflops"],
+                    bytes_model="N*D*4 (x) + N*D*4 (quantize) + N*8 (indices) + K*D*4 per call; K <= 512 with "
+                                "fp32 inputs sits left of the tensor/HBM ridge (SURVEY.md 8d)")
     if name == "vq_assign" and k.get("tflops") is not None:
         # K >= ~508 with fp32 inputs sits right of the ridge: tensor-bound
         return dict(kernel=name, bound="tensor", achieved=k["tflops"], peak=pk["tc_sus"] or pk["tc"],
@@ -425,7 +434,7 @@ def run_ours(args, w):
     for name in kern:
         if "gbps_alg" not in kern[name]:
             continue
-        r = roofline_of(kern, name, pk)
+        r = roofline_of(kern, name, pk, codes=w["codes"])
         if name in traffic:
             r["traffic"] = traffic[name]["bytes_per_launch"]
             r["traffic_source"] = traffic[name]["source"]

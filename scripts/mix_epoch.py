@@ -42,23 +42,40 @@ def main():
     ap.add_argument("--cpu-batches", type=int, default=3)
     ap.add_argument("--trace", type=int, default=5, help="batches traced call by call after the timed loop")
     args = ap.parse_args()
+    import torch.distributed as dist
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:                                                     # replicas over mini-batches (C3)
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
     import __graft_entry__ as G
-    G.build()
+    if rank == 0:
+        G.build()
+    if world > 1:
+        dist.barrier()
     import stemgnn_b200 as S
     from stemgnn_b200 import _lib
-    dev = torch.device("cuda:0")
     n, ei, text, etable, etype = mix_graph(0)
     data = dict(edge_index=ei.to(dev), x=torch.arange(n, device=dev), xe=etype.to(dev), num_nodes=n)
     text_d, etable_d = text.to(dev), etable.to(dev)
     seeds = torch.arange(n).repeat(WEIGHT)                            # get_train_node_idx, weight 5
-    loader = S.NeighborLoader(data, num_neighbors=FANOUT, input_nodes=seeds, batch_size=BATCH, shuffle=True, seed=1)
+    all_batches = -(-seeds.numel() // BATCH)
+    if world > 1:                                                     # every rank samples its own share of the seeds
+        seeds = seeds[torch.randperm(seeds.numel(), generator=torch.Generator().manual_seed(7))][rank::world]
+        seeds = seeds[:(all_batches // world) * BATCH]
+    loader = S.NeighborLoader(data, num_neighbors=FANOUT, input_nodes=seeds, batch_size=BATCH, shuffle=True,
+                              seed=1 + rank)
     torch.manual_seed(0)
     enc = S.Encoder(F, HID, nn.ReLU, LAYERS, backbone="sage", normalize="batch", dropout=0.15).to(dev).train()
     vq = S.VectorQuantize(dim=HID, codebook_size=128, codebook_dim=HID, heads=4, separate_codebook_per_head=True,
                           decay=0.8, commitment_weight=10, use_cosine_sim=True, orthogonal_reg_weight=1,
                           orthogonal_reg_max_codes=32, orthogonal_reg_active_codes_only=False, kmeans_init=False,
                           ema_update=False).to(dev).train()
-    opt = torch.optim.AdamW(list(enc.parameters()) + list(vq.parameters()), lr=1e-4, capturable=True)
+    params = list(enc.parameters()) + list(vq.parameters())
+    opt = torch.optim.AdamW(params, lr=1e-4, capturable=True)
+
+    ar_events = []
 
     def step(batch):
         x = S.gather_rows(text_d, batch.x)                            # node_text_feat[data.x]
@@ -70,6 +87,17 @@ def main():
         q, ind, vq_loss, _ = vq(z)
         loss = q.square().mean() + vq_loss.sum()
         loss.backward()
+        if world > 1:                                                 # one flat all-reduce of the gradients
+            ar0 = torch.cuda.Event(enable_timing=True); ar1 = torch.cuda.Event(enable_timing=True)
+            ar0.record()
+            flat = torch.cat([p.grad.reshape(-1) for p in params])
+            dist.all_reduce(flat)
+            flat /= world
+            o = 0
+            for p in params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
+            ar1.record()
+            ar_events.append((ar0, ar1))
         opt.step()
         return loss, aug_ei.size(1), x.size(0)
 
@@ -78,6 +106,8 @@ def main():
     for _ in range(3):                                                # warm-up batches
         step(next(it))
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
     l0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     edges = nodes = done = 0
@@ -95,15 +125,26 @@ def main():
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
     ms = e0.elapsed_time(e1)
+    if world > 1:                                                     # max over ranks; totals over ranks
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+        tot = torch.tensor([edges, nodes], dtype=torch.float64, device=dev)
+        dist.all_reduce(tot)
+        edges, nodes = float(tot[0]), float(tot[1])
     launches = _lib.launch_count() - l0
+    ar_ms = sum(a.elapsed_time(b) for a, b in ar_events[3:]) / max(len(ar_events) - 3, 1) if ar_events else 0.0
     line = dict(metric="edges/sec encoder fwd+bwd & VQ nodes/sec", value=LAYERS * edges / ms * 1e3, unit="edges/s",
-                n_gpus=1, steps=done, ms_per_step=ms / done, epoch_s_extrapolated=ms / done * len(loader) / 1e3,
+                n_gpus=world, steps=done, ms_per_step=ms / done, epoch_s_extrapolated=ms / done * len(loader) / 1e3,
+                scaling="strong (the epoch's mini-batches are dealt over the ranks)",
                 wall_s=wall, vq_nodes_per_s=nodes / ms * 1e3, dtype="f32", data="synthetic",
-                gpu_launches=launches / done, final_loss=float(loss.detach()),
+                grad_allreduce_ms_per_step=ar_ms, gpu_launches=launches / done, final_loss=float(loss.detach()),
                 config=dict(workload="pretrain mix (195,095 nodes, 1,274,551 edges, 768 feats, 237 edge types), "
                             "mini-batches of 1,024 seeds, fan-out [10,10], 2-layer SAGE 768-768 + shipped VQ 4x128x768",
-                            batches_per_epoch=len(loader), mean_nodes=nodes / done, mean_aug_edges=edges / done))
-    if args.trace > 0:                                                # per-call device times (CUDA events)
+                            batches_per_epoch_per_rank=len(loader), mean_nodes=nodes / done / world,
+                            mean_aug_edges=edges / done / world,
+                            parallelism="single GPU" if world == 1 else f"dp{world}: replicas over mini-batches, flat gradient all-reduce (NCCL)"))
+    if args.trace > 0 and world == 1:                                                # per-call device times (CUDA events)
         _lib.TRACE = []
         ta, tb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ta.record()
@@ -118,7 +159,7 @@ def main():
         _lib.TRACE = None
         line["traced_ms_per_step"] = ta.elapsed_time(tb) / args.trace
         line["kernels_ms_per_step"] = {k: round(v[0] / args.trace, 4) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])}
-    if args.cpu_batches > 0:
+    if args.cpu_batches > 0 and rank == 0:
         from oracle.encoder_ref import EncoderRef
         torch.set_num_threads(os.cpu_count() or 1)
         ref = EncoderRef(F, HID, nn.ReLU, LAYERS, backbone="sage", normalize="batch", dropout=0.15).train()
@@ -137,7 +178,11 @@ def main():
                                     cores=os.cpu_count(), kind="port",
                                     sample=f"{len(kept)} sampled mini-batches, encoder fwd+bwd+AdamW only "
                                            "(no sampler, no augmentation, no VQ), oracle/ restatement")
-    print(json.dumps(line), flush=True)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        os._exit(0)
 
 
 if __name__ == "__main__":
