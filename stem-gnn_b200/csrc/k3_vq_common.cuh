@@ -35,8 +35,11 @@ __global__ void vq_gather_kernel(VqView q, int32_t* best, const int32_t* cand, c
 __global__ void vq_rescan_kernel(VqView q, int32_t* best, const float* e2, double* partials, int nblk,
                                  const int32_t* open_list, const int32_t* open_count,
                                  unsigned long long* stats);
+constexpr int VQ_GATHER_ROWS = 4;    // rows per gather WARP = per commitment partial / open-list entry
+constexpr int VQ_SQ_CHUNKS = 128;    // first-stage CTAs of the commitment reduction
 constexpr int VQ_CAND_CAP = 8;   // candidate slots per row written by the tcgen05 path
-__global__ void vq_sqerr_reduce_kernel(const double* partials, int nblk, double* sq_err);
+__global__ void vq_sqerr_chunk_kernel(const double* partials, int nblk, double* chunk_sums);
+__global__ void vq_sqerr_reduce_kernel(const double* chunk_sums, int nchunks, double* sq_err);
 
 // path 2 (k3_vq_tc.cu): returns 0 on success
 bool vq_tc_supported(const VqView& q);

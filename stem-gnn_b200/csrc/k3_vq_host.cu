@@ -9,7 +9,7 @@ using namespace stemgnn;
 namespace {
 struct VqPlan {
     int64_t items;   // heads * rows
-    int64_t nblk;    // gather CTAs per head
+    int64_t nblk;    // gather warps (entries of VQ_GATHER_ROWS rows) per head
     int path;
 };
 
@@ -28,7 +28,7 @@ int make_view(const stemgnn_vq_assign_args* a, VqView& q, VqPlan& p) {
     q.ind = a->ind; q.ind_row_stride = a->ind_row_stride; q.ind_head_stride = a->ind_head_stride;
     q.quantize = a->quantize; q.q_row_stride = a->q_row_stride; q.q_head_stride = a->q_head_stride;
     p.items = a->heads * a->rows;
-    p.nblk = (a->rows + 7) / 8;
+    p.nblk = (a->rows + VQ_GATHER_ROWS - 1) / VQ_GATHER_ROWS;
     p.path = a->path;
     if (p.path == 0) p.path = vq_tc_supported(q) ? 2 : 1;
     if (p.path == 2 && !vq_tc_supported(q)) {
@@ -45,6 +45,7 @@ size_t base_bytes(const VqView& q, const VqPlan& p) {
     b += align_up((size_t)p.items * 4, 256);                         // best
     b += align_up((size_t)q.heads * (size_t)(p.nblk > 0 ? p.nblk : 1) * 8, 256);  // partials
     b += align_up((size_t)q.heads * (size_t)(p.nblk > 0 ? p.nblk : 1) * 4, 256);  // open_list
+    b += align_up((size_t)q.heads * VQ_SQ_CHUNKS * 8, 256);                        // commitment chunk sums
     b += 256;                                                                      // open_count
     return b;
 }
@@ -92,6 +93,7 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
     int32_t* best = ws.take<int32_t>(p.items);
     double* partials = ws.take<double>((size_t)q.heads * p.nblk);
     int32_t* open_list = ws.take<int32_t>((size_t)q.heads * p.nblk);
+    double* chunk_sums = ws.take<double>((size_t)q.heads * VQ_SQ_CHUNKS);
     int32_t* open_count = ws.take<int32_t>(1);
     cudaMemsetAsync(open_count, 0, 4, stream);
 
@@ -109,7 +111,7 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
         rc = vq_assign_tc(q, e2, best, &cand, ws.base + ws.off, workspace_bytes - ws.off, stream);
         if (rc) return rc;
     }
-    dim3 ggrid((unsigned)p.nblk, (unsigned)q.heads);
+    dim3 ggrid((unsigned)((p.nblk + 7) / 8), (unsigned)q.heads);      // one warp per entry of VQ_GATHER_ROWS rows
     SG_LAUNCH(vq_gather_kernel<<<ggrid, 256, 0, stream>>>(
         q, best, cand, e2, a->sq_err ? partials : nullptr, open_list, open_count,
         reinterpret_cast<unsigned long long*>(a->stats)));
@@ -117,8 +119,10 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
         SG_LAUNCH(vq_rescan_kernel<<<(unsigned)sm_count(), 1024, 0, stream>>>(
             q, best, e2, a->sq_err ? partials : nullptr, (int)p.nblk, open_list, open_count,
             reinterpret_cast<unsigned long long*>(a->stats)));
-    if (a->sq_err)
-        SG_LAUNCH(vq_sqerr_reduce_kernel<<<(unsigned)q.heads, 256, 0, stream>>>(partials, (int)p.nblk, a->sq_err));
+    if (a->sq_err) {
+        SG_LAUNCH(vq_sqerr_chunk_kernel<<<dim3(VQ_SQ_CHUNKS, (unsigned)q.heads), 256, 0, stream>>>(partials, (int)p.nblk, chunk_sums));
+        SG_LAUNCH(vq_sqerr_reduce_kernel<<<(unsigned)q.heads, 256, 0, stream>>>(chunk_sums, VQ_SQ_CHUNKS, a->sq_err));
+    }
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

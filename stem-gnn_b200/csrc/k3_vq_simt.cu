@@ -234,62 +234,152 @@ __device__ __forceinline__ float gather_row(const float* __restrict__ xp, const 
     return s;
 }
 
-__global__ void __launch_bounds__(256)
+// best == -1: settle the row from its candidate list (about 1 row in 20) with the reference's fp32
+// formula, first index winning ties.  Returns the code, or -2 when only the exact scan can decide.
+// The candidate ids arrive in one 32-byte load and all candidate code rows are in flight together
+// (walked one by one -- id, then row, then the next id -- a settled row took three times as long as a
+// plain one and held its warp's other rows back).  Every (row, code) dot product is summed in
+// warp_dot's order, so a pair scores the same wherever it is evaluated.  Out of line: inlined four
+// times it pushed the gather kernel into spills.
+__device__ __noinline__ int settle_row(const VqView& q, const float* __restrict__ xp, const float* __restrict__ E,
+                                       const float* __restrict__ e2h, const int32_t* __restrict__ cand_row, int lane) {
+    const int mine = lane < VQ_CAND_CAP ? cand_row[lane] : -1;
+    const unsigned invalid = __ballot_sync(0xffffffffu, mine < 0);
+    const int n = __ffs(invalid) - 1;                      // ids are -1 padded behind the last one; lanes >= CAP are -1
+    int c[VQ_CAND_CAP];
+#pragma unroll
+    for (int j = 0; j < VQ_CAND_CAP; ++j) c[j] = __shfl_sync(0xffffffffu, mine, j);
+    float dot[VQ_CAND_CAP], x2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < VQ_CAND_CAP; ++j) dot[j] = 0.f;
+    const bool v4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
+    if (v4) {
+        for (int d = lane * 4; d < q.D; d += 128) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(xp + d));
+            float4 w[VQ_CAND_CAP];
+#pragma unroll
+            for (int j = 0; j < VQ_CAND_CAP; ++j)
+                w[j] = j < n ? __ldg(reinterpret_cast<const float4*>(E + (int64_t)c[j] * q.D + d))
+                             : make_float4(0.f, 0.f, 0.f, 0.f);
+            x2 = fmaf(u.x, u.x, x2); x2 = fmaf(u.y, u.y, x2); x2 = fmaf(u.z, u.z, x2); x2 = fmaf(u.w, u.w, x2);
+#pragma unroll
+            for (int j = 0; j < VQ_CAND_CAP; ++j) {
+                dot[j] = fmaf(u.x, w[j].x, dot[j]); dot[j] = fmaf(u.y, w[j].y, dot[j]);
+                dot[j] = fmaf(u.z, w[j].z, dot[j]); dot[j] = fmaf(u.w, w[j].w, dot[j]);
+            }
+        }
+    } else {
+        for (int d = lane; d < q.D; d += 32) {
+            const float u = __ldg(xp + d);
+            x2 = fmaf(u, u, x2);
+#pragma unroll
+            for (int j = 0; j < VQ_CAND_CAP; ++j)
+                if (j < n) dot[j] = fmaf(u, __ldg(E + (int64_t)c[j] * q.D + d), dot[j]);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x2 += __shfl_xor_sync(0xffffffffu, x2, o);
+    if (q.metric != 0) x2 = 0.f;
+    float bs = -INFINITY;
+    int bi = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < VQ_CAND_CAP; ++j) {
+        float t = dot[j];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (j < n) {
+            const float sc = vq_score(q.metric, x2, e2h[c[j]], t);
+            if (sc > bs || (sc == bs && c[j] < bi)) { bs = sc; bi = c[j]; }
+        }
+    }
+    return bi < q.K ? bi : -2;
+}
+
+// GR rows per warp: the chain best[row] -> code row address -> loads -> stores is two dependent memory
+// latencies long; all GR index loads go first, then the x and code segments of every row are in
+// flight together.  A warp is its own unit of bookkeeping (one commitment partial, one open-list
+// entry per warp) and the kernel has NO CTA barrier: with per-CTA partials the top stall was
+// `barrier` (7.6 warps per issue, ncu) -- every warp waited for the slowest of its CTA, the one that
+// had a row to settle, and the idle warps held the SM's occupancy.
+__global__ void __launch_bounds__(256, 3)
 vq_gather_kernel(VqView q, int32_t* __restrict__ best, const int32_t* __restrict__ cand,
                  const float* __restrict__ e2, double* __restrict__ partials,
                  int32_t* __restrict__ open_list, int32_t* __restrict__ open_count,
                  unsigned long long* __restrict__ stats) {
-    __shared__ double wsum[8];
+    constexpr int GR = VQ_GATHER_ROWS;
     const int w = threadIdx.x >> 5, lane = lane_id();
     const int64_t h = blockIdx.y;
-    const int64_t m = (int64_t)blockIdx.x * 8 + w;
+    const int64_t nent = (q.rows + GR - 1) / GR;
+    const int64_t ent = (int64_t)blockIdx.x * 8 + w;
+    if (ent >= nent) return;
+    const int64_t m0 = ent * GR;
     const int64_t eh = q.embed_heads == 1 ? 0 : h;
     const float* E = q.embed + eh * (int64_t)q.K * q.D;
     const float* e2h = e2 + eh * (int64_t)q.K;
-    int b = 0;
-    double part = 0.0;
-    if (m < q.rows) {
-        const int64_t flat = h * q.rows + m;
-        const float* xp = q.x + m * q.x_row_stride + h * q.x_head_stride;
-        b = best[flat];
-        if (b == -1) {
-            const bool vec4 = (q.D & 3) == 0 && ((reinterpret_cast<uintptr_t>(xp) | reinterpret_cast<uintptr_t>(E)) & 15) == 0;
-            const float x2 = q.metric == 0 ? warp_dot(xp, xp, q.D, vec4, lane) : 0.f;
-            float bs = -INFINITY;
-            int bi = 0x7fffffff;
-            for (int j = 0; j < VQ_CAND_CAP; ++j) {
-                const int c = cand[flat * VQ_CAND_CAP + j];
-                if (c < 0) break;
-                const float s = vq_score(q.metric, x2, e2h[c], warp_dot(xp, E + (int64_t)c * q.D, q.D, vec4, lane));
-                if (s > bs || (s == bs && c < bi)) { bs = s; bi = c; }
-            }
+    const float* x0 = q.x + m0 * q.x_row_stride + h * q.x_head_stride;
+    float* q0 = q.quantize ? q.quantize + m0 * q.q_row_stride + h * q.q_head_stride : nullptr;
+    int b[GR];
+#pragma unroll
+    for (int r = 0; r < GR; ++r) b[r] = m0 + r < q.rows ? best[h * q.rows + m0 + r] : -3;
+    bool open = false;
+#pragma unroll
+    for (int r = 0; r < GR; ++r) {
+        if (b[r] == -1) {
+            const int64_t flat = h * q.rows + m0 + r;
+            b[r] = settle_row(q, x0 + r * q.x_row_stride, E, e2h, cand + flat * VQ_CAND_CAP, lane);
             if (lane == 0 && stats) atomicAdd(stats + 0, 1ull);
-            b = bi < q.K ? bi : -2;
-            if (b == -2 && lane == 0) best[flat] = -2;      // NaN scores: the exact scan decides
+            if (b[r] == -2 && lane == 0) best[flat] = -2;      // NaN scores: the exact scan decides
         }
-        if (b >= 0) {
-            float* qp = q.quantize ? q.quantize + m * q.q_row_stride + h * q.q_head_stride : nullptr;
-            part = (double)gather_row(xp, E + (int64_t)b * q.D, qp, q.D, lane);
-            if (lane == 0 && q.ind) q.ind[m * q.ind_row_stride + h * q.ind_head_stride] = (int64_t)b;
-        }
+        open = open || b[r] == -2;
     }
-    const int any_open = __syncthreads_or(b == -2);
-    if (any_open && threadIdx.x == 0)
-        open_list[atomicAdd(open_count, 1)] = (int32_t)(h * gridDim.x + blockIdx.x);
+    float s[GR];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    if (lane == 0) wsum[w] = part;
-    __syncthreads();
-    if (threadIdx.x == 0 && partials) {
-        double t = 0.0;
+    for (int r = 0; r < GR; ++r) s[r] = 0.f;
+    const bool vec4 = (q.D & 3) == 0 && ((q.x_row_stride | q.q_row_stride) & 3) == 0 &&
+                      ((reinterpret_cast<uintptr_t>(E) | reinterpret_cast<uintptr_t>(x0) | reinterpret_cast<uintptr_t>(q0)) & 15) == 0;
+    if (vec4) {
+        for (int d = lane * 4; d < q.D; d += 128) {
+            float4 ev[GR], xv[GR];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) t += wsum[i];
-        partials[h * gridDim.x + blockIdx.x] = t;
+            for (int r = 0; r < GR; ++r)
+                if (b[r] >= 0) {
+                    ev[r] = __ldg(reinterpret_cast<const float4*>(E + (int64_t)b[r] * q.D + d));
+                    xv[r] = __ldg(reinterpret_cast<const float4*>(x0 + r * q.x_row_stride + d));
+                }
+#pragma unroll
+            for (int r = 0; r < GR; ++r)
+                if (b[r] >= 0) {
+                    float df;
+                    df = ev[r].x - xv[r].x; s[r] = fmaf(df, df, s[r]); df = ev[r].y - xv[r].y; s[r] = fmaf(df, df, s[r]);
+                    df = ev[r].z - xv[r].z; s[r] = fmaf(df, df, s[r]); df = ev[r].w - xv[r].w; s[r] = fmaf(df, df, s[r]);
+                    if (q0) *reinterpret_cast<float4*>(q0 + r * q.q_row_stride + d) = ev[r];
+                }
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < GR; ++r)
+            if (b[r] >= 0)
+                s[r] = gather_row(x0 + r * q.x_row_stride, E + (int64_t)b[r] * q.D,
+                                  q0 ? q0 + r * q.q_row_stride : nullptr, q.D, lane);
+    }
+    double part = 0.0;
+#pragma unroll
+    for (int r = 0; r < GR; ++r) {          // rows in index order: the commitment sum stays deterministic
+        if (b[r] < 0) continue;
+        double pr = (double)s[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) pr += __shfl_xor_sync(0xffffffffu, pr, o);
+        part += pr;
+        if (lane == 0 && q.ind) q.ind[(m0 + r) * q.ind_row_stride + h * q.ind_head_stride] = (int64_t)b[r];
+    }
+    if (lane == 0) {
+        if (open) open_list[atomicAdd(open_count, 1)] = (int32_t)(h * nent + ent);
+        if (partials) partials[h * nent + ent] = part;
     }
 }
 
 // ---- exact scan of the rows left open: one CTA per row at a time, over the whole GPU ----------
-// An entry of open_list is a gather CTA (8 consecutive rows of one head) with at least one row at
+// An entry of open_list is a gather warp (VQ_GATHER_ROWS consecutive rows of one head) with at least one row at
 // best == -2.  A CTA of 32 warps scans all K codes for each such row (warp w takes the groups of
 // eight codes w, w+32, ...: the scan is bound by L2 latency, so 256 code rows are in flight per
 // SM; first index wins ties; an all-NaN row takes index 0 like argmax does), writes the row's
@@ -313,8 +403,8 @@ vq_rescan_kernel(VqView q, int32_t* __restrict__ best, const float* __restrict__
         const float* E = q.embed + eh * (int64_t)q.K * q.D;
         const float* e2h = e2 + eh * (int64_t)q.K;
         double extra = 0.0;
-        for (int r = 0; r < 8; ++r) {
-            const int64_t m = bx * 8 + r;
+        for (int r = 0; r < VQ_GATHER_ROWS; ++r) {
+            const int64_t m = bx * VQ_GATHER_ROWS + r;
             if (m >= q.rows) break;
             const int64_t flat = h * q.rows + m;
             if (best[flat] != -2) continue;                   // CTA-uniform
@@ -361,20 +451,39 @@ vq_rescan_kernel(VqView q, int32_t* __restrict__ best, const float* __restrict__
     }
 }
 
-// one CTA per head: fixed-order reduction of the per-CTA partials
-__global__ void __launch_bounds__(256)
-vq_sqerr_reduce_kernel(const double* __restrict__ partials, int nblk, double* __restrict__ sq_err) {
+// fixed-order reduction of the per-warp partials of one head, in two stages: VQ_SQ_CHUNKS CTAs sum
+// contiguous chunks (thread-strided, then a tree), one CTA sums the chunk sums.  (One CTA walking all
+// partials of a 2.5M-row call took 116 us.)
+
+__device__ __forceinline__ double block_sum_256(double t) {
     __shared__ double sm[256];
-    const double* p = partials + (int64_t)blockIdx.x * nblk;
-    double t = 0.0;
-    for (int i = threadIdx.x; i < nblk; i += 256) t += p[i];
     sm[threadIdx.x] = t;
     __syncthreads();
     for (int s = 128; s > 0; s >>= 1) {
         if (threadIdx.x < s) sm[threadIdx.x] += sm[threadIdx.x + s];
         __syncthreads();
     }
-    if (threadIdx.x == 0) sq_err[blockIdx.x] = sm[0];
+    return sm[0];
+}
+
+__global__ void __launch_bounds__(256)
+vq_sqerr_chunk_kernel(const double* __restrict__ partials, int nblk, double* __restrict__ chunk_sums) {
+    const double* p = partials + (int64_t)blockIdx.y * nblk;
+    const int per = (nblk + VQ_SQ_CHUNKS - 1) / VQ_SQ_CHUNKS;
+    const int lo = blockIdx.x * per, hi = lo + per < nblk ? lo + per : nblk;
+    double t = 0.0;
+    for (int i = lo + threadIdx.x; i < hi; i += 256) t += p[i];
+    t = block_sum_256(t);
+    if (threadIdx.x == 0) chunk_sums[blockIdx.y * VQ_SQ_CHUNKS + blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(256)
+vq_sqerr_reduce_kernel(const double* __restrict__ chunk_sums, int nchunks, double* __restrict__ sq_err) {
+    const double* p = chunk_sums + (int64_t)blockIdx.x * nchunks;
+    double t = 0.0;
+    for (int i = threadIdx.x; i < nchunks; i += 256) t += p[i];
+    t = block_sum_256(t);
+    if (threadIdx.x == 0) sq_err[blockIdx.x] = t;
 }
 
 // ---- backward: g_x = g_q + g_loss*coef*(x - q) ---------------------------------------------------

@@ -1,0 +1,145 @@
+"""GPU: the BASELINE.json configurations at their real widths against the oracle restatement.
+
+* C1  Cora-shaped finetune step (2,708 nodes, 10,556 edges, 1,433 feats -> 768, shipped VQ frozen):
+      1,433 is not a multiple of 4, so the first layer exercises the scalar aggregation path and the
+      nn.Linear route; the second layer and the VQ projections run on K5/K6.
+* C3  one sampled pretrain mini-batch of the mix graph (768-wide, 237 edge types given as a type
+      table) through the encoder and the shipped VQ (4 x 128 x 768 cosine, learnable codebook).
+Bars: 1e-5 of the output scale for fp32 values, identical code indices except where the two best
+cosine scores are closer than 1e-6 (north_star)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+import stemgnn_b200 as S
+from oracle.encoder_ref import EncoderRef
+from oracle.vq_ref import vq_forward_ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close(a, b, tol=1e-5, what=""):
+    a, b = a.detach().cpu().double(), b.detach().cpu().double()
+    scale = b.abs().max().item() + 1e-30
+    err = (a - b).abs().max().item() / scale
+    assert err < tol, f"{what}: max error {err:.3e} of the output scale"
+
+
+def _close_l2(a, b, tol, what=""):
+    """Gradients upstream of a ReLU: a pre-activation within the 1e-6 dense-layer error of zero lands on
+    either side on the two machines (31M activations here: about a hundred do), and each such flip
+    moves one column sum by one whole term -- against column sums that cancel down to ~200 terms'
+    worth, that is an l2 error of ~2e-3 on the BatchNorm bias gradient (measured 1.7e-3).  Such
+    tensors are compared in the l2 norm with room for that; a wrong formula is off by O(1)."""
+    a, b = a.detach().cpu().double(), b.detach().cpu().double()
+    err = ((a - b).norm() / (b.norm() + 1e-30)).item()
+    assert err < tol, f"{what}: relative l2 error {err:.3e}"
+
+
+def _pair(in_dim, hid, layers, normalize, seed):
+    torch.manual_seed(seed)
+    ref = EncoderRef(in_dim, hid, nn.ReLU, layers, backbone="sage", normalize=normalize, dropout=0.0)
+    enc = S.Encoder(in_dim, hid, nn.ReLU, layers, backbone="sage", normalize=normalize, dropout=0.0)
+    assert set(ref.state_dict()) == set(enc.state_dict())
+    enc.load_state_dict(ref.state_dict())
+    return ref.train(), enc.to(DEV).train()
+
+
+def _shipped_vq(dim, codes, seed, frozen):
+    torch.manual_seed(seed)
+    vq = S.VectorQuantize(dim=dim, codebook_size=codes, codebook_dim=dim, heads=4, separate_codebook_per_head=True,
+                          decay=0.8, commitment_weight=10, use_cosine_sim=True, orthogonal_reg_weight=0,
+                          kmeans_init=False, ema_update=False, learnable_codebook=True)
+    state = {k: getattr(vq._codebook, k).detach().clone() for k in ("embed", "embed_avg", "cluster_size")}
+    pin = nn.Linear(dim, 4 * dim); pout = nn.Linear(4 * dim, dim)
+    pin.load_state_dict(vq.project_in.state_dict()); pout.load_state_dict(vq.project_out.state_dict())
+    return vq.to(DEV).train(not frozen), state, pin, pout
+
+
+def _index_mismatch_is_a_near_tie(h, embed, ind_gpu, ind_ref):
+    """rows where the indices differ must have their two candidate scores within 1e-6 (fp64)."""
+    bad = (ind_gpu != ind_ref).nonzero()
+    assert bad.size(0) <= max(4, ind_ref.numel() // 10000), f"{bad.size(0)} index mismatches"
+    hn = torch.nn.functional.normalize(h.double().view(h.size(0), 4, -1), dim=-1)
+    for r, hd in bad.tolist():
+        sa = (hn[r, hd] * embed[hd, ind_gpu[r, hd]].double()).sum()
+        sb = (hn[r, hd] * embed[hd, ind_ref[r, hd]].double()).sum()
+        assert abs(float(sa - sb)) < 1e-6
+
+
+def test_c1_cora_shaped_finetune_step():
+    n, e, f, hid = 2708, 10556, 1433, 768
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, f, generator=g)
+    ei = torch.randint(0, n, (2, e), generator=g)
+    ref, enc = _pair(f, hid, 2, "none", 1)                      # config/finetune.yaml:4 normalize: none
+    vq, state, pin, pout = _shipped_vq(hid, 128, 2, frozen=True)
+    up = torch.randn(n, hid, generator=g)
+
+    z_r = ref(x, ei)
+    q_r, ind_r, loss_r, _ = vq_forward_ref(z_r, state, heads=4, separate_codebook_per_head=True, cosine=True,
+                                           training=False, ema_update=False, project_in=pin, project_out=pout)
+    ((z_r + q_r) * up).sum().backward()
+
+    z = enc(x.to(DEV), ei.to(DEV))
+    q, ind, loss, _ = vq(z)
+    ((z + q) * up.to(DEV)).sum().backward()
+
+    _close(z, z_r)
+    assert float(loss) == 0.0 and tuple(ind.shape) == (n, 4) and ind.dtype == torch.int64
+    _index_mismatch_is_a_near_tie(pin(z_r).detach(), state["embed"], ind.cpu(), ind_r)
+    same = (ind.cpu() == ind_r).all(dim=1)
+    _close(q[same.to(DEV)], q_r[same])
+    for (k, p), (_, pr) in zip(enc.named_parameters(), ref.named_parameters()):
+        assert (p.grad is None) == (pr.grad is None), k        # normalize 'none': the BatchNorm is never called
+        if pr.grad is not None:
+            _close(p.grad, pr.grad, 2e-5)
+
+
+def test_c3_mix_minibatch_encoder_and_shipped_vq():
+    # a sampled mini-batch of the mix graph, scaled to run the CPU oracle in seconds
+    n_all, e_all, f, t = 40000, 260000, 768, 237
+    g = torch.Generator().manual_seed(3)
+    ei_all = torch.randint(0, n_all, (2, e_all), generator=g)
+    text = torch.randn(n_all, f, generator=g)
+    table = torch.randn(t, f, generator=g)
+    etype = torch.randint(0, t, (e_all,), generator=g)
+    smp = S.NeighborSampler(ei_all.to(DEV), n_all, [10, 10], seed=4)
+    n_id, ei, e_id = smp.sample(torch.randperm(n_all, generator=g)[:256])
+    x = S.gather_rows(text.to(DEV), n_id)
+    et = etype.to(DEV)[e_id]
+    assert torch.equal(x.cpu(), text[n_id.cpu()])
+    n = n_id.numel()
+    ref, enc = _pair(f, f, 2, "batch", 5)
+    vq, state, pin, pout = _shipped_vq(f, 128, 6, frozen=False)
+    up = torch.randn(n, f, generator=g)
+
+    xr = x.cpu().clone().requires_grad_(True)
+    z_r = ref(xr, ei.cpu(), table[et.cpu()])                    # the reference gathers edge_text_feat[data.xe]
+    state_r = {k: v.clone().requires_grad_(k == "embed") for k, v in state.items()}
+    q_r, ind_r, loss_r, _ = vq_forward_ref(z_r, state_r, heads=4, separate_codebook_per_head=True, cosine=True,
+                                           training=True, ema_update=False, commitment_weight=10,
+                                           learnable_codebook=True, project_in=pin, project_out=pout)
+    ((q_r * up).sum() + loss_r.sum()).backward()
+
+    xg = x.clone().requires_grad_(True)
+    z = enc(xg, ei, (table.to(DEV), et))                         # type-table form: no E x 768 tensor
+    q, ind, loss, _ = vq(z)
+    ((q * up.to(DEV)).sum() + loss.sum()).backward()
+
+    _close(z, z_r, what="z")
+    _index_mismatch_is_a_near_tie(pin(z_r).detach(), state["embed"], ind.cpu(), ind_r)
+    if bool((ind.cpu() == ind_r).all()):
+        _close(q, q_r, what="quantize")
+        _close(loss, loss_r, what="loss")
+        _close(vq._codebook.embed.grad, state_r["embed"].grad, 2e-5, "embed.grad")
+        _close(vq.project_out.weight.grad, pout.weight.grad, 2e-5, "project_out.weight.grad")
+        _close(vq.project_in.weight.grad, pin.weight.grad, 2e-5, "project_in.weight.grad")
+        for (k, p), (_, pr) in zip(reversed(list(enc.named_parameters())), reversed(list(ref.named_parameters()))):
+            if k.startswith(("layers.1", "norms.1")):
+                _close(p.grad, pr.grad, 2e-5, k)
+            else:
+                _close_l2(p.grad, pr.grad, 1e-2, k)
+        _close_l2(xg.grad, xr.grad, 1e-2, "x.grad")
