@@ -137,8 +137,13 @@ def test_c3_mix_minibatch_encoder_and_shipped_vq():
         _close(vq._codebook.embed.grad, state_r["embed"].grad, 2e-5, "embed.grad")
         _close(vq.project_out.weight.grad, pout.weight.grad, 2e-5, "project_out.weight.grad")
         _close(vq.project_in.weight.grad, pin.weight.grad, 2e-5, "project_in.weight.grad")
+        wscale = enc.layers[1].lin_l.weight.grad.abs().max().item()
         for (k, p), (_, pr) in zip(reversed(list(enc.named_parameters())), reversed(list(ref.named_parameters()))):
-            if k.startswith(("layers.1", "norms.1")):
+            if k.endswith("lin_l.bias"):
+                # a bias in front of BatchNorm has a gradient of exactly zero (the column mean is
+                # removed): both sides hold rounding noise, there is nothing to compare
+                assert p.grad.abs().max().item() < 1e-4 * wscale and pr.grad.abs().max().item() < 1e-4 * wscale, k
+            elif k.startswith(("layers.1", "norms.1")):
                 _close(p.grad, pr.grad, 2e-5, k)
             else:
                 _close_l2(p.grad, pr.grad, 1e-2, k)
