@@ -352,6 +352,19 @@ int stemgnn_l2norm_forward(int64_t rows, int64_t dim, const float* x, float eps,
 int stemgnn_l2norm_backward(int64_t rows, int64_t dim, const float* g, const float* y, const float* norm,
                             float eps, float* gx, stemgnn_stream_t stream);
 
+/* ------------------------------------------------------------------ K12: negative edge sampling
+ * Replaces torch_geometric.utils.negative_sampling(pos_edge_index, num_nodes) (2.3.0, sparse method)
+ * called at STEM-GNN/model/pt_model.py:60.  `num_candidates` Philox draws (keyed by *seed, a device
+ * uint64) over the N(N-1) ordered pairs without self loops; a candidate survives if it is not an edge
+ * of edge_index and is the first of its value; survivors are written in candidate order into
+ * neg_out [2, capacity] (row 1 at neg_out + capacity), count_out (device int64) = number of survivors
+ * (may exceed capacity: only the first `capacity` are stored).  The caller sizes num_candidates like
+ * PyG (1.1 * wanted / (1 - E / N(N-1))) and retries with more if the count falls short. */
+int stemgnn_negative_sampling_workspace(int64_t num_edges, int64_t num_candidates, size_t* bytes_host);
+int stemgnn_negative_sampling(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes,
+                              int64_t num_candidates, int64_t capacity, const uint64_t* seed, int64_t* neg_out,
+                              int64_t* count_out, void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

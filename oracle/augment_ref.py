@@ -30,3 +30,17 @@ def dropout_adj_ref(edge_index, edge_attr, rand, p, force_undirected):
 def mask_feature_ref(x, mask, fill_value=0.0):
     """`x.masked_fill(~mask, fill_value)` with mask broadcast as [1,F] (col), [N,1] (row) or [N,F]."""
     return x.masked_fill(~mask, fill_value)
+
+
+def check_negative_edges(edge_index, num_nodes, neg):
+    """Properties every output of torch_geometric.utils.negative_sampling (2.3.0) has, whatever its
+    random draws were: no self loops, no positive edge, no pair twice, ids in range."""
+    import numpy as np
+    ei, neg = np.asarray(edge_index), np.asarray(neg)
+    assert neg.shape[0] == 2
+    assert ((neg >= 0) & (neg < num_nodes)).all()
+    assert (neg[0] != neg[1]).all(), "self loop drawn"
+    pos = set((ei[0] * num_nodes + ei[1]).tolist())
+    ids = neg[0] * num_nodes + neg[1]
+    assert not pos.intersection(ids.tolist()), "a positive edge was returned"
+    assert len(np.unique(ids)) == ids.size, "a pair was returned twice"

@@ -40,6 +40,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batches", type=int, default=0, help="0 = the full epoch (953)")
     ap.add_argument("--cpu-batches", type=int, default=3)
+    ap.add_argument("--encoder-vq-only", action="store_true",
+                    help="stand-in loss on the encoder + VQ only (the earlier form of this script) instead of the "
+                         "reference's five pretrain losses")
     ap.add_argument("--trace", type=int, default=5, help="batches traced call by call after the timed loop")
     args = ap.parse_args()
     import torch.distributed as dist
@@ -72,10 +75,39 @@ def main():
                           decay=0.8, commitment_weight=10, use_cosine_sim=True, orthogonal_reg_weight=1,
                           orthogonal_reg_max_codes=32, orthogonal_reg_active_codes_only=False, kmeans_init=False,
                           ema_update=False).to(dev).train()
-    params = list(enc.parameters()) + list(vq.parameters())
+    # the rest of PretrainModel (model/pt_model.py:12-23) and its decoders (pretrain.py:121-123)
+    import copy
+    feat_dec = nn.Linear(HID, F).to(dev)
+    topo_dec = S.InnerProductDecoder(hidden_dim=HID, output_dim=HID).to(dev)
+    topo_sem_dec = nn.Linear(2 * HID, HID).to(dev)
+    sem_enc = copy.deepcopy(enc)
+    sem_proj = nn.Linear(HID, HID).to(dev)
+    full = not args.encoder_vq_only
+    modules = [enc, vq] + ([feat_dec, topo_dec, topo_sem_dec, sem_proj] if full else [])
+    params = [p for m in modules for p in m.parameters()]
     opt = torch.optim.AdamW(params, lr=1e-4, capturable=True)
-
+    EPS, RATIO = 1e-15, 0.1                                           # pt_model.py:8, utils/args.py:46
     ar_events = []
+
+    def losses_of(z, quantize, commit, x, ei, et, bs):
+        """PretrainModel.forward (pt_model.py:128-157) with the default weights of utils/args.py:44-51."""
+        query = quantize
+        feat = nn.functional.mse_loss(feat_dec(query[:bs]), x[:bs])                      # :42-43
+        e = ei.size(1)
+        k = max(int(e * RATIO), 1)
+        pos = ei[:, torch.randperm(e, device=dev)[:k]]                                   # :51-57
+        neg = S.negative_sampling(pos, z.size(0))                                        # :60
+        topo = -torch.log(topo_dec(query, pos, sigmoid=True) + EPS).mean() \
+               - torch.log(1 - topo_dec(query, neg, sigmoid=True) + EPS).mean()          # :62-65
+        pick = torch.randperm(e, device=dev)[:k]                                         # :72-78
+        target = S.gather_rows(etable_d, et[pick])                                       # edge_attr[perm]
+        topo_sem = nn.functional.mse_loss(S.edge_concat_linear(query, ei[:, pick], topo_sem_dec), target)   # :80-81
+        with torch.no_grad():
+            zs = sem_enc(x, ei, (etable_d, et))                                          # :92
+        h = sem_proj(quantize)
+        zs, h = nn.functional.normalize(zs[:bs], dim=-1), nn.functional.normalize(h[:bs], dim=-1)
+        sem = (1 - (zs * h).sum(-1)).mean()                                              # :95-99
+        return 100 * feat + 0.01 * topo + 100 * topo_sem + 1 * sem + commit.sum()        # pretrain.py:51-58
 
     def step(batch):
         x = S.gather_rows(text_d, batch.x)                            # node_text_feat[data.x]
@@ -85,7 +117,10 @@ def main():
         opt.zero_grad(set_to_none=True)
         z = enc(aug_x, aug_ei, (etable_d, aug_t))                     # edge_text_feat[data.xe] as a table
         q, ind, vq_loss, _ = vq(z)
-        loss = q.square().mean() + vq_loss.sum()
+        if full:
+            loss = losses_of(z, q, vq_loss, x, batch.edge_index, batch.xe, batch.batch_size)
+        else:
+            loss = q.square().mean() + vq_loss.sum()
         loss.backward()
         if world > 1:                                                 # one flat all-reduce of the gradients
             ar0 = torch.cuda.Event(enable_timing=True); ar1 = torch.cuda.Event(enable_timing=True)
@@ -98,8 +133,14 @@ def main():
                 p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
             ar1.record()
             ar_events.append((ar0, ar1))
+        if full:
+            nn.utils.clip_grad_norm_(params, 1.0)                     # pretrain.py:62
         opt.step()
-        return loss, aug_ei.size(1), x.size(0)
+        if full:
+            with torch.no_grad():                                     # ema_update_sem_encoder, pt_model.py:104-106
+                torch._foreach_mul_(list(sem_enc.parameters()), 0.99)
+                torch._foreach_add_(list(sem_enc.parameters()), list(enc.parameters()), alpha=0.01)
+        return loss, aug_ei.size(1) + (batch.edge_index.size(1) if full else 0), x.size(0)
 
     total = len(loader) if args.batches <= 0 else min(args.batches, len(loader))
     it = iter(loader)
@@ -140,7 +181,7 @@ def main():
                 wall_s=wall, vq_nodes_per_s=nodes / ms * 1e3, dtype="f32", data="synthetic",
                 grad_allreduce_ms_per_step=ar_ms, gpu_launches=launches / done, final_loss=float(loss.detach()),
                 config=dict(workload="pretrain mix (195,095 nodes, 1,274,551 edges, 768 feats, 237 edge types), "
-                            "mini-batches of 1,024 seeds, fan-out [10,10], 2-layer SAGE 768-768 + shipped VQ 4x128x768",
+                            "mini-batches of 1,024 seeds, fan-out [10,10], 2-layer SAGE 768-768 + shipped VQ 4x128x768" + (", the reference's five pretrain losses (feature / topology / edge-semantics / tree-semantics reconstruction + commitment), clip, AdamW, EMA teacher encoder" if full else ", stand-in loss"),
                             batches_per_epoch_per_rank=len(loader), mean_nodes=nodes / done / world,
                             mean_aug_edges=edges / done / world,
                             parallelism="single GPU" if world == 1 else f"dp{world}: replicas over mini-batches, flat gradient all-reduce (NCCL)"))

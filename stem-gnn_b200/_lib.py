@@ -92,6 +92,8 @@ SIGNATURES = {
                                               C.POINTER(_i64), C.POINTER(C.c_size_t)]),
     "stemgnn_node_map_init": (_i32, [_vp, _i64, _vp]),
     "stemgnn_neighbor_sample": (_i32, [C.POINTER(NeighborSampleArgs), _vp, C.c_size_t, _vp]),
+    "stemgnn_negative_sampling_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
+    "stemgnn_negative_sampling": (_i32, [_vp, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
     "stemgnn_l2norm_forward": (_i32, [_i64, _i64, _vp, _f32, _vp, _vp, _vp]),
     "stemgnn_l2norm_backward": (_i32, [_i64, _i64, _vp, _vp, _vp, _f32, _vp, _vp]),
 }

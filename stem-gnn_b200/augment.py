@@ -153,3 +153,60 @@ def mask_feature(x, p=0.5, mode="col", fill_value=0., training=True):
         return _MaskFill.apply(x, None, mask, 0.0, float(fill_value), False), mask.view(1, -1)
     out, mask = _MaskFill.apply(x, None, None, float(p), float(fill_value), True)
     return out, mask
+
+
+def negative_sampling(edge_index, num_nodes=None, num_neg_samples=None, method="sparse",
+                      force_undirected=False):
+    """torch_geometric.utils.negative_sampling (2.3.0) as the reference calls it
+    (`negative_sampling(pos_edge_index, z.size(0))`, model/pt_model.py:60): up to `num_neg_samples`
+    (default: as many as there are edges) distinct node pairs (i, j), i != j, that are not edges.
+    Both PyG methods ("sparse", "dense") map to the one device implementation (K12)."""
+    if force_undirected:
+        raise NotImplementedError("negative_sampling(force_undirected=True) is outside the hot path")
+    assert method in ["sparse", "dense"]
+    if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.size(0) != 2:
+        raise ValueError("edge_index must be an int64 tensor of shape [2, E]")
+    if not edge_index.is_cuda:
+        raise _lib.StemGnnError("negative_sampling: edge_index must be a CUDA tensor (no CPU fallback)")
+    L = _lib.lib()
+    ei = edge_index.contiguous()
+    dev, E = ei.device, ei.size(1)
+    N = int(num_nodes) if num_nodes is not None else (int(ei.max()) + 1 if E else 0)
+    population = N * N - N
+    want = E if num_neg_samples is None else int(num_neg_samples)
+    if population <= 0 or E >= population or want <= 0:
+        return ei.new_empty((2, 0))
+    want = min(want, population - E)
+    prob = 1.0 - E / population
+    out = count = None
+    for attempt in range(3):                                      # PyG retries three times as well
+        m = min(int(1.1 * (1.5 ** attempt) * want / prob) + 16, (1 << 30) - E - 1)
+        need = C.c_size_t(0)
+        _lib.check(L.stemgnn_negative_sampling_workspace(E, m, C.byref(need)))
+        ws = _lib.workspace(need.value, dev)
+        out = torch.empty(2, want, dtype=torch.int64, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+        seed = _seed_tensor(dev)
+        with _lib.traced("negative_sampling", E * 16 + m * 24 + want * 16, 0, 6):
+            _lib.check(L.stemgnn_negative_sampling(_lib.ptr(ei), E, N, m, want, _lib.ptr(seed), _lib.ptr(out),
+                                                   _lib.ptr(cnt), _lib.ptr(ws), need.value, _lib.stream()))
+        count = int(cnt.item())
+        if count >= want:
+            return out
+    return out[:, :count]
+
+
+def edge_concat_linear(z, edge_index, linear):
+    """`linear(torch.cat([z[edge_index[0]], z[edge_index[1]]], dim=-1))` -- the topo_sem decoder input of
+    model/pt_model.py:80-81 -- without the E x 2D concatenation: two row gathers (K9) feed ONE
+    two-source tensor-core GEMM (K5) against the two halves of `linear.weight`."""
+    from . import dense
+    d = z.size(1)
+    w = linear.weight
+    if w.size(1) != 2 * d:
+        raise ValueError("linear must take 2 * z.size(1) input features")
+    a = _GatherRows.apply(z, edge_index[0].contiguous())
+    b = _GatherRows.apply(z, edge_index[1].contiguous())
+    if z.is_cuda and dense.supported(d, w.size(0)):
+        return dense.linear_sum([a, b], [w[:, :d], w[:, d:]], linear.bias)
+    return linear(torch.cat([a, b], dim=-1))

@@ -9,7 +9,7 @@ import torch.nn.functional as F
 from torch import Tensor
 
 from .conv import GCNConv, GINConv, MixtureSageLayer, MySAGEConv
-from . import norm_act
+from . import dense, norm_act
 from .decoder import edge_dot
 from .graph import structure_of
 
@@ -172,9 +172,16 @@ class InnerProductDecoder(nn.Module):
         if self.proj_z:
             self.lin = nn.Linear(hidden_dim, output_dim)
 
+    def _project(self, z):
+        if not self.proj_z:
+            return z
+        w = self.lin.weight
+        if z.is_cuda and z.dtype == torch.float32 and z.dim() == 2 and dense.supported(w.size(0), w.size(1)):
+            return dense.linear_sum([z], [w], self.lin.bias)          # K5/K6 instead of torch's fp32 SGEMM
+        return self.lin(z)
+
     def forward(self, z: Tensor, edge_index: Tensor, sigmoid: bool = True) -> Tensor:
-        z = self.lin(z) if self.proj_z else z
-        return edge_dot(z, edge_index, sigmoid)
+        return edge_dot(self._project(z), edge_index, sigmoid)
 
     def forward_all(self, z: Tensor, sigmoid: bool = True) -> Tensor:
         z = self.lin(z) if self.proj_z else z

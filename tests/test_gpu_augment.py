@@ -102,3 +102,68 @@ def test_gather_rows_bit_exact(f):
     bad = torch.tensor([1, 5000, -1], device=DEV)
     out = S.gather_rows(src, bad)
     assert torch.equal(out[0], src[1]) and bool(out[1:].isnan().all())
+
+
+def test_negative_sampling_properties_and_determinism():
+    from oracle.augment_ref import check_negative_edges
+    n, e = 20000, 150000
+    ei = _graph(n, e, 8)
+    ei[1, :50] = ei[0, :50]                                 # self loops among the positives
+    ei[:, 50:100] = ei[:, 100:150]                          # duplicated positives
+    torch.manual_seed(5)
+    neg = S.negative_sampling(ei.to(DEV), n)
+    assert neg.dtype == torch.int64 and tuple(neg.shape) == (2, e)
+    check_negative_edges(ei.numpy(), n, neg.cpu().numpy())
+    torch.manual_seed(5)
+    assert torch.equal(S.negative_sampling(ei.to(DEV), n), neg)      # same torch seed, same sample
+    torch.manual_seed(6)
+    assert not torch.equal(S.negative_sampling(ei.to(DEV), n), neg)
+    few = S.negative_sampling(ei.to(DEV), n, num_neg_samples=1000)
+    assert tuple(few.shape) == (2, 1000)
+    assert S.negative_sampling(ei[:, :0].to(DEV), n).shape == (2, 0)
+
+
+def test_negative_sampling_dense_graph_and_uniformity():
+    from oracle.augment_ref import check_negative_edges
+    n = 12
+    full = torch.tensor([[i, j] for i in range(n) for j in range(n) if i != j]).t().contiguous()
+    keep = torch.randperm(full.size(1), generator=torch.Generator().manual_seed(1))[:80]
+    ei = full[:, keep]                                       # 80 of the 132 pairs are edges
+    non_edges = 132 - 80
+    hits = torch.zeros(n * n)
+    torch.manual_seed(0)
+    trials = 600
+    for _ in range(trials):
+        neg = S.negative_sampling(ei.to(DEV), n, num_neg_samples=20).cpu()
+        check_negative_edges(ei.numpy(), n, neg.numpy())
+        assert neg.size(1) == 20
+        hits[neg[0] * n + neg[1]] += 1
+    assert int((hits > 0).sum()) == non_edges               # every non-edge is reachable
+    expect = trials * 20 / non_edges
+    chi2 = float(((hits[hits > 0] - expect) ** 2 / expect).sum())
+    assert chi2 < 110, chi2                                  # 51 dof: P(chi2 > 110) ~ 3e-6
+    # more requested than exist: everything that is left comes back
+    torch.manual_seed(1)
+    allneg = S.negative_sampling(ei.to(DEV), n, num_neg_samples=1000)
+    check_negative_edges(ei.numpy(), n, allneg.cpu().numpy())
+    assert 40 <= allneg.size(1) <= non_edges            # like PyG, three rounds may leave a few undrawn
+
+
+def test_edge_concat_linear_matches_cat_linear():
+    n, e, d, o = 3000, 20011, 64, 32
+    g = torch.Generator().manual_seed(2)
+    z = torch.randn(n, d, generator=g).to(DEV).requires_grad_(True)
+    ei = torch.randint(0, n, (2, e), generator=g).to(DEV)
+    lin = torch.nn.Linear(2 * d, o).to(DEV)
+    up = torch.randn(e, o, generator=g).to(DEV)
+    out = S.edge_concat_linear(z, ei, lin)
+    out.backward(up)
+    gz, gw, gb = z.grad.clone(), lin.weight.grad.clone(), lin.bias.grad.clone()
+    z.grad = None; lin.zero_grad()
+    ref = lin(torch.cat([z[ei[0]], z[ei[1]]], dim=-1))      # pt_model.py:80-81
+    ref.backward(up)
+    scale = lambda t: t.abs().max().item()
+    assert (out - ref).abs().max().item() < 1e-5 * scale(ref)
+    assert (gz - z.grad).abs().max().item() < 2e-5 * scale(z.grad)
+    assert (gw - lin.weight.grad).abs().max().item() < 2e-5 * scale(lin.weight.grad)
+    assert (gb - lin.bias.grad).abs().max().item() < 2e-5 * scale(lin.bias.grad)
