@@ -397,7 +397,17 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
     // against 136 / 218 us); once it reaches a few MB (N=512, K=1024: 4 MB) streaming it twice as
     // often costs more than the exposed epilogue (730 vs 687 us).  STEMGNN_LIN_BM=128|256 forces one.
     static const int forced = [] { const char* e = getenv("STEMGNN_LIN_BM"); return e ? atoi(e) : 0; }();
-    const int mh = forced == 256 ? 2 : (forced == 128 ? 1 : ((size_t)n_tiles * kct * lin::W_STAGE_BYTES >= (2u << 20) ? 2 : 1));
+    // The 256-row shape is ~6 % faster per tile there, but has half as many work items: when those
+    // do not fill whole rounds of the grid the tail eats the gain (M = 43,008, N = 768: 504 items =
+    // 3.4 rounds of 148 CTAs -> 557 us against 455 us with 1,008 items of 128 rows).
+    const int sms = sm_count();
+    auto fill = [&](int mhh) {
+        const int64_t it = ((a->m + 128 * mhh - 1) / (128 * mhh)) * n_tiles;
+        const int64_t rounds = (it + sms - 1) / sms;
+        return (double)it / (double)(rounds * sms);
+    };
+    const bool wide = (size_t)n_tiles * kct * lin::W_STAGE_BYTES >= (2u << 20);
+    const int mh = forced == 256 ? 2 : (forced == 128 ? 1 : ((wide && fill(2) >= 0.93 * fill(1)) ? 2 : 1));
     const int smem_bytes = mh == 2 ? lin::Shape<2>::SMEM_BYTES : lin::Shape<1>::SMEM_BYTES;
     cudaError_t e = mh == 2
         ? cudaFuncSetAttribute(lin::lin_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes)
@@ -406,7 +416,6 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
         set_error("stemgnn_linear: cudaFuncSetAttribute(%d B smem): %s", smem_bytes, cudaGetErrorString(e));
         return STEMGNN_ECUDA;
     }
-    const int sms = sm_count();
     const int bm = 128 * mh;
     const int64_t items = ((a->m + bm - 1) / bm) * n_tiles;
     const unsigned grid = (unsigned)(items < sms ? items : sms);
