@@ -45,9 +45,16 @@ class _GatherRows(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
+        # index_add_ of the gathered rows' gradients, as a pull: rows grouped by id with the stable
+        # sort of K0, summed in position order by K1 (deterministic, no atomics)
+        from .graph import CSR
+        from .ops import _aggregate_call
         (ids,) = ctx.saved_tensors
-        gs = torch.zeros(ctx.n_src, g.size(1), dtype=g.dtype, device=g.device)
-        gs.index_add_(0, ids, g)          # features are data on the reference path; kept for completeness
+        g = g.contiguous()
+        pos = torch.arange(ids.numel(), dtype=torch.int64, device=ids.device)
+        csr = CSR(torch.stack([pos, ids]), ctx.n_src, 1)
+        gs = torch.empty(ctx.n_src, g.size(1), dtype=g.dtype, device=g.device)
+        _aggregate_call(csr, g.size(0), g, gs)
         return gs, None
 
 

@@ -167,3 +167,6 @@ def test_edge_concat_linear_matches_cat_linear():
     assert (gz - z.grad).abs().max().item() < 2e-5 * scale(z.grad)
     assert (gw - lin.weight.grad).abs().max().item() < 2e-5 * scale(lin.weight.grad)
     assert (gb - lin.bias.grad).abs().max().item() < 2e-5 * scale(lin.bias.grad)
+    z.grad = None
+    S.edge_concat_linear(z, ei, lin).backward(up)            # the gather's backward is a pull in position order:
+    assert torch.equal(z.grad, gz)                           # bit-identical from run to run (index_add_ is not)
