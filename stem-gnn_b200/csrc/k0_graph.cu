@@ -18,27 +18,30 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 16;                       // items per thread
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;     // 4096 items per CTA
 constexpr int RS_WARP_ITEMS = 32 * RS_ITEMS;       // 512 items per warp, contiguous
-constexpr int RS_BINS = 256;
+// Digit width: 8 bits (256 bins), or 9 bits (512 bins) when that saves a pass -- 169,343 nodes are 18
+// bits: two passes of 9 instead of 8 + 8 + 2; the 512 codes of the arxiv-shaped VQ: one pass.
+constexpr int RS_MAX_BINS = 512;
 
 // key of item i for this pass: either from the int64 edge_index row (pass 0) or the int32 buffer
 __device__ __forceinline__ int load_key(const int64_t* k64, const int32_t* k32, int64_t i) {
     return k64 ? (int)k64[i] : k32[i];
 }
 
+template <int BINS>
 __global__ void __launch_bounds__(RS_THREADS)
 radix_hist_kernel(const int64_t* __restrict__ k64, const int32_t* __restrict__ k32, int64_t n,
-                  int shift, int nblk, int32_t* __restrict__ block_hist /* [256][nblk] */) {
-    __shared__ int hist[RS_BINS];
-    hist[threadIdx.x] = 0;
+                  int shift, int nblk, int32_t* __restrict__ block_hist /* [BINS][nblk] */) {
+    __shared__ int hist[BINS];
+    for (int b = threadIdx.x; b < BINS; b += RS_THREADS) hist[b] = 0;
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * RS_TILE;
 #pragma unroll 4
     for (int r = 0; r < RS_ITEMS; ++r) {
         int64_t i = base + (int64_t)r * RS_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&hist[(load_key(k64, k32, i) >> shift) & 0xFF], 1);
+        if (i < n) atomicAdd(&hist[(load_key(k64, k32, i) >> shift) & (BINS - 1)], 1);
     }
     __syncthreads();
-    block_hist[(int64_t)threadIdx.x * nblk + blockIdx.x] = hist[threadIdx.x];
+    for (int b = threadIdx.x; b < BINS; b += RS_THREADS) block_hist[(int64_t)b * nblk + blockIdx.x] = hist[b];
 }
 
 __device__ __forceinline__ int block_excl_scan_256(int v, int* total_out) {
@@ -82,22 +85,32 @@ radix_scan_kernel(int32_t* __restrict__ block_hist, int nblk, int32_t* __restric
 }
 
 // Stable scatter.  Item order inside a CTA is (warp, round, lane) = ascending index.
+template <int BINS>
 __global__ void __launch_bounds__(RS_THREADS)
 radix_scatter_kernel(const int64_t* __restrict__ k64, const int32_t* __restrict__ k32,
                      const int32_t* __restrict__ vin /* NULL => identity */, int64_t n, int shift,
                      int nblk, const int32_t* __restrict__ block_hist,
                      const int32_t* __restrict__ digit_total, int32_t* __restrict__ kout,
                      int32_t* __restrict__ vout) {
-    __shared__ int wcount[RS_WARPS][RS_BINS];
-    __shared__ int blockbase[RS_BINS];
+    constexpr int PER = BINS / RS_THREADS;          // digits per thread in the digit-total scan (1 or 2)
+    __shared__ int wcount[RS_WARPS][BINS];
+    __shared__ int blockbase[BINS];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < RS_WARPS * RS_BINS; i += RS_THREADS) (&wcount[0][0])[i] = 0;
+    for (int i = threadIdx.x; i < RS_WARPS * BINS; i += RS_THREADS) (&wcount[0][0])[i] = 0;
 
     // global base of each digit = exclusive scan of digit totals, plus this tile's offset
     {
+        int d[PER], sum = 0;
+#pragma unroll
+        for (int j = 0; j < PER; ++j) { d[j] = digit_total[threadIdx.x * PER + j]; sum += d[j]; }
         int tot;
-        int ex = block_excl_scan_256(digit_total[threadIdx.x], &tot);
-        blockbase[threadIdx.x] = ex + block_hist[(int64_t)threadIdx.x * nblk + blockIdx.x];
+        int ex = block_excl_scan_256(sum, &tot);
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+            const int b = threadIdx.x * PER + j;
+            blockbase[b] = ex + block_hist[(int64_t)b * nblk + blockIdx.x];
+            ex += d[j];
+        }
     }
     __syncthreads();
 
@@ -117,7 +130,7 @@ radix_scatter_kernel(const int64_t* __restrict__ k64, const int32_t* __restrict_
     for (int r = 0; r < RS_ITEMS; ++r) {
         int64_t i = wbase + r * 32 + lane;
         bool valid = i < n;
-        int d = valid ? ((keys[r] >> shift) & 0xFF) : 0x100 + lane;  // invalid: unique, no peers
+        int d = valid ? ((keys[r] >> shift) & (BINS - 1)) : BINS + lane;  // invalid: unique, no peers
         unsigned peers = __match_any_sync(0xffffffffu, d);
         int leader = __ffs(peers) - 1;
         int old = 0;
@@ -130,12 +143,12 @@ radix_scatter_kernel(const int64_t* __restrict__ k64, const int32_t* __restrict_
         __syncwarp();
     }
     __syncthreads();
-    {   // exclusive prefix over warps for digit = threadIdx.x
+    for (int b = threadIdx.x; b < BINS; b += RS_THREADS) {   // exclusive prefix over warps per digit
         int run = 0;
 #pragma unroll
         for (int i = 0; i < RS_WARPS; ++i) {
-            int t = wcount[i][threadIdx.x];
-            wcount[i][threadIdx.x] = run;
+            int t = wcount[i][b];
+            wcount[i][b] = run;
             run += t;
         }
     }
@@ -144,7 +157,7 @@ radix_scatter_kernel(const int64_t* __restrict__ k64, const int32_t* __restrict_
     for (int r = 0; r < RS_ITEMS; ++r) {
         int64_t i = wbase + r * 32 + lane;
         if (i < n) {
-            int d = (keys[r] >> shift) & 0xFF;
+            int d = (keys[r] >> shift) & (BINS - 1);
             int64_t pos = (int64_t)blockbase[d] + wcount[w][d] + ranks[r];
             kout[pos] = keys[r];
             vout[pos] = vals[r];
@@ -193,10 +206,19 @@ __global__ void gcn_weight_kernel(const int64_t* __restrict__ ei, int64_t n_edge
     w[e] = __fmul_rn(__fmul_rn(is, 1.0f), id);
 }
 
-static int radix_passes(int64_t key_range) {
+static int key_bits(int64_t key_range) {
     int bits = 1;
     while (bits < 32 && ((int64_t)1 << bits) < key_range) ++bits;
-    return (bits + 7) / 8;
+    return bits;
+}
+// 9-bit digits when they need fewer passes than 8-bit ones
+static int radix_digit_bits(int64_t key_range) {
+    const int bits = key_bits(key_range);
+    return (bits + 8) / 9 < (bits + 7) / 8 ? 9 : 8;
+}
+static int radix_passes(int64_t key_range) {
+    const int bits = key_bits(key_range), db = radix_digit_bits(key_range);
+    return (bits + db - 1) / db;
 }
 
 size_t radix_sort_workspace(int64_t n) {
@@ -204,8 +226,8 @@ size_t radix_sort_workspace(int64_t n) {
     size_t b = 0;
     b += 2 * align_up((size_t)n * 4, 256);       // keys ping-pong
     b += align_up((size_t)n * 4, 256);           // values (the other buffer is the caller's output)
-    b += align_up((size_t)RS_BINS * (size_t)(nblk > 0 ? nblk : 1) * 4, 256);
-    b += align_up(RS_BINS * 4, 256);
+    b += align_up((size_t)RS_MAX_BINS * (size_t)(nblk > 0 ? nblk : 1) * 4, 256);
+    b += align_up(RS_MAX_BINS * 4, 256);
     return b;
 }
 
@@ -217,19 +239,26 @@ const int32_t* radix_sort_pairs(const int64_t* k64, const int32_t* k32, int64_t 
     int32_t* kbuf[2] = {ws.take<int32_t>(n), ws.take<int32_t>(n)};
     int32_t* vws = ws.take<int32_t>(n);
     const int nblk = (int)((n + RS_TILE - 1) / RS_TILE);
-    int32_t* block_hist = ws.take<int32_t>((size_t)RS_BINS * nblk);
-    int32_t* digit_total = ws.take<int32_t>(RS_BINS);
-    const int P = radix_passes(key_range);
+    int32_t* block_hist = ws.take<int32_t>((size_t)RS_MAX_BINS * nblk);
+    int32_t* digit_total = ws.take<int32_t>(RS_MAX_BINS);
+    const int P = radix_passes(key_range), DB = radix_digit_bits(key_range);
     const int32_t* kin = k32;
     const int32_t* vin = nullptr;
     for (int p = 0; p < P; ++p) {
         int32_t* kout = kbuf[p & 1];
         int32_t* vout = ((P - 1 - p) & 1) ? vws : vals_out;   // last pass writes vals_out
         const int64_t* kk64 = p == 0 ? k64 : nullptr;
-        SG_LAUNCH(radix_hist_kernel<<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, n, 8 * p, nblk, block_hist));
-        SG_LAUNCH(radix_scan_kernel<<<RS_BINS, RS_THREADS, 0, stream>>>(block_hist, nblk, digit_total));
-        SG_LAUNCH(radix_scatter_kernel<<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, vin, n, 8 * p, nblk,
-                                                              block_hist, digit_total, kout, vout));
+        if (DB == 9) {
+            SG_LAUNCH(radix_hist_kernel<512><<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, n, 9 * p, nblk, block_hist));
+            SG_LAUNCH(radix_scan_kernel<<<512, RS_THREADS, 0, stream>>>(block_hist, nblk, digit_total));
+            SG_LAUNCH(radix_scatter_kernel<512><<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, vin, n, 9 * p, nblk,
+                                                                       block_hist, digit_total, kout, vout));
+        } else {
+            SG_LAUNCH(radix_hist_kernel<256><<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, n, 8 * p, nblk, block_hist));
+            SG_LAUNCH(radix_scan_kernel<<<256, RS_THREADS, 0, stream>>>(block_hist, nblk, digit_total));
+            SG_LAUNCH(radix_scatter_kernel<256><<<nblk, RS_THREADS, 0, stream>>>(kk64, kin, vin, n, 8 * p, nblk,
+                                                                       block_hist, digit_total, kout, vout));
+        }
         kin = kout;
         vin = vout;
     }
