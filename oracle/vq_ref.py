@@ -126,3 +126,34 @@ def vq_forward_ref(x, state, *, heads=1, separate_codebook_per_head=False, cosin
     if project_out is not None:
         q = project_out(q)                                                # :1041
     return q.squeeze(1), ind, loss, orig_q.squeeze(1)
+
+
+def kmeans_ref(samples, num_clusters, num_iters, cosine, means):
+    """model/vq.py:182-222 with the initial means passed in (the reference draws them with
+    `sample_fn`, vq.py:192).  samples (Hc, n, D).  Returns (means, bins)."""
+    Hc, n, D = samples.shape
+    bins = None
+    for _ in range(num_iters):
+        dists = samples @ means.transpose(1, 2) if cosine else -cdist_ref(samples, means)   # :195-198
+        buckets = dists.argmax(dim=-1)                                                     # :200
+        bins = torch.zeros(Hc, num_clusters, dtype=buckets.dtype)
+        bins.scatter_add_(-1, buckets, torch.ones_like(buckets))                            # :201
+        zero = bins == 0
+        new = torch.zeros(Hc, num_clusters, D, dtype=samples.dtype)
+        new.scatter_add_(1, buckets.unsqueeze(-1).expand(-1, -1, D), samples)               # :209
+        new = new / bins.masked_fill(zero, 1).unsqueeze(-1)                                 # :210
+        if cosine:
+            new = l2norm(new)                                                               # :214
+        means = torch.where(zero.unsqueeze(-1), means, new)                                 # :216-220
+    return means, bins
+
+
+def kmeans_init_ref(flatten, state, num_iters, cosine, means):
+    """{Euclidean,CosineSim}Codebook.init_embed_ (vq.py:320-342 / 573-595): k-means on the first batch,
+    embed = means, embed_avg = means * cluster_size, cluster_size = bins."""
+    K = state["embed"].shape[1]
+    embed, bins = kmeans_ref(flatten, K, num_iters, cosine, means)
+    bins = bins.to(embed.dtype)
+    state["embed"].data.copy_(embed)
+    state["embed_avg"].data.copy_(embed * bins.unsqueeze(-1))
+    state["cluster_size"].data.copy_(bins)

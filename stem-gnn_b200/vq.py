@@ -24,6 +24,18 @@ def _kaiming_uniform(*shape):
     return t
 
 
+def _batched_sample_vectors(samples, num):
+    """model/vq.py:106-116: `num` rows of every codebook's samples [Hc, n, D], without replacement
+    when there are enough of them."""
+    out = []
+    for rows in samples.unbind(dim=0):
+        n = rows.size(0)
+        pick = torch.randperm(n, device=rows.device)[:num] if n >= num \
+            else torch.randint(0, n, (num,), device=rows.device)
+        out.append(rows[pick])
+    return torch.stack(out, dim=0)
+
+
 class _Codebook(nn.Module):
     """State holder shared by the Euclidean (model/vq.py:241-514) and cosine (model/vq.py:516-688)
     codebooks: buffers initted (1,), cluster_size (Hc,K), embed_avg (Hc,K,D) and embed (Hc,K,D;
@@ -38,6 +50,7 @@ class _Codebook(nn.Module):
         self.kmeans_iters, self.decay, self.eps = kmeans_iters, decay, eps
         self.use_ddp, self.learnable_codebook, self.ema_update = use_ddp, learnable_codebook, ema_update
         self.path = path
+        self.sample_fn = _batched_sample_vectors                  # like the reference's attribute (vq.py:287)
         if kmeans_init:
             embed = torch.zeros(num_codebooks, codebook_size, dim)
         else:
@@ -77,12 +90,7 @@ class _Codebook(nn.Module):
             return
         Hc, K, D = self.embed.shape
         rows = x.view(x.size(0), heads, D).permute(1, 0, 2) if Hc == heads else x.reshape(1, -1, D)
-        n = rows.size(1)
-        picks = []
-        for _ in range(Hc):                                       # sample_vectors, vq.py:106-113
-            picks.append(torch.randperm(n, device=x.device)[:K] if n >= K
-                         else torch.randint(0, n, (K,), device=x.device))
-        means = torch.stack([rows[h][picks[h]] for h in range(Hc)]).contiguous()
+        means = self.sample_fn(rows, K).contiguous()              # vq.py:192
         counts = None
         for _ in range(self.kmeans_iters):
             ind, _, _, _ = ops.vq_assign_raw(x, means, heads, self.metric, ops.PATH_EXACT,

@@ -36,3 +36,21 @@ DEC_CASES = {
     "dec_inner_raw": dict(n=80, e=300, dim=20, proj=None, sigmoid=False),
     "dec_inner_proj": dict(n=64, e=257, dim=24, proj=16, sigmoid=True),
 }
+
+
+# k-means initialisation (model/vq.py:182-222, 320-342) with the initial means fixed by a deterministic
+# sample_fn (rows 0, 7, 14, ... of every codebook's samples) on both sides
+KMEANS_CASES = {
+    "km_euclid": dict(dim=16, codebook_size=12, kmeans_init=True, kmeans_iters=10),
+    "km_cosine": dict(dim=16, codebook_size=12, kmeans_init=True, kmeans_iters=6, use_cosine_sim=True),
+    "km_heads": dict(dim=16, codebook_size=8, codebook_dim=8, heads=2, separate_codebook_per_head=True,
+                     kmeans_init=True, kmeans_iters=5, use_cosine_sim=True),
+}
+
+
+def strided_sample_fn(samples, num):
+    """Deterministic stand-in for batched_sample_vectors (model/vq.py:115-116)."""
+    import torch
+    n = samples.shape[1]
+    idx = (torch.arange(num, device=samples.device) * 7) % n
+    return samples[:, idx]

@@ -26,7 +26,7 @@ warnings.filterwarnings("ignore")
 from model.vq import VectorQuantize  # noqa: E402  (the reference's own module)
 from model.encoder import Encoder, InnerProductDecoder  # noqa: E402  (the reference's own module, on the shim)
 
-from tests.golden.cases import DEC_CASES, ENC_CASES, VQ_CASES  # noqa: E402
+from tests.golden.cases import DEC_CASES, ENC_CASES, KMEANS_CASES, VQ_CASES, strided_sample_fn  # noqa: E402
 
 
 def gen_vq(name, cfg):
@@ -63,6 +63,24 @@ def gen_vq(name, cfg):
         out["after." + k] = v.detach().numpy()
     np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
     print(name, {k: v.shape for k, v in out.items() if not k.startswith(("before", "after"))})
+
+
+def gen_kmeans(name, cfg):
+    """First training forward of a kmeans_init module: init_embed_ runs the reference's own kmeans()."""
+    torch.manual_seed(0)
+    vq = VectorQuantize(**cfg)
+    vq.train()
+    vq._codebook.sample_fn = strided_sample_fn
+    x = torch.randn(300, cfg["dim"]) + 2.0 * torch.randn(6, cfg["dim"])[torch.randint(0, 6, (300,))]
+    before = {k: v.detach().clone().numpy() for k, v in vq.state_dict().items()}
+    q, ind, loss, oq = vq(x)
+    out = dict(x=x.numpy(), quantize=q.detach().numpy(), embed_ind=ind.numpy(), loss=loss.detach().numpy())
+    for k, v in before.items():
+        out["before." + k] = v
+    for k, v in vq.state_dict().items():
+        out["after." + k] = v.detach().numpy()
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(name, ind.shape, float(vq._codebook.initted))
 
 
 def gen_enc(name, c):
@@ -120,6 +138,10 @@ def gen_dec(name, c):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "kmeans":   # only the k-means fixtures (added later)
+        for k, v in KMEANS_CASES.items():
+            gen_kmeans(k, v)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "dec":      # only the decoder fixtures (added later)
         for k, v in DEC_CASES.items():
             gen_dec(k, v)
@@ -130,3 +152,5 @@ if __name__ == "__main__":
         gen_enc(k, v)
     for k, v in DEC_CASES.items():
         gen_dec(k, v)
+    for k, v in KMEANS_CASES.items():
+        gen_kmeans(k, v)

@@ -74,3 +74,32 @@ def test_vq_matches_reference_golden(golden_dir, name):
                                        rtol=1e-5, atol=2e-6)
     else:
         assert not loss.requires_grad and float(loss) == 0.0
+
+
+from tests.golden.cases import KMEANS_CASES, strided_sample_fn  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(KMEANS_CASES))
+def test_kmeans_init_matches_reference_golden(golden_dir, name):
+    """kmeans_init=True: the first training forward initialises the codebook with k-means run by K3
+    (exact scan) and K4 (per-cluster sums); the fixture holds what the reference's own kmeans()
+    (vq.py:182-222) produced from the same initial means."""
+    cfg = dict(KMEANS_CASES[name])
+    g = _load(golden_dir, name)
+    vq = S.VectorQuantize(**cfg)
+    sd = {k[len("before."):]: torch.from_numpy(v.copy()) for k, v in g.items() if k.startswith("before.")}
+    assert set(sd) == set(vq.state_dict())
+    vq.load_state_dict(sd)
+    vq.to(DEV).train()
+    vq._codebook.sample_fn = strided_sample_fn
+    x = torch.from_numpy(g["x"].copy()).to(DEV)
+    q, ind, loss, _ = vq(x)
+    assert float(vq._codebook.initted) == 1.0
+    assert np.array_equal(ind.cpu().numpy(), g["embed_ind"])
+    np.testing.assert_allclose(q.detach().cpu().numpy(), g["quantize"], rtol=1e-5, atol=2e-6)
+    np.testing.assert_allclose(loss.detach().cpu().numpy(), g["loss"], rtol=1e-5, atol=1e-7)
+    for k in ("embed", "embed_avg", "cluster_size"):
+        np.testing.assert_allclose(getattr(vq._codebook, k).detach().cpu().numpy(),
+                                   g["after._codebook." + k], rtol=1e-5, atol=2e-6)
+    q2, ind2, _, _ = vq(x)                                   # initialised: the second call does not re-run k-means
+    assert float(vq._codebook.initted) == 1.0

@@ -172,3 +172,38 @@ def test_decoder_oracle_matches_reference_golden(golden_dir, name):
     if not c["proj"]:     # the closed form used for the large GPU cases
         g64 = edge_dot_grad_ref(g["z"], g["edge_index"], g["g_out"], c["sigmoid"])
         np.testing.assert_allclose(g["g_z"], g64, rtol=1e-5, atol=1e-6)
+
+
+from tests.golden.cases import KMEANS_CASES, strided_sample_fn  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(KMEANS_CASES))
+def test_kmeans_init_oracle_matches_reference_golden(golden_dir, name):
+    """The reference's own kmeans() (vq.py:182-222) ran inside init_embed_ when the fixture was made;
+    the restatement must reproduce the initialised codebook and the forward that follows it."""
+    from oracle.vq_ref import kmeans_init_ref, l2norm
+    cfg = dict(KMEANS_CASES[name])
+    g = _load(golden_dir, name)
+    x = torch.from_numpy(g["x"].copy())
+    heads, cosine = cfg.get("heads", 1), cfg.get("use_cosine_sim", False)
+    pin = pout = None
+    h = x
+    if "before.project_in.weight" in g:
+        D = cfg["codebook_dim"] * heads
+        pin, pout = nn.Linear(cfg["dim"], D), nn.Linear(D, cfg["dim"])
+        pin.load_state_dict({k: torch.from_numpy(g["before.project_in." + k].copy()) for k in ("weight", "bias")})
+        pout.load_state_dict({k: torch.from_numpy(g["before.project_out." + k].copy()) for k in ("weight", "bias")})
+        h = pin(x).detach()
+    flatten = h.view(x.size(0), heads, -1).permute(1, 0, 2).contiguous()
+    if cosine:
+        flatten = l2norm(flatten)
+    state = {k: torch.from_numpy(g["before._codebook." + k].copy()) for k in ("embed", "embed_avg", "cluster_size")}
+    assert float(g["before._codebook.initted"][0]) == 0.0 and float(g["after._codebook.initted"][0]) == 1.0
+    kmeans_init_ref(flatten, state, cfg["kmeans_iters"], cosine,
+                    strided_sample_fn(flatten, cfg["codebook_size"]))
+    q, ind, loss, _ = vq_forward_ref(x, state, project_in=pin, project_out=pout, **vq_kwargs(cfg))
+    assert np.array_equal(ind.numpy(), g["embed_ind"])
+    np.testing.assert_allclose(q.detach().numpy(), g["quantize"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-7)
+    for k in ("embed", "embed_avg", "cluster_size"):
+        np.testing.assert_allclose(state[k].numpy(), g["after._codebook." + k], rtol=1e-5, atol=1e-6)
