@@ -24,10 +24,9 @@ Parity pinning status
   for the handful of PyG symbols encoder.py:9-14 imports), so the Encoder layer loop,
   MySAGEConv.forward/message and MixtureSageLayer are the reference's own code, while the
   third-party aggregation arithmetic underneath is "parity unpinned by the reference".
-"""
-
 * Augmentations / samplers (`augment_ref.py`, `sampler_ref.py`): torch_geometric.utils 2.3.0
   (`mask_feature`, `dropout_adj`, `negative_sampling`) and the NeighborLoader sampling algorithm
   (torch_sparse 0.6.15 `neighbor_sample`) are third-party code absent from /root/reference; restated
   from the published algorithms with the random draws passed in or replayed -- parity unpinned by the
   reference (it has no tests for its loop either).
+"""
