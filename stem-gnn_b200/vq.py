@@ -91,6 +91,11 @@ class _Codebook(nn.Module):
         Hc, K, D = self.embed.shape
         rows = x.view(x.size(0), heads, D).permute(1, 0, 2) if Hc == heads else x.reshape(1, -1, D)
         means = self.sample_fn(rows, K).contiguous()              # vq.py:192
+        if self.use_ddp:
+            # every rank must start from the same means (counts and sums are all-reduced below).  The
+            # reference draws a multinomial share of them on every rank and gathers (vq.py:158-180);
+            # here rank 0's sample is broadcast -- a valid k-means start, not the same draw.
+            dist.broadcast(means, src=0)
         counts = None
         for _ in range(self.kmeans_iters):
             ind, _, _, _ = ops.vq_assign_raw(x, means, heads, self.metric, ops.PATH_EXACT,
