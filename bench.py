@@ -512,10 +512,10 @@ def run_partitioned(args, w):
     pg = S.PartitionedGraph(None, n, rank=rank, world=world,
                             pre_split=(torch.cat(fwd_parts, 1), torch.cat(bwd_parts, 1)))
     del fwd_parts, bwd_parts
+    # BatchNorm statistics over ALL ranks' rows come from the library (K7 + norm_act.BatchSync: a
+    # gather of (mean, var, n) forward, an all-reduce of the two column sums backward), not from
+    # nn.SyncBatchNorm -- the fused BatchNorm + ReLU + dropout passes stay in use on every rank
     enc, vq, opt = build_models(w, dev, S)
-    if world > 1:
-        enc = nn.SyncBatchNorm.convert_sync_batchnorm(enc)
-        opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
     params = list(enc.parameters())
 
     def step(x):

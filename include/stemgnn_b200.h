@@ -228,6 +228,15 @@ int stemgnn_bn_act_backward(int64_t rows, int64_t feat, const float* x, int64_t 
                             const float* beta, int relu, float p, const uint64_t* seed, int batch_stats,
                             float* sum_g, float* sum_gx, float* gx, int64_t ldgx, void* workspace,
                             size_t workspace_bytes, stemgnn_stream_t stream);
+/* The same backward with the batch split over several processes (1-D partition, SURVEY.md 8e "BatchNorm
+ * batch statistics all-reduced"): call stemgnn_bn_act_backward with gx = NULL for this rank's sum_g /
+ * sum_gx, all-reduce them, then this entry point applies gx with the GLOBAL sums and row count
+ * (mean / invstd are the global statistics). */
+int stemgnn_bn_act_backward_apply(int64_t rows, int64_t feat, const float* x, int64_t ldx, const float* gy,
+                                  int64_t ldg, const float* mean, const float* invstd, const float* gamma,
+                                  const float* beta, int relu, float p, const uint64_t* seed, const float* sum_g,
+                                  const float* sum_gx, int64_t batch_rows, float* gx, int64_t ldgx,
+                                  stemgnn_stream_t stream);
 
 /* ------------------------------------------------------------------ K4: EMA statistics
  * Replaces onehot.sum(1) and einsum('h n d, h n c -> h c d') (model/vq.py:492,497 / 665,670):

@@ -76,6 +76,8 @@ SIGNATURES = {
     "stemgnn_bn_act_forward": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp, _vp, _i64, _vp]),
     "stemgnn_bn_act_backward": (_i32, [_i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp, _i32,
                                        _vp, _vp, _vp, _i64, _vp, C.c_size_t, _vp]),
+    "stemgnn_bn_act_backward_apply": (_i32, [_i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp,
+                                             _vp, _vp, _i64, _vp, _i64, _vp]),
     "stemgnn_vq_assign_workspace": (_i32, [C.POINTER(VqAssignArgs), C.POINTER(C.c_size_t)]),
     "stemgnn_vq_assign": (_i32, [C.POINTER(VqAssignArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_vq_backward": (_i32, [_vp, _vp, _vp, _vp, _f32, _i64, _vp, _vp]),

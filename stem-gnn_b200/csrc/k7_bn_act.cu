@@ -146,11 +146,13 @@ template <bool BWD>
 __global__ void __launch_bounds__(256)
 apply_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ gy, int64_t ldg, int64_t rows, int feat,
              Cols cc, const float* __restrict__ sg, const float* __restrict__ sgx, int relu, float p, float inv_keep,
-             const uint64_t* __restrict__ seed_p, float* __restrict__ out, int64_t ldo) {
+             const uint64_t* __restrict__ seed_p, float* __restrict__ out, int64_t ldo, int64_t batch_rows) {
     const int f4 = feat >> 2;
     const int64_t total = rows * f4;
     const uint64_t seed = p > 0.f ? *seed_p : 0;
-    const float inv_n = 1.f / (float)rows;
+    // batch_rows: rows the statistics (and sg / sgx) were taken over -- all ranks' rows when the batch
+    // is split over several processes, else this call's rows
+    const float inv_n = 1.f / (float)(batch_rows > 0 ? batch_rows : rows);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / f4;
         const int c = (int)(i - r * f4) * 4;
@@ -245,7 +247,7 @@ extern "C" int stemgnn_bn_act_forward(int64_t rows, int64_t feat, const float* x
     SG_CHECK_ARG(p >= 0.f && p < 1.f && (p == 0.f || seed), "dropout p must be in [0, 1) and needs a seed");
     bn::Cols cc{mean, invstd, gamma, beta};
     SG_LAUNCH(bn::apply_kernel<false><<<ew_grid(rows * (feat / 4)), 256, 0, stream>>>(
-        x, ldx, nullptr, 0, rows, (int)feat, cc, nullptr, nullptr, relu, p, 1.f / (1.f - p), seed, out, ldo));
+        x, ldx, nullptr, 0, rows, (int)feat, cc, nullptr, nullptr, relu, p, 1.f / (1.f - p), seed, out, ldo, 0));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }
@@ -278,8 +280,28 @@ extern "C" int stemgnn_bn_act_backward(int64_t rows, int64_t feat, const float* 
         SG_CHECK_ARG(ldgx >= feat && ldgx % 4 == 0, "ldgx");
         SG_LAUNCH(bn::apply_kernel<true><<<ew_grid(rows * (feat / 4)), 256, 0, stream>>>(
             x, ldx, gy, ldg, rows, (int)feat, cc, batch_stats ? sum_g : nullptr, batch_stats ? sum_gx : nullptr, relu, p,
-            inv_keep, seed, gx, ldgx));
+            inv_keep, seed, gx, ldgx, 0));
     }
+    SG_CHECK_LAUNCH();
+    return STEMGNN_OK;
+}
+
+extern "C" int stemgnn_bn_act_backward_apply(int64_t rows, int64_t feat, const float* x, int64_t ldx, const float* gy,
+                                             int64_t ldg, const float* mean, const float* invstd, const float* gamma,
+                                             const float* beta, int relu, float p, const uint64_t* seed,
+                                             const float* sum_g, const float* sum_gx, int64_t batch_rows, float* gx,
+                                             int64_t ldgx, stemgnn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (int rc = bn_check(rows, feat, x, ldx)) return rc;
+    if (int rc = bn_check(rows, feat, gy, ldg)) return rc;
+    if (feat == 0 || rows == 0) return STEMGNN_OK;
+    SG_CHECK_ARG(mean && invstd && gamma && beta && sum_g && sum_gx && gx, "NULL pointer");
+    SG_CHECK_ARG(ldgx >= feat && ldgx % 4 == 0, "ldgx");
+    SG_CHECK_ARG(batch_rows >= rows, "batch_rows must cover this call's rows");
+    SG_CHECK_ARG(p >= 0.f && p < 1.f && (p == 0.f || seed), "dropout p must be in [0, 1) and needs a seed");
+    bn::Cols cc{mean, invstd, gamma, beta};
+    SG_LAUNCH(bn::apply_kernel<true><<<ew_grid(rows * (feat / 4)), 256, 0, stream>>>(
+        x, ldx, gy, ldg, rows, (int)feat, cc, sum_g, sum_gx, relu, p, 1.f / (1.f - p), seed, gx, ldgx, batch_rows));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

@@ -120,6 +120,7 @@ class Encoder(nn.Module):
         layer (encoder.py:283-323).  The CSR/CSC structure of `edge_index` is built once and
         shared by every layer and by the backward pass."""
         graph = structure_of(edge_index, x.size(0)) if isinstance(edge_index, Tensor) else edge_index
+        sync = graph.batch_sync() if hasattr(graph, "batch_sync") else None    # partitioned graph: full-batch BN
         z, slot, reg_sum, reg_n = x, 0, None, 0
         self._last_env_reg = None
         for i, layer in enumerate(self.layers):
@@ -143,9 +144,13 @@ class Encoder(nn.Module):
                     and norm_act.supported(z, self.norms[i], self.activation if act_here else None)):
                 # BatchNorm (+ ReLU + dropout) in three passes over z (K7) on the same norms[i] module
                 z = norm_act.bn_act_drop(z, self.norms[i], relu=act_here,
-                                         p=self.dropout.p if act_here else 0.0, training=self.dropout.training)
+                                         p=self.dropout.p if act_here else 0.0, training=self.dropout.training,
+                                         sync=sync)
             else:
                 if self.normalize != "none":
+                    if sync is not None and self.norms[i].training and not isinstance(self.norms[i], nn.SyncBatchNorm):
+                        raise NotImplementedError("BatchNorm over a partitioned graph needs the fused K7 path "
+                                                  "(float32, width % 4 == 0, ReLU or no activation)")
                     z = self.norms[i](z)
                 if act_here:
                     z = self.dropout(self.activation(z))

@@ -63,9 +63,49 @@ def batch_stats(x):
     return mean, var
 
 
+class BatchSync:
+    """Collectives that make the batch statistics those of ALL ranks' rows when one batch (graph) is
+    split over several processes (the 1-D partition): `gather(v)` returns every rank's
+    vector stacked in rank order [world, len(v)], `reduce(v)` the element-wise sum over ranks,
+    `batch_rows` the global row count.  The defaults are torch.distributed calls on `group`."""
+
+    def __init__(self, batch_rows, world, group=None, gather=None, reduce=None):
+        self.batch_rows, self.world, self.group = int(batch_rows), int(world), group
+        self._gather, self._reduce = gather, reduce
+
+    def gather(self, v):
+        if self._gather is not None:
+            return self._gather(v)
+        import torch.distributed as dist
+        out = v.new_empty((self.world, v.numel()))
+        dist.all_gather_into_tensor(out, v.contiguous(), group=self.group)
+        return out
+
+    def reduce(self, v):
+        if self._reduce is not None:
+            return self._reduce(v)
+        import torch.distributed as dist
+        dist.all_reduce(v, group=self.group)
+        return v
+
+
+def synced_batch_stats(x, sync: BatchSync):
+    """Global (mean, biased variance) from every rank's local ones: combined in rank order on every
+    rank (identical results everywhere): mean = sum n_r mean_r / N, var = sum n_r (var_r + (mean_r -
+    mean)^2) / N."""
+    mean, var = batch_stats(x)
+    f = mean.numel()
+    pack = torch.cat([mean, var, mean.new_full((1,), float(x.size(0)))])
+    g = sync.gather(pack)
+    w = (g[:, -1] / float(sync.batch_rows)).unsqueeze(1)
+    gmean = (w * g[:, :f]).sum(0)
+    gvar = (w * (g[:, f:2 * f] + (g[:, :f] - gmean) ** 2)).sum(0)
+    return gmean, gvar
+
+
 class _BnActDrop(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, mean, invstd, use_batch_stats, relu, p, seed):
+    def forward(ctx, x, gamma, beta, mean, invstd, use_batch_stats, relu, p, seed, sync=None):
         x = _rows16(x)
         n, f = x.shape
         out = torch.empty((n, f), dtype=torch.float32, device=x.device)
@@ -75,6 +115,7 @@ class _BnActDrop(torch.autograd.Function):
                 beta.data_ptr(), int(relu), float(p), _lib.ptr(seed), out.data_ptr(), out.stride(0), _lib.stream()))
         ctx.save_for_backward(x, gamma, beta, mean, invstd, seed)
         ctx.cfg = (bool(use_batch_stats), bool(relu), float(p))
+        ctx.sync = sync if use_batch_stats else None
         return out
 
     @staticmethod
@@ -87,30 +128,41 @@ class _BnActDrop(torch.autograd.Function):
         sum_gx = torch.empty_like(sum_g)
         gx = torch.empty((n, f), dtype=torch.float32, device=x.device) if ctx.needs_input_grad[0] else None
         ws = _ws(n, f, x.device)
+        L = _lib.lib()
+        split = ctx.sync is not None and gx is not None     # batch split over ranks: sums, all-reduce, apply
         with _lib.traced("bn_act_backward", (5 if gx is not None else 2) * n * f * 4, 0, 3):
-            _lib.check(_lib.lib().stemgnn_bn_act_backward(
+            _lib.check(L.stemgnn_bn_act_backward(
                 n, f, x.data_ptr(), x.stride(0), gy.data_ptr(), gy.stride(0), mean.data_ptr(), invstd.data_ptr(),
                 gamma.data_ptr(), beta.data_ptr(), int(relu), p, _lib.ptr(seed), int(use_batch_stats),
-                sum_g.data_ptr(), sum_gx.data_ptr(), _lib.ptr(gx), gx.stride(0) if gx is not None else 0,
-                ws.data_ptr(), ws.numel(), _lib.stream()))
+                sum_g.data_ptr(), sum_gx.data_ptr(), None if split else _lib.ptr(gx),
+                gx.stride(0) if gx is not None and not split else 0, ws.data_ptr(), ws.numel(), _lib.stream()))
+            if split:
+                tot = ctx.sync.reduce(torch.cat([sum_g, sum_gx]))        # global sums enter g_x only;
+                _lib.check(L.stemgnn_bn_act_backward_apply(               # gamma / beta keep this rank's share
+                    n, f, x.data_ptr(), x.stride(0), gy.data_ptr(), gy.stride(0), mean.data_ptr(),
+                    invstd.data_ptr(), gamma.data_ptr(), beta.data_ptr(), int(relu), p, _lib.ptr(seed),
+                    tot[:f].data_ptr(), tot[f:].data_ptr(), ctx.sync.batch_rows, gx.data_ptr(), gx.stride(0),
+                    _lib.stream()))
         return (gx, sum_gx if ctx.needs_input_grad[1] else None, sum_g if ctx.needs_input_grad[2] else None,
-                None, None, None, None, None, None)
+                None, None, None, None, None, None, None)
 
 
-def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool):
-    """dropout(relu(bn(z))) with bn's own parameters / buffers; `relu=False`, `p=0` give plain BatchNorm."""
+def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool, sync: BatchSync = None):
+    """dropout(relu(bn(z))) with bn's own parameters / buffers; `relu=False`, `p=0` give plain BatchNorm.
+    `sync`: z holds only this rank's rows of the batch (partitioned graph) -- statistics and the
+    backward's column sums are taken over all ranks' rows, like full-batch BatchNorm on one GPU."""
     use_batch = bn.training or bn.running_mean is None
     f = z.size(1)
     if use_batch:
         with torch.no_grad():
-            mean, var = batch_stats(z.detach())
+            mean, var = synced_batch_stats(z.detach(), sync) if sync is not None else batch_stats(z.detach())
             if bn.training and bn.track_running_stats and bn.running_mean is not None:
                 bn.num_batches_tracked.add_(1)
                 if bn.momentum is None:
                     m = 1.0 / bn.num_batches_tracked.to(torch.float32)        # cumulative moving average
                 else:
                     m = bn.momentum
-                n = z.size(0)
+                n = sync.batch_rows if sync is not None else z.size(0)
                 bn.running_mean.mul_(1 - m).add_(mean * m)
                 bn.running_var.mul_(1 - m).add_(var * (n / max(n - 1, 1)) * m)
     else:
@@ -125,4 +177,4 @@ def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool):
         st = _seed_tensor(z.device)
         seed = st.clone()                 # this call's key, kept for the backward
         st.add_(_GOLDEN)                  # device-side advance: a replayed CUDA graph draws new masks
-    return _BnActDrop.apply(z, gamma, beta, mean, invstd, use_batch, relu, p_eff, seed)
+    return _BnActDrop.apply(z, gamma, beta, mean, invstd, use_batch, relu, p_eff, seed, sync)

@@ -62,7 +62,8 @@ class PartitionedGraph:
     def __init__(self, edge_index: Optional[torch.Tensor], num_nodes: int, rank: Optional[int] = None,
                  world: Optional[int] = None, group=None,
                  gather: Optional[Callable[[torch.Tensor], torch.Tensor]] = None, pre_split=None,
-                 halo_slices: Optional[int] = None, halo_dtype: Optional[torch.dtype] = None):
+                 halo_slices: Optional[int] = None, halo_dtype: Optional[torch.dtype] = None,
+                 stat_gather=None, stat_reduce=None):
         if world is None:
             world = dist.get_world_size(group) if dist.is_initialized() else 1
         if rank is None:
@@ -78,6 +79,7 @@ class PartitionedGraph:
             fwd, bwd = pre_split
         self.fwd_edges, self.bwd_edges = fwd, bwd
         self._gather = gather
+        self._stat_gather, self._stat_reduce = stat_gather, stat_reduce     # BatchNorm collectives (tests inject them)
         self._csr = {}
         # halo pipeline: number of feature slices per exchange (None: by width) and the wire dtype
         # (None = fp32, bit-identical to one GPU; torch.bfloat16 halves the bytes at a stated 2^-9
@@ -85,6 +87,14 @@ class PartitionedGraph:
         self.halo_slices, self.halo_dtype = halo_slices, halo_dtype
         if halo_dtype not in (None, torch.float32, torch.bfloat16):
             raise ValueError("halo_dtype must be None, torch.float32 or torch.bfloat16")
+
+    def batch_sync(self):
+        """Collectives for full-batch BatchNorm over the partition (norm_act.BatchSync), or None when
+        this process holds the whole graph."""
+        if self.world == 1 and self._stat_gather is None:
+            return None
+        from .norm_act import BatchSync
+        return BatchSync(self.num_nodes_global, self.world, self.group, self._stat_gather, self._stat_reduce)
 
     # ---- structure (K0 on the local edge lists) ------------------------------------------------
     def fwd_csr(self) -> CSR:

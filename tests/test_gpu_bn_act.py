@@ -106,3 +106,45 @@ def test_encoder_uses_fused_norm_and_matches_unfused_modules():
         h = ref.layers[0](x, ei); h = F.relu(ref.norms[0](h)); h = ref.norms[1](ref.layers[1](h, ei))
     _close(z.detach(), h, 2e-5)
     _close(enc.norms[0].running_var, ref.norms[0].running_var)
+
+
+@pytest.mark.parametrize("world", [1, 2, 3])
+@pytest.mark.parametrize("relu", [False, True])
+def test_batch_split_over_ranks_equals_full_batch(world, relu):
+    """SyncBN for the 1-D partition: every rank holds a block of rows; statistics are
+    combined from all ranks' (mean, var, n), the backward's column sums are all-reduced.  The ranks
+    run one after the other with the collectives replaced by their known results; outputs and
+    gradients must equal the full-batch op's rows."""
+    from stemgnn_b200.norm_act import BatchSync, batch_stats, bn_act_drop
+    n, f = 1201, 64
+    g_ = torch.Generator().manual_seed(world)
+    z = (torch.randn(n, f, generator=g_) * 2 + 3).to(DEV)
+    up = torch.randn(n, f, generator=g_).to(DEV)
+    bn = torch.nn.BatchNorm1d(f).to(DEV).train()
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.5, 0.5)
+    zf = z.clone().requires_grad_(True)
+    full = bn_act_drop(zf, bn, relu, 0.0, True)
+    full.backward(up)
+    sum_g, sum_gx = bn.bias.grad.clone(), bn.weight.grad.clone()
+    run_mean, run_var = bn.running_mean.clone(), bn.running_var.clone()
+    bounds = [(r * n // world, (r + 1) * n // world) for r in range(world)]
+    packs = torch.stack([torch.cat([*batch_stats(z[lo:hi]), torch.tensor([float(hi - lo)], device=DEV)])
+                         for lo, hi in bounds])
+    acc_g, acc_gx = torch.zeros(f, device=DEV), torch.zeros(f, device=DEV)
+    for lo, hi in bounds:
+        bn2 = torch.nn.BatchNorm1d(f).to(DEV).train()
+        bn2.load_state_dict({k: (torch.zeros_like(v) if "running_mean" in k else torch.ones_like(v) if "running_var" in k
+                                 else v.clone() if "num_batches" not in k else torch.zeros_like(v))
+                             for k, v in bn.state_dict().items()})
+        sync = BatchSync(n, world, gather=lambda v: packs, reduce=lambda v: torch.cat([sum_g, sum_gx]))
+        zl = z[lo:hi].clone().requires_grad_(True)
+        out = bn_act_drop(zl, bn2, relu, 0.0, True, sync=sync)
+        out.backward(up[lo:hi])
+        torch.testing.assert_close(out, full[lo:hi], rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(zl.grad, zf.grad[lo:hi], rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(bn2.running_mean, run_mean, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(bn2.running_var, run_var, rtol=1e-5, atol=1e-6)
+        acc_g += bn2.bias.grad; acc_gx += bn2.weight.grad     # parameter gradients are this rank's share
+    torch.testing.assert_close(acc_g, sum_g, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(acc_gx, sum_gx, rtol=1e-4, atol=1e-4)

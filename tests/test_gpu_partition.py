@@ -73,6 +73,37 @@ def test_encoder_on_a_partition_matches_full_graph_rows():
     torch.testing.assert_close(z_loc, z_full[lo:hi], rtol=1e-6, atol=1e-6)
 
 
+def test_encoder_with_batchnorm_on_a_partition_uses_full_batch_statistics():
+    """normalize='batch': a rank's BatchNorm must use the statistics of ALL nodes, so its
+    rows equal the single-GPU encoder's.  Collectives are replaced by their known results."""
+    import torch.nn as nn
+    n, e, f, hid, world, rank = 600, 5000, 24, 32, 3, 1
+    g = torch.Generator().manual_seed(6)
+    ei = torch.randint(0, n, (2, e), generator=g).to(DEV)
+    x = torch.randn(n, f, generator=g).to(DEV)
+    torch.manual_seed(0)
+    enc = S.Encoder(f, hid, nn.ReLU, 2, backbone="sage", normalize="batch", dropout=0.0).to(DEV).train()
+    state = {k: v.clone() for k, v in enc.state_dict().items()}
+    pre_bn = []
+    hooks = [l.register_forward_hook(lambda m, i, o: pre_bn.append(o.detach())) for l in enc.layers]
+    with torch.no_grad():
+        z_full = enc(x, ei)
+        for h in hooks:
+            h.remove()
+        h1_full = S.bn_act_drop(pre_bn[0], nn.BatchNorm1d(hid).to(DEV).train(), True, 0.0, True)   # default affine
+        per = S.block_size(n, world)
+        parts = S.partition_1d(n, world)
+        lo, hi = parts[rank]
+        pad = lambda t: torch.cat([t, t.new_zeros(world * per - n, t.size(1))])
+        packs = [torch.stack([torch.cat([*S.batch_stats(z[a:b]), torch.tensor([float(b - a)], device=DEV)])
+                              for a, b in parts]) for z in pre_bn]
+        enc.load_state_dict(state)                           # running statistics back to their start
+        pg = S.PartitionedGraph(ei, n, rank=rank, world=world, gather=_Queue([pad(x), pad(h1_full)]),
+                                stat_gather=lambda v, it=iter(packs): next(it), stat_reduce=lambda v: v)
+        z_loc = enc(x[lo:hi], pg)
+    torch.testing.assert_close(z_loc, z_full[lo:hi], rtol=1e-5, atol=1e-5)
+
+
 def test_feature_sliced_halo_pipeline_is_bit_identical():
     """The exchange pipelined over 3 feature slices (columns 0-87, 88-175, 176-255 gathered and
     aggregated one after the other into column ranges of the output) gives the same bits."""
