@@ -92,9 +92,22 @@ typedef struct {
     float* out;              /* [n_rows,F] */
     int64_t out_ld;          /* row stride of out in floats; 0 = feat (contiguous).  ABI 2 */
     int64_t row_x_ld;        /* row stride of row_x in floats; 0 = feat */
+    void* hub_ws;            /* device scratch of stemgnn_aggregate_hub_workspace(num_edges) bytes, or NULL.  ABI 4 */
+    size_t hub_ws_bytes;
 } stemgnn_aggregate_args;
 
 int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t stream);
+
+/* Hub rows.  Real citation / co-purchase graphs have rows with 10^4 edges (ogbn-arxiv: largest
+ * in-degree 13,155; ogbn-products: 17,481): walked by one group of lanes such a row alone outlasts
+ * the rest of the launch.  With hub_ws set, rows of >= 256 edges are put on a device work list by
+ * the first launch and summed by a second one that cuts each of them into column slices (32 columns,
+ * 8 from 4,096 edges on) over many CTAs, longest rows first, and stages 256 / 1,024 edges at a time in
+ * shared memory -- the additions of every column stay in edge order, so the result is the same bits.
+ * The scratch holds four counters and the list.  The caller zero-fills it ONCE (cudaMemset) before its
+ * first use; every call leaves it zeroed again.  It must not be shared by calls that may run
+ * concurrently.  hub_ws == NULL keeps every row in the first launch. */
+int stemgnn_aggregate_hub_workspace(int64_t num_edges, size_t* bytes);
 
 /* K2a. out[r, :] = x[r, :] / cnt[r] (IEEE division, rows of `feat` floats; out may alias x).
  * MeanAggregation's backward divides the upstream gradient of a destination by its clamped count

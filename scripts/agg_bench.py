@@ -6,10 +6,24 @@ pkg = importlib.import_module("stem-gnn_b200")
 from importlib import import_module
 ops = import_module("stem-gnn_b200.ops"); graph = import_module("stem-gnn_b200.graph")
 
-def run(n, e, f, reps=5, seed=0):
+def skewed_dst(n, e, g, cap=17000):
+    """SURVEY.md 8d's power-law variant: destinations drawn with p(rank k) ~ 1/k (Zipf, alpha = 1), no node
+    above `cap` edges in expectation (ogbn-products' largest degree is 17,481), ranks scattered over the
+    node ids by a random permutation so that hubs are not the first rows the launch starts."""
+    w = 1.0 / torch.arange(1, n + 1, dtype=torch.float64)
+    w = torch.minimum(w, torch.tensor(cap / e, dtype=torch.float64) * w.sum())
+    dst_rank = torch.multinomial(w, e, replacement=True, generator=g)
+    return torch.randperm(n, generator=g)[dst_rank]
+
+
+def run(n, e, f, reps=5, seed=0, skew=False):
     dev = torch.device("cuda:0")
     g = torch.Generator().manual_seed(seed)
-    ei = torch.randint(0, n, (2, e), generator=g).to(dev)
+    ei = torch.randint(0, n, (2, e), generator=g)
+    if skew:
+        ei[1] = skewed_dst(n, e, g)
+    max_deg = int(torch.bincount(ei[1], minlength=n).max())
+    ei = ei.to(dev)
     x = torch.randn(n, f, device=dev, requires_grad=True)
     gs = graph.GraphStructure(ei, n)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -31,11 +45,16 @@ def run(n, e, f, reps=5, seed=0):
         res[name] = min(ts)
     gb_gather = (e * f * 4 + n * f * 4 + e * 4 + n * 4) / 1e9
     gb_min = (2 * n * f * 4 + e * 4 + n * 4) / 1e9
-    print(json.dumps(dict(n=n, e=e, f=f, fwd_us=round(res["fwd"], 1), bwd_us=round(res["bwd"], 1),
+    print(json.dumps(dict(n=n, e=e, f=f, skew=skew, max_in_deg=max_deg, fwd_us=round(res["fwd"], 1), bwd_us=round(res["bwd"], 1),
                           fwd_gather_GBps=round(gb_gather / res["fwd"] * 1e6), fwd_min_GBps=round(gb_min / res["fwd"] * 1e6))), flush=True)
 
 if __name__ == "__main__":
-    print("tag", sys.argv[1:] , os.environ.get("STEMGNN_AGG_ROWWARP"))
+    print("tag", sys.argv[1:], "no_hub =", os.environ.get("STEMGNN_AGG_NO_HUB"))
+    if "skew" in sys.argv[1:]:
+        for sk in (False, True):
+            run(169343, 1166243, 128, skew=sk); run(169343, 1166243, 256, skew=sk)
+        run(2449029 // 2, 61859140 // 2, 256, reps=2, skew=True)
+        sys.exit(0)
     run(169343, 1166243, 128); run(169343, 1166243, 256)
     run(2449029 // 2, 61859140 // 2, 100); run(2449029 // 2, 61859140 // 2, 256)
     run(2708, 10556, 1432); run(500000, 5000000, 64); run(500000, 2000000, 512)

@@ -8,7 +8,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libstemgnn_b200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 _i64, _i32, _vp, _f32, _f64 = C.c_int64, C.c_int, C.c_void_p, C.c_float, C.c_double
 
@@ -18,7 +18,8 @@ class AggregateArgs(C.Structure):
                 ("n_gather_rows", _i64), ("num_edges", _i64), ("feat", _i64), ("gathered", _vp),
                 ("row_cnt", _vp), ("gather_cnt", _vp), ("edge_feat", _vp), ("type_table", _vp),
                 ("edge_type", _vp), ("edge_weight", _vp), ("row_x", _vp), ("act", _i32),
-                ("backward", _i32), ("out", _vp), ("out_ld", _i64), ("row_x_ld", _i64)]
+                ("backward", _i32), ("out", _vp), ("out_ld", _i64), ("row_x_ld", _i64),
+                ("hub_ws", _vp), ("hub_ws_bytes", C.c_size_t)]
 
 
 class VqAssignArgs(C.Structure):
@@ -65,6 +66,7 @@ SIGNATURES = {
     "stemgnn_csr_build": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
     "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "stemgnn_aggregate": (_i32, [C.POINTER(AggregateArgs), _vp]),
+    "stemgnn_aggregate_hub_workspace": (_i32, [_i64, C.POINTER(C.c_size_t)]),
     "stemgnn_row_scale": (_i32, [_i64, _i64, _vp, _vp, _vp, _vp]),
     "stemgnn_edge_dot": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _i32, _vp, _vp]),
     "stemgnn_linear_workspace": (_i32, [C.POINTER(LinearArgs), C.POINTER(C.c_size_t)]),

@@ -36,13 +36,25 @@ template <> struct Vec<1> {
 
 struct AggParams {
     const int32_t* rowptr; const int32_t* col; const int32_t* perm;
-    int64_t n_rows; int F;
+    int64_t n_rows, num_edges; int F;
     const float* gathered; const float* row_cnt; const float* gather_cnt;
     const float* edge_feat; const float* type_table; const int32_t* edge_type;
     const float* edge_weight; const float* row_x;
     int relu; float* out;
     int64_t out_ld, row_x_ld;   // row strides (floats) of out / row_x: column slices of wider matrices
+    int* hub;                   // [0] big hubs, [1] small hubs, [2] next work item, [3] CTAs done, [4..] row ids; or NULL
+    int hub_cap;                // slots of the row list: big hubs from the front, small ones from the back
 };
+
+// Rows with at least this many edges ("hubs": ogbn-arxiv's largest in-degree is 13,155, ogbn-products'
+// 17,481) leave the row-per-group kernel: one group walks its row with U*CH loads in flight, so a
+// 17,000-edge row alone takes milliseconds after every other row has finished.  They are appended to
+// a work list and summed by aggregate_hub_kernel below (same order of additions, same bits).
+constexpr int HUB_ROW_EDGES = 256;
+constexpr int HUB_BIG_EDGES = 4096;    // from here on a hub is cut into 8-column instead of 32-column slices
+constexpr int HUB_TILE_FLOATS = 8192;  // 32 KB staging buffer: 256 edges x 32 columns or 1024 edges x 8
+constexpr int HUB_LOADERS = 256;
+constexpr int HUB_THREADS = HUB_LOADERS + 32;
 
 // One group of U edges of one row.  FULL (all U edges exist, every chunk of the lane inside F) drops
 // the predicates; a separate predicate-free loop for full groups was measured and LOST 5-15 %
@@ -131,6 +143,13 @@ aggregate_kernel(const AggParams a) {
     if (row >= a.n_rows) return;
     const int F = a.F;
     const int beg = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+    if (a.hub != nullptr && end - beg >= HUB_ROW_EDGES) {
+        if (lane == 0) {
+            if (end - beg >= HUB_BIG_EDGES) a.hub[4 + atomicAdd(a.hub, 1)] = (int)row;
+            else a.hub[4 + a.hub_cap - 1 - atomicAdd(a.hub + 1, 1)] = (int)row;
+        }
+        return;
+    }
 
     for (int f0 = 0; f0 < F; f0 += TILE_F) {
         int foff[CH];
@@ -169,11 +188,199 @@ aggregate_kernel(const AggParams a) {
     }
 }
 
+
+// Hub rows.  A work item is (hub row, slice of feature columns): columns are independent, so slicing
+// keeps every column's additions in edge order while a row spreads over several CTAs.  In a CTA 256
+// loader threads (edge slots x lanes of 16 B) fetch a tile of edges, turn each fetched chunk into its
+// message (the arithmetic of edge_group above) and stage it in shared memory; the ninth warp then adds
+// the tile to its column sums one edge after the other while the loaders already have the next tile's
+// loads in flight.  Two size classes share the 32 KB staging buffer:
+//   hubs below HUB_BIG_EDGES: 32-column slices (one 128 B line per edge), 32 slots x U edges per tile --
+//     a tile costs one memory round trip, which bounds the item;
+//   bigger hubs: 8-column slices (one 32 B sector per edge), 128 slots x U edges per tile -- four times
+//     the edges per round trip, so the item runs at the speed of its chain of dependent additions
+//     (4 cycles per edge; 40 us for 19,000 edges), the floor for a sum in a prescribed order.
+// Big hubs are listed from the front of the work list and small ones from its back, items are handed out
+// front to back through a counter: longest first, and the order inside a class (atomics) does not matter.
+// The last CTA to leave puts the four counters back to zero for the next call.
+template <int MODE, bool BWD, bool RELU>
+__global__ void __launch_bounds__(HUB_THREADS, 2)
+aggregate_hub_kernel(const AggParams a) {
+    constexpr int U = MODE == MODE_XE ? 4 : 8;
+    static_assert((HUB_LOADERS / 2) * U * 8 <= HUB_TILE_FLOATS && (HUB_LOADERS / 8) * U * 32 <= HUB_TILE_FLOATS,
+                  "tile does not fit the staging buffer");
+    __shared__ float4 tile4[HUB_TILE_FLOATS / 4];
+    __shared__ int s_item;
+    const int tid = threadIdx.x;
+    const bool loader = tid < HUB_LOADERS;
+    const int F = a.F;
+    const int n_big = a.hub[0], n_small = a.hub[1];
+    if (n_big + n_small == 0) return;              // no hub in this structure: counters are still zero
+    // 8-column slices only while 32-column ones would leave CTAs of this grid without an item: read by
+    // sectors, a gathered row that has to come from DRAM costs more than its bytes
+    const int slices_small = (F + 31) >> 5;
+    const bool narrow = n_big * slices_small < (int)gridDim.x;
+    const int slices_big = narrow ? (F + 7) >> 3 : slices_small;
+    const int items_big = n_big * slices_big;
+    const int n_items = items_big + n_small * slices_small;
+    const int* list = a.hub + 4;
+
+    int next_item = 0;                  // thread 0: fetched one item ahead, so the counter's round trip hides
+    if (tid == 0) next_item = atomicAdd(a.hub + 2, 1);
+    for (;;) {
+        __syncthreads();                // everyone is done with s_item and the last tile of the previous item
+        if (tid == 0) s_item = next_item;
+        __syncthreads();
+        const int item = s_item;
+        if (item >= n_items) break;
+        if (tid == 0) next_item = atomicAdd(a.hub + 2, 1);
+        const bool big = item < items_big;
+        const int j = big ? item : item - items_big;
+        const int per = big ? slices_big : slices_small;
+        const int64_t row = big ? list[j / per] : list[a.hub_cap - 1 - j / per];
+        const int width = (big && narrow) ? 8 : 32; // columns of this slice
+        const int lps = width >> 2;                 // 16 B lanes per edge slot
+        const int slots = HUB_LOADERS / lps;        // edge slots per round
+        const int tile_edges = slots * U;
+        const int f0 = (j % per) * width;
+        const int beg = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+        const int l = tid % lps, s = (tid / lps) % slots;
+        const int c = tid - HUB_LOADERS;            // column of the slice a summing thread owns
+        const int foff = f0 + l * 4;
+        const bool fok = foff < F;          // F % 4 == 0 on this path: a 16 B chunk is inside or outside
+        const bool col_ok = !loader && c < width && f0 + c < F;
+        Vec<4> rx;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) rx.v[k] = 0.f;
+        if (loader && BWD && MODE == MODE_XE && RELU && fok) rx.load(a.row_x + row * a.row_x_ld + foff);
+        float acc = 0.f;
+        // the slot indices of a tile are fetched while the rows of the tile before it are in flight, so a
+        // tile costs one memory round trip instead of two dependent ones
+        int cidx[U];
+        int eid[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int e = beg + u * slots + s;
+            const bool ok = loader && e < end && fok;
+            cidx[u] = ok ? __ldg(a.col + e) : -1;
+            eid[u] = (ok && MODE != MODE_PLAIN) ? __ldg(a.perm + e) : 0;
+        }
+
+        for (int p = beg; p < end; p += tile_edges) {
+            Vec<4> m[U];
+            if (loader) {
+                float scal[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    scal[u] = 1.f;
+                    if (cidx[u] >= 0) {
+                        if (MODE == MODE_W) scal[u] = __ldg(a.edge_weight + eid[u]);
+                        else if (BWD && a.gather_cnt) scal[u] = __ldg(a.gather_cnt + cidx[u]);
+                    }
+                }
+                Vec<4> xe[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { m[u].v[k] = 0.f; xe[u].v[k] = 0.f; }
+                    if (cidx[u] >= 0) {
+                        m[u].load(a.gathered + (int64_t)cidx[u] * F + foff);
+                        if (MODE == MODE_XE) {
+                            const float* xp = a.edge_feat ? a.edge_feat + (int64_t)eid[u] * F
+                                                          : a.type_table + (int64_t)__ldg(a.edge_type + eid[u]) * F;
+                            xe[u].load(xp + foff);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {           // next tile's slots; the loads above are already issued
+                    const int e = p + tile_edges + u * slots + s;
+                    const bool ok = e < end && fok;
+                    cidx[u] = ok ? __ldg(a.col + e) : -1;
+                    eid[u] = (ok && MODE != MODE_PLAIN) ? __ldg(a.perm + e) : 0;
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float v = m[u].v[k];
+                        if (MODE == MODE_W) {
+                            v = __fmul_rn(scal[u], v);
+                        } else if (!BWD) {
+                            if (MODE == MODE_XE) v = __fadd_rn(v, xe[u].v[k]);
+                            if (RELU) v = v > 0.f ? v : 0.f;
+                        } else {
+                            if (a.gather_cnt) v = __fdiv_rn(v, scal[u]);
+                            if (MODE == MODE_XE && RELU) {
+                                const float pre = __fadd_rn(rx.v[k], xe[u].v[k]);
+                                v = pre > 0.f ? v : 0.f;
+                            }
+                        }
+                        m[u].v[k] = v;
+                    }
+                }
+            }
+            __syncthreads();                    // the previous tile has been summed
+            if (loader) {
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                    tile4[(u * slots + s) * lps + l] = make_float4(m[u].v[0], m[u].v[1], m[u].v[2], m[u].v[3]);
+            }
+            __syncthreads();
+            if (col_ok) {
+                // edge i of the tile sits at float i * width + c; 16 values are fetched ahead of the 16
+                // dependent additions of the batch before them
+                const float* t = reinterpret_cast<const float*>(tile4) + c;
+                const int n = min(tile_edges, end - p);
+                const int batches = n >> 4;
+                float cur[16];
+                if (batches > 0) {
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) cur[q] = t[q * width];
+                }
+                for (int b = 0; b < batches; ++b) {
+                    float nxt[16];
+                    const bool more = b + 1 < batches;
+                    if (more) {
+                        const float* tn = t + (b + 1) * 16 * width;
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) nxt[q] = tn[q * width];
+                    }
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) acc = __fadd_rn(acc, cur[q]);
+                    if (more) {
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) cur[q] = nxt[q];
+                    }
+                }
+                for (int i = batches << 4; i < n; ++i) acc = __fadd_rn(acc, t[i * width]);
+            }
+        }
+        if (col_ok) {
+            float r = acc;
+            if (!BWD && a.row_cnt) r = __fdiv_rn(r, __ldg(a.row_cnt + row));
+            if (BWD && MODE == MODE_PLAIN && RELU) r = __ldg(a.row_x + row * a.row_x_ld + f0 + c) > 0.f ? r : 0.f;
+            a.out[row * a.out_ld + f0 + c] = r;
+        }
+    }
+    if (tid == 0 && atomicAdd(a.hub + 3, 1) == (int)gridDim.x - 1) {
+        // every CTA has read the counts and drawn its last item before it counted itself out
+        a.hub[0] = 0; a.hub[1] = 0; a.hub[2] = 0; a.hub[3] = 0;
+    }
+}
+
 template <int VEC, int LANES, int CH, int MODE, bool BWD, bool RELU>
 static void launch(const AggParams& p, cudaStream_t s) {
     constexpr int ROWS_PER_BLOCK = 8 * (32 / LANES);
     unsigned grid = (unsigned)((p.n_rows + ROWS_PER_BLOCK - 1) / ROWS_PER_BLOCK);
     SG_LAUNCH(aggregate_kernel<VEC, LANES, CH, MODE, BWD, RELU><<<grid, 256, 0, s>>>(p));
+    if (VEC == 4 && p.hub != nullptr) {
+        // the number of hubs is only known on the device: a fixed grid (two CTAs per SM, fewer when the
+        // edge count bounds the work items below that) drains the list, and leaves at once if it is empty
+        const int64_t items = (p.num_edges / HUB_ROW_EDGES) * ((p.F + 7) / 8);
+        const int64_t full = 2 * (int64_t)sm_count();
+        SG_LAUNCH(aggregate_hub_kernel<MODE, BWD, RELU><<<(unsigned)(items < full ? items : full), HUB_THREADS, 0, s>>>(p));
+    }
 }
 
 template <int MODE, bool BWD, bool RELU>
@@ -217,6 +424,15 @@ using namespace stemgnn;
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
+// four counters + one slot per possible hub (disjoint rows of >= HUB_ROW_EDGES edges each)
+static size_t hub_ws_bytes(int64_t num_edges) { return sizeof(int) * (size_t)(4 + num_edges / HUB_ROW_EDGES + 1); }
+
+extern "C" int stemgnn_aggregate_hub_workspace(int64_t num_edges, size_t* bytes) {
+    SG_CHECK_ARG(bytes != nullptr && num_edges >= 0, "bytes is NULL or negative size");
+    *bytes = hub_ws_bytes(num_edges);
+    return STEMGNN_OK;
+}
+
 extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     SG_CHECK_ARG(a != nullptr, "args is NULL");
@@ -236,7 +452,7 @@ extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream
 
     AggParams p;
     p.rowptr = a->rowptr; p.col = a->col; p.perm = a->perm;
-    p.n_rows = a->n_rows; p.F = (int)a->feat;
+    p.n_rows = a->n_rows; p.num_edges = a->num_edges; p.F = (int)a->feat;
     p.gathered = a->gathered; p.row_cnt = a->row_cnt; p.gather_cnt = a->gather_cnt;
     p.edge_feat = a->edge_feat; p.type_table = a->type_table; p.edge_type = a->edge_type;
     p.edge_weight = a->edge_weight; p.row_x = a->row_x;
@@ -248,6 +464,14 @@ extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream
     bool vec4 = (a->feat % 4 == 0) && aligned16(a->gathered) && aligned16(a->out) &&
                 aligned16(a->edge_feat) && aligned16(a->type_table) && aligned16(a->row_x) &&
                 p.out_ld % 4 == 0 && p.row_x_ld % 4 == 0;
+    // hub rows (>= HUB_ROW_EDGES edges) go through the work list when the caller lends one; without it,
+    // or on the unaligned scalar path, every row stays in the row-per-group kernel
+    p.hub = nullptr; p.hub_cap = 0;
+    if (a->hub_ws != nullptr && vec4 && a->num_edges >= HUB_ROW_EDGES) {
+        SG_CHECK_ARG(a->hub_ws_bytes >= hub_ws_bytes(a->num_edges), "hub_ws smaller than stemgnn_aggregate_hub_workspace");
+        p.hub = static_cast<int*>(a->hub_ws);
+        p.hub_cap = (int)(a->num_edges / HUB_ROW_EDGES + 1);
+    }
     const int mode = has_w ? MODE_W : (has_xe ? MODE_XE : MODE_PLAIN);
     // a backward pass with neither a per-edge division nor a relu mask is the plain sum over the
     // transposed structure: the forward kernel

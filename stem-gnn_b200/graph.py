@@ -16,8 +16,9 @@ from . import _lib
 
 class CSR:
     """rowptr[N+1] int32, col[E] int32 (other endpoint), perm[E] int32 (original edge id),
-    cnt[N] fp32 = max(degree, 1)."""
-    __slots__ = ("rowptr", "col", "perm", "cnt", "n", "e")
+    cnt[N] fp32 = max(degree, 1); hub = the scratch stemgnn_aggregate keeps its list of hub rows
+    (>= 256 edges) in -- one per CSR, so aggregations over one CSR must be ordered on one stream."""
+    __slots__ = ("rowptr", "col", "perm", "cnt", "n", "e", "hub")
 
     def __init__(self, edge_index, num_nodes, group_row):
         L = _lib.lib()
@@ -29,6 +30,8 @@ class CSR:
         self.perm = torch.empty(E, dtype=torch.int32, device=dev)
         self.cnt = torch.empty(N, dtype=torch.float32, device=dev)
         need = C.c_size_t(0)
+        _lib.check(L.stemgnn_aggregate_hub_workspace(E, C.byref(need)))
+        self.hub = torch.zeros(need.value, dtype=torch.uint8, device=dev)     # zeroed once; each call leaves it so
         _lib.check(L.stemgnn_csr_build_workspace(E, N, C.byref(need)))
         ws = _lib.workspace(need.value, dev)
         with _lib.traced("csr_build", E * (16 + 12) + (2 * N + 1) * 4, 0):

@@ -1,6 +1,7 @@
 """Autograd operators over the C-ABI: aggregation (K1 forward / K2 backward) and the VQ
 assignment / statistics / EMA calls (K3, K4)."""
 import ctypes as C
+import os
 
 import torch
 
@@ -37,6 +38,9 @@ def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_c
         edge_feat=_lib.ptr(edge_feat), type_table=_lib.ptr(type_table),
         edge_type=_lib.ptr(edge_type), edge_weight=_lib.ptr(edge_weight), row_x=_lib.ptr(row_x),
         act=act, backward=int(backward), out=_lib.ptr(out))
+    hub = getattr(csr, "hub", None)
+    if hub is not None and os.environ.get("STEMGNN_AGG_NO_HUB") != "1":      # A/B switch for scripts/agg_bench.py
+        a.hub_ws, a.hub_ws_bytes = hub.data_ptr(), hub.numel()
     if out_cols is not None:
         lo, hi = out_cols
         if hi - lo != gathered.size(1) or lo % 4:

@@ -84,6 +84,75 @@ def test_aggregate_edge_features_dense_and_table(f):
     _check(x, ei, n, reduce="mean", act="relu", table=table, etype=etype)
 
 
+def _hub_graph(n, e, seed, hubs):
+    """Uniform graph in which node h of `hubs` = {node: degree} receives (and node h + 1 sends) that many
+    edges, interleaved with the others so that a hub's edges are spread over the whole edge list."""
+    g = torch.Generator().manual_seed(seed)
+    ei = torch.randint(0, n, (2, e), generator=g)
+    pos = torch.randperm(e, generator=g)
+    at = 0
+    for node, deg in hubs.items():
+        ei[1, pos[at:at + deg]] = node
+        ei[0, pos[at + deg:at + 2 * deg]] = node + 1
+        at += 2 * deg
+    return ei
+
+
+@pytest.mark.parametrize("f", [8, 36, 100, 128, 256, 768])
+def test_hub_rows_every_mode_bit_exact(f):
+    """Rows of 255 / 256 / 257 edges sit on both sides of the hub threshold, 4,095 / 4,096 on both sides of
+    the big-hub one (8-column slices), 700 and 5,003 span several staged tiles with a ragged tail: same
+    bits as the sequential scatter_add_ in every mode."""
+    n, e = 600, 40000
+    hubs = {7: 255, 100: 256, 200: 257, 300: 700, 400: 5003, 500: 4096, 550: 4095}
+    g = torch.Generator().manual_seed(11)
+    ei = _hub_graph(n, e, 11, hubs)
+    deg = torch.bincount(ei[1], minlength=n)
+    assert deg[400] >= 5003 and deg[100] >= 256
+    x = torch.randn(n, f, generator=g)
+    _check(x, ei, n, reduce="mean", act="relu")
+    _check(x, ei, n, reduce="sum", act="none")
+    table = torch.randn(7, f, generator=g)
+    etype = torch.randint(0, 7, (e,), generator=g)
+    _check(x, ei, n, reduce="mean", act="relu", xe=table[etype])
+    _check(x, ei, n, reduce="mean", act="relu", table=table, etype=etype)
+
+
+def test_hub_rows_weighted_gcn_sum():
+    n, e, f = 500, 12000, 64
+    g = torch.Generator().manual_seed(12)
+    ei = _hub_graph(n, e, 12, {3: 2000, 250: 300})
+    xw = torch.randn(n, f, generator=g)
+    xc = xw.clone().requires_grad_(True)
+    ref = P.gcn_propagate_ref(xc, ei, n)
+    go = torch.randn(n, f, generator=g)
+    ref.backward(go)
+    g_sl, w = S.GraphStructure(ei.to(DEV), n).gcn()
+    xg = xw.to(DEV).requires_grad_(True)
+    out = S.aggregate(xg, g_sl, reduce="sum", edge_weight=w)
+    out.backward(go.to(DEV))
+    np.testing.assert_array_equal(out.detach().cpu().numpy(), ref.detach().numpy())
+    np.testing.assert_array_equal(xg.grad.cpu().numpy(), xc.grad.numpy())
+
+
+def test_hub_path_equals_row_per_group_path(monkeypatch):
+    """A/B inside the library: the same skewed graph with the hub list switched off (every row walked by
+    one group of lanes) gives identical bits, forward and backward."""
+    n, e, f = 20000, 400000, 256
+    g = torch.Generator().manual_seed(13)
+    ei = _hub_graph(n, e, 13, {11: 17000, 5000: 13155, 9000: 1000, 15000: 256}).to(DEV)
+    x = torch.randn(n, f, generator=g).to(DEV)
+    go = torch.randn(n, f, generator=g).to(DEV)
+    res = []
+    for off in ("0", "1"):
+        monkeypatch.setenv("STEMGNN_AGG_NO_HUB", off)
+        xg = x.clone().requires_grad_(True)
+        out = S.aggregate(xg, S.GraphStructure(ei, n), reduce="mean", act="relu")
+        out.backward(go)
+        res.append((out.detach(), xg.grad))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
 def test_aggregate_empty_graph_and_empty_features():
     n = 10
     ei = torch.zeros(2, 0, dtype=torch.int64)
