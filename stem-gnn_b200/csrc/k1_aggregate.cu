@@ -12,6 +12,7 @@
 // No atomics, no E x F intermediates: per edge the kernel moves F*4 B (gathered row) + 4 B
 // (col) [+ F*4 B dense edge feature + 4 B perm], per row F*4 B out + 4 B rowptr.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace stemgnn {
 
@@ -214,6 +215,9 @@ aggregate_hub_kernel(const AggParams a) {
     const int tid = threadIdx.x;
     const bool loader = tid < HUB_LOADERS;
     const int F = a.F;
+    // launched with programmatic stream serialisation: the CTAs may already be resident while the
+    // row-per-group launch drains; its list and counters are visible from here on
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int n_big = a.hub[0], n_small = a.hub[1];
     if (n_big + n_small == 0) return;              // no hub in this structure: counters are still zero
     // 8-column slices only while 32-column ones would leave CTAs of this grid without an item: read by
@@ -379,7 +383,20 @@ static void launch(const AggParams& p, cudaStream_t s) {
         // edge count bounds the work items below that) drains the list, and leaves at once if it is empty
         const int64_t items = (p.num_edges / HUB_ROW_EDGES) * ((p.F + 7) / 8);
         const int64_t full = 2 * (int64_t)sm_count();
-        SG_LAUNCH(aggregate_hub_kernel<MODE, BWD, RELU><<<(unsigned)(items < full ? items : full), HUB_THREADS, 0, s>>>(p));
+        // programmatic dependent launch: the hub grid's launch latency overlaps the first launch's tail (it
+        // waits at griddepcontrol.wait), which is what the second launch costs a structure without hubs
+        static const bool pdl = [] { const char* e = getenv("STEMGNN_AGG_PDL"); return e ? atoi(e) != 0 : true; }();   // STEMGNN_AGG_PDL=0: plain stream order
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(items < full ? items : full));
+        cfg.blockDim = dim3(HUB_THREADS);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        SG_LAUNCH(cudaLaunchKernelEx(&cfg, aggregate_hub_kernel<MODE, BWD, RELU>, p));
     }
 }
 
