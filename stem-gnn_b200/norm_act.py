@@ -77,9 +77,9 @@ class BatchSync:
         if self._gather is not None:
             return self._gather(v)
         import torch.distributed as dist
-        out = v.new_empty((self.world, v.numel()))
-        dist.all_gather_into_tensor(out, v.contiguous(), group=self.group)
-        return out
+        out = v.new_empty(self.world * v.numel())      # flat: gloo rejects a [world, len] output, nccl takes both
+        dist.all_gather_into_tensor(out, v.contiguous().view(-1), group=self.group)
+        return out.view(self.world, v.numel())
 
     def reduce(self, v):
         if self._reduce is not None:
@@ -94,8 +94,14 @@ def synced_batch_stats(x, sync: BatchSync):
     rank (identical results everywhere): mean = sum n_r mean_r / N, var = sum n_r (var_r + (mean_r -
     mean)^2) / N."""
     mean, var = batch_stats(x)
+    return merge_batch_stats(mean, var, x.size(0), sync)
+
+
+def merge_batch_stats(mean, var, rows, sync: BatchSync):
+    """The host side of `synced_batch_stats`: this rank's (mean, biased variance, row count) gathered
+    and combined (plain tensor arithmetic on [world, F] -- runs on any device, tested over gloo)."""
     f = mean.numel()
-    pack = torch.cat([mean, var, mean.new_full((1,), float(x.size(0)))])
+    pack = torch.cat([mean, var, mean.new_full((1,), float(rows))])
     g = sync.gather(pack)
     w = (g[:, -1] / float(sync.batch_rows)).unsqueeze(1)
     gmean = (w * g[:, :f]).sum(0)

@@ -95,3 +95,52 @@ def test_partitioned_aggregation_two_ranks_gloo():
         p.join(100)
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert dict(ret) == {0: 1, 1: 1}
+
+
+def _bn_worker(rank, world, port, n, f, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from stemgnn_b200.norm_act import BatchSync, merge_batch_stats
+        from stemgnn_b200.partition import partition_1d
+        g = torch.Generator().manual_seed(5)
+        x = (torch.randn(n, f, generator=g) * 3 + 7).double()
+        gy = torch.randn(n, f, generator=g).double()
+        lo, hi = partition_1d(n, world)[rank]
+        xl, gl = x[lo:hi], gy[lo:hi]
+        sync = BatchSync(n, world)                                   # torch.distributed defaults
+        # forward: (mean, biased var, rows) of the uneven shares -> the full batch's
+        mean, var = merge_batch_stats(xl.mean(0), xl.var(0, unbiased=False), hi - lo, sync)
+        assert torch.allclose(mean, x.mean(0), rtol=1e-12, atol=1e-12)
+        assert torch.allclose(var, x.var(0, unbiased=False), rtol=1e-11, atol=1e-12)
+        # backward: the two column sums are the only thing the ranks exchange; with the batch's sums and
+        # row count the local rows of the input gradient equal those of the full-batch formula
+        invstd = (var + 1e-5).rsqrt()
+        xhat_l = (xl - mean) * invstd
+        sums = sync.reduce(torch.cat([gl.sum(0), (gl * xhat_l).sum(0)]))
+        sum_g, sum_gx = sums[:f], sums[f:]
+        gx_l = invstd * (gl - sum_g / n - xhat_l * sum_gx / n)       # gamma = 1
+        xr = x.clone().requires_grad_(True)
+        torch.nn.functional.batch_norm(xr, None, None, training=True, eps=1e-5).backward(gy)
+        assert torch.allclose(gx_l, xr.grad[lo:hi], rtol=1e-9, atol=1e-11)
+        ret[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_batchnorm_statistics_over_two_ranks_gloo():
+    """norm_act.BatchSync over real collectives (all_gather_into_tensor / all_reduce on gloo): the merge of
+    per-rank statistics and the split of the backward at its reduction (what K7 does on each side of
+    stemgnn_bn_act_backward / _backward_apply) against torch's full-batch batch_norm in float64."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_bn_worker, args=(r, world, port, 1001, 20, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(100)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert dict(ret) == {0: 1, 1: 1}
