@@ -59,9 +59,33 @@ def peaks():
     return dict(hbm=6650.0, tc=1590.0, tc_sus=1400.0, src="fallback")
 
 
+ZIPF_CAP = 17000        # no destination above ~17,000 in-edges (ogbn-products' largest: 17,481)
+
+
+class ZipfNodes:
+    """SURVEY.md 8d's power-law variant: node ids drawn with p(rank k) ~ 1/k (Zipf, alpha = 1), no rank
+    above `ZIPF_CAP` edges in expectation, ranks scattered over the ids by a seeded permutation (so the
+    hubs are not the first rows a launch starts).  Inverse-CDF sampling on the host, float64."""
+
+    def __init__(self, n, e, g):
+        base = 1.0 / torch.arange(1, n + 1, dtype=torch.float64)
+        wgt = base
+        for _ in range(30):                      # fixed point of "largest probability = ZIPF_CAP / e"
+            wgt = torch.minimum(base, wgt.sum() * (ZIPF_CAP / e))
+        self.cdf = torch.cumsum(wgt / wgt.sum(), 0)
+        self.cdf[-1] = 1.0
+        self.ids = torch.randperm(n, generator=g)
+
+    def draw(self, count, g):
+        u = torch.rand(count, dtype=torch.float64, generator=g)
+        return self.ids[torch.searchsorted(self.cdf, u, right=True).clamp_(max=self.ids.numel() - 1)]
+
+
 def synth_graph(w, seed, device="cpu"):
     g = torch.Generator(device="cpu").manual_seed(seed)
     ei = torch.randint(0, w["n"], (2, w["e"]), generator=g)
+    if w.get("degree") == "zipf":
+        ei[1] = ZipfNodes(w["n"], w["e"], g).draw(w["e"], g)
     x = torch.randn(w["n"], w["f"], generator=g)
     return x.to(device), ei.to(device)
 
@@ -430,6 +454,8 @@ def run_ours(args, w):
     top = max(kern, key=lambda k: kern[k]["ms_per_step"])
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     traffic = json.load(open(traffic_file)).get(args.workload, {}) if os.path.exists(traffic_file) else {}
+    if w.get("degree") == "zipf":
+        traffic = {}                      # the ncu captures are of the uniform headline configuration
     rooflines = {}
     for name in kern:
         if "gbps_alg" not in kern[name]:
@@ -501,8 +527,12 @@ def run_partitioned(args, w):
     lo, hi = S.partition_1d(n, world)[rank]
     # same seeded global edge list on every rank, generated in slices to bound host memory
     fwd_parts, bwd_parts, chunk = [], [], 1 << 24
+    zipf = ZipfNodes(n, e, g) if w.get("degree") == "zipf" else None
     for c0 in range(0, e, chunk):
-        ei = torch.randint(0, n, (2, min(chunk, e - c0)), generator=g).to(dev)
+        ei = torch.randint(0, n, (2, min(chunk, e - c0)), generator=g)
+        if zipf is not None:
+            ei[1] = zipf.draw(ei.size(1), g)
+        ei = ei.to(dev)
         fwd_parts.append(S.local_edges(ei, lo, hi, 1)[0])
         bwd_parts.append(S.local_edges(ei, lo, hi, 0)[0])
         del ei
@@ -625,8 +655,14 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--partition", action="store_true",
                     help="1-D destination partition across the ranks (strong scaling, static graph)")
+    ap.add_argument("--degree", default="uniform", choices=["uniform", "zipf"],
+                    help="in-degree distribution of the synthetic graph: uniform endpoints (the headline "
+                         "configuration) or SURVEY.md 8d's power-law variant with hubs of up to ~17,000 in-edges")
     args = ap.parse_args()
-    w = WORKLOADS[args.workload]
+    w = dict(WORKLOADS[args.workload])
+    if args.degree == "zipf":
+        w["degree"] = "zipf"
+        w["desc"] += f"; destinations Zipf(1) over a random node order, capped at ~{ZIPF_CAP:,} in-edges"
     if args.impl == "reference":
         run_reference(args, w)
     elif args.partition or args.workload == "products":
