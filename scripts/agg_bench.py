@@ -49,11 +49,12 @@ def run(n, e, f, reps=5, seed=0, skew=False):
                           fwd_gather_GBps=round(gb_gather / res["fwd"] * 1e6), fwd_min_GBps=round(gb_min / res["fwd"] * 1e6))), flush=True)
 
 if __name__ == "__main__":
-    print("tag", sys.argv[1:], "no_hub =", os.environ.get("STEMGNN_AGG_NO_HUB"))
+    print("tag", sys.argv[1:], "no_hub =", os.environ.get("STEMGNN_AGG_NO_HUB"), "ring =", os.environ.get("STEMGNN_AGG_HUB_RING"))
     if "skew" in sys.argv[1:]:
         for sk in (False, True):
             run(169343, 1166243, 128, skew=sk); run(169343, 1166243, 256, skew=sk)
-        run(2449029 // 2, 61859140 // 2, 256, reps=2, skew=True)
+        if "small" not in sys.argv[1:]:
+            run(2449029 // 2, 61859140 // 2, 256, reps=2, skew=True)
         sys.exit(0)
     run(169343, 1166243, 128); run(169343, 1166243, 256)
     run(2449029 // 2, 61859140 // 2, 100); run(2449029 // 2, 61859140 // 2, 256)

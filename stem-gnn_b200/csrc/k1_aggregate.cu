@@ -373,31 +373,195 @@ aggregate_hub_kernel(const AggParams a) {
     }
 }
 
+// The same work items for the plain mode (message = the gathered row itself, relu at most): the loaders
+// copy with cp.async straight into a ring of three 32 KB stages instead of staging in registers, so two
+// tiles per CTA are in flight while a third is summed (the register version holds 32 registers of payload
+// per loader and keeps one).  The relu moves into the summing warp; everything else is as above.
+constexpr int HUB_RING_STAGES = 3;
+constexpr int HUB_RING_BYTES = HUB_RING_STAGES * HUB_TILE_FLOATS * (int)sizeof(float);
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool BWD, bool RELU>
+__global__ void __launch_bounds__(HUB_THREADS, 2)
+aggregate_hub_ring_kernel(const AggParams a) {
+    constexpr int U = 8;
+    constexpr int NST = HUB_RING_STAGES;
+    extern __shared__ float4 ring4[];
+    __shared__ int s_item;
+    const int tid = threadIdx.x;
+    const bool loader = tid < HUB_LOADERS;
+    const int F = a.F;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int n_big = a.hub[0], n_small = a.hub[1];
+    if (n_big + n_small == 0) return;
+    const int slices_small = (F + 31) >> 5;
+    const bool narrow = n_big * slices_small < (int)gridDim.x;
+    const int slices_big = narrow ? (F + 7) >> 3 : slices_small;
+    const int items_big = n_big * slices_big;
+    const int n_items = items_big + n_small * slices_small;
+    const int* list = a.hub + 4;
+
+    int next_item = 0;
+    if (tid == 0) next_item = atomicAdd(a.hub + 2, 1);
+    for (;;) {
+        __syncthreads();                // s_item and every stage of the previous item are free
+        if (tid == 0) s_item = next_item;
+        __syncthreads();
+        const int item = s_item;
+        if (item >= n_items) break;
+        if (tid == 0) next_item = atomicAdd(a.hub + 2, 1);
+        const bool big = item < items_big;
+        const int j = big ? item : item - items_big;
+        const int per = big ? slices_big : slices_small;
+        const int64_t row = big ? list[j / per] : list[a.hub_cap - 1 - j / per];
+        const int width = (big && narrow) ? 8 : 32;
+        const int lps = width >> 2;
+        const int slots = HUB_LOADERS / lps;
+        const int tile_edges = slots * U;
+        const int f0 = (j % per) * width;
+        const int beg = __ldg(a.rowptr + row), end = __ldg(a.rowptr + row + 1);
+        const int n_tiles = (end - beg + tile_edges - 1) / tile_edges;
+        const int l = tid % lps, s = (tid / lps) % slots;
+        const int c = tid - HUB_LOADERS;
+        const int foff = f0 + l * 4;
+        const bool fok = loader && foff < F;
+        const bool col_ok = !loader && c < width && f0 + c < F;
+        const float* src = a.gathered + foff;
+
+        int cidx[U];                    // gathered rows of the tile to be issued next
+        auto load_idx = [&](int tile) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int e = beg + tile * tile_edges + u * slots + s;
+                cidx[u] = (fok && tile < n_tiles && e < end) ? __ldg(a.col + e) : -1;
+            }
+        };
+        auto issue = [&](int tile) {
+            float4* st = ring4 + (tile % NST) * (HUB_TILE_FLOATS / 4);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (cidx[u] >= 0) cp_async16(st + (u * slots + s) * lps + l, src + (int64_t)cidx[u] * F);
+            cp_async_commit();
+        };
+        // prologue: the slot indices of the first NST - 1 tiles in ONE round trip, then their copies
+        static_assert(NST == 3, "the prologue below fills two stages");
+        int first[U];
+        load_idx(0);
+#pragma unroll
+        for (int u = 0; u < U; ++u) first[u] = cidx[u];
+        load_idx(1);
+        {
+            float4* st = ring4;
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (first[u] >= 0) cp_async16(st + (u * slots + s) * lps + l, src + (int64_t)first[u] * F);
+            cp_async_commit();
+        }
+        issue(1);
+        load_idx(2);
+
+        float acc = 0.f;
+        for (int t = 0; t < n_tiles; ++t) {
+            cp_async_wait<NST - 2>();   // this thread's copies of tile t have landed
+            __syncthreads();            // ... everyone's have, and tile t - 1 has been summed
+            if (loader) {
+                issue(t + NST - 1);     // into the stage tile t - 1 just left
+                load_idx(t + NST);
+            } else if (col_ok) {
+                const float* tl = reinterpret_cast<const float*>(ring4 + (t % NST) * (HUB_TILE_FLOATS / 4)) + c;
+                const int n = min(tile_edges, end - beg - t * tile_edges);
+                const int batches = n >> 4;
+                float cur[16];
+                if (batches > 0) {
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) cur[q] = tl[q * width];
+                }
+                for (int b = 0; b < batches; ++b) {
+                    float nxt[16];
+                    const bool more = b + 1 < batches;
+                    if (more) {
+                        const float* tn = tl + (b + 1) * 16 * width;
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) nxt[q] = tn[q * width];
+                    }
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) {
+                        float v = cur[q];
+                        if (!BWD && RELU) v = v > 0.f ? v : 0.f;
+                        acc = __fadd_rn(acc, v);
+                    }
+                    if (more) {
+#pragma unroll
+                        for (int q = 0; q < 16; ++q) cur[q] = nxt[q];
+                    }
+                }
+                for (int i = batches << 4; i < n; ++i) {
+                    float v = tl[i * width];
+                    if (!BWD && RELU) v = v > 0.f ? v : 0.f;
+                    acc = __fadd_rn(acc, v);
+                }
+            }
+        }
+        cp_async_wait<0>();             // only empty groups are left
+        if (col_ok) {
+            float r = acc;
+            if (!BWD && a.row_cnt) r = __fdiv_rn(r, __ldg(a.row_cnt + row));
+            if (BWD && RELU) r = __ldg(a.row_x + row * a.row_x_ld + f0 + c) > 0.f ? r : 0.f;
+            a.out[row * a.out_ld + f0 + c] = r;
+        }
+    }
+    if (tid == 0 && atomicAdd(a.hub + 3, 1) == (int)gridDim.x - 1) {
+        a.hub[0] = 0; a.hub[1] = 0; a.hub[2] = 0; a.hub[3] = 0;
+    }
+}
+
+// Second launch of an aggregation whose caller lent a hub scratch.  The number of hubs is only known on
+// the device: a fixed grid (two CTAs per SM, fewer when the edge count bounds the work items below that)
+// drains the list, and leaves at once if it is empty.  It is a programmatic dependent launch: the grid's
+// launch latency overlaps the first launch's tail (it waits at griddepcontrol.wait), which is what the
+// second launch costs a structure without hubs.
+template <int MODE, bool BWD, bool RELU>
+static void launch_hub(const AggParams& p, cudaStream_t s) {
+    static const bool pdl = [] { const char* e = getenv("STEMGNN_AGG_PDL"); return e ? atoi(e) != 0 : true; }();
+    static const bool ring_on = [] { const char* e = getenv("STEMGNN_AGG_HUB_RING"); return e ? atoi(e) != 0 : true; }();
+    const int64_t items = (p.num_edges / HUB_ROW_EDGES) * ((p.F + 7) / 8);
+    const int64_t full = 2 * (int64_t)sm_count();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(items < full ? items : full));
+    cfg.blockDim = dim3(HUB_THREADS);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    if constexpr (MODE == MODE_PLAIN) {
+        static const bool ring_ok = cudaFuncSetAttribute(aggregate_hub_ring_kernel<BWD, RELU>,
+                                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                         HUB_RING_BYTES) == cudaSuccess;
+        if (ring_on && ring_ok && !(BWD && p.gather_cnt)) {
+            cfg.dynamicSmemBytes = HUB_RING_BYTES;
+            SG_LAUNCH(cudaLaunchKernelEx(&cfg, aggregate_hub_ring_kernel<BWD, RELU>, p));
+            return;
+        }
+    }
+    SG_LAUNCH(cudaLaunchKernelEx(&cfg, aggregate_hub_kernel<MODE, BWD, RELU>, p));
+}
+
 template <int VEC, int LANES, int CH, int MODE, bool BWD, bool RELU>
 static void launch(const AggParams& p, cudaStream_t s) {
     constexpr int ROWS_PER_BLOCK = 8 * (32 / LANES);
     unsigned grid = (unsigned)((p.n_rows + ROWS_PER_BLOCK - 1) / ROWS_PER_BLOCK);
     SG_LAUNCH(aggregate_kernel<VEC, LANES, CH, MODE, BWD, RELU><<<grid, 256, 0, s>>>(p));
-    if (VEC == 4 && p.hub != nullptr) {
-        // the number of hubs is only known on the device: a fixed grid (two CTAs per SM, fewer when the
-        // edge count bounds the work items below that) drains the list, and leaves at once if it is empty
-        const int64_t items = (p.num_edges / HUB_ROW_EDGES) * ((p.F + 7) / 8);
-        const int64_t full = 2 * (int64_t)sm_count();
-        // programmatic dependent launch: the hub grid's launch latency overlaps the first launch's tail (it
-        // waits at griddepcontrol.wait), which is what the second launch costs a structure without hubs
-        static const bool pdl = [] { const char* e = getenv("STEMGNN_AGG_PDL"); return e ? atoi(e) != 0 : true; }();   // STEMGNN_AGG_PDL=0: plain stream order
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)(items < full ? items : full));
-        cfg.blockDim = dim3(HUB_THREADS);
-        cfg.dynamicSmemBytes = 0;
-        cfg.stream = s;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = pdl ? 1 : 0;
-        SG_LAUNCH(cudaLaunchKernelEx(&cfg, aggregate_hub_kernel<MODE, BWD, RELU>, p));
-    }
+    if (VEC == 4 && p.hub != nullptr) launch_hub<MODE, BWD, RELU>(p, s);
 }
 
 template <int MODE, bool BWD, bool RELU>
