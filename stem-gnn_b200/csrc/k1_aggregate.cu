@@ -11,6 +11,8 @@
 // so U*CH independent 16 B loads per thread are in flight (HBM/L2-latency bound, guideline 7).
 // No atomics, no E x F intermediates: per edge the kernel moves F*4 B (gathered row) + 4 B
 // (col) [+ F*4 B dense edge feature + 4 B perm], per row F*4 B out + 4 B rowptr.
+// Rows of >= 256 edges ("hubs") are handed to a second launch that spreads a row over many CTAs by
+// column slices (aggregate_hub_kernel / aggregate_hub_ring_kernel): same order of additions per column.
 #include "common.cuh"
 #include <cstdlib>
 

@@ -35,6 +35,14 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert h.stemgnn_csr_build_workspace(-1, 4, C.byref(need)) == -1
     assert b"negative" in h.stemgnn_last_error()
     assert h.stemgnn_csr_build_workspace(1000, 10, C.byref(need)) == 0 and need.value > 0
+    # hub scratch: four counters and one slot per possible row of >= 256 edges
+    assert h.stemgnn_aggregate_hub_workspace(0, C.byref(need)) == 0 and need.value == 4 * 5
+    assert h.stemgnn_aggregate_hub_workspace(1166243, C.byref(need)) == 0 and need.value == 4 * (4 + 1166243 // 256 + 1)
+    assert h.stemgnn_aggregate_hub_workspace(-5, C.byref(need)) == -1
+    # a scratch smaller than that is refused before anything is launched
+    a = _lib.AggregateArgs(n_rows=10, n_gather_rows=10, num_edges=1000, feat=8, rowptr=16, col=16, gathered=16,
+                           out=16, hub_ws=16, hub_ws_bytes=8)
+    assert h.stemgnn_aggregate(C.byref(a), None) == -1 and b"hub_ws" in h.stemgnn_last_error()
 
 
 def test_no_cpu_fallback():
