@@ -31,6 +31,10 @@ typedef void* stemgnn_stream_t; /* cudaStream_t */
 #define STEMGNN_EUNSUPPORTED (-4)
 
 const char* stemgnn_last_error(void);
+/* Layout version of the argument structs below; a binding checks it at load time.
+ * 2: out_ld / row_x_ld in stemgnn_aggregate_args; 3: stemgnn_bn_act_backward_apply and the loop-side
+ * entry points (augmentations, sampler, l2norm, negative sampling); 4: hub_ws / hub_ws_bytes appended to
+ * stemgnn_aggregate_args. */
 int stemgnn_abi_version(void);
 /* number of CUDA kernels this library has launched in this process (all entry points) */
 uint64_t stemgnn_launch_count(void);
