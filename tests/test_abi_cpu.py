@@ -35,6 +35,10 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert h.stemgnn_csr_build_workspace(-1, 4, C.byref(need)) == -1
     assert b"negative" in h.stemgnn_last_error()
     assert h.stemgnn_csr_build_workspace(1000, 10, C.byref(need)) == 0 and need.value > 0
+    # maximum sizes: the structure's indices are int32
+    assert h.stemgnn_csr_build_workspace(2 ** 31 - 1, 10, C.byref(need)) == -1
+    assert h.stemgnn_csr_build_workspace(10, 2 ** 31, C.byref(need)) == -1
+    assert h.stemgnn_csr_build_workspace(2 ** 31 - 2, 2 ** 31 - 2, C.byref(need)) == 0 and need.value > 2 ** 34
     # hub scratch: four counters and one slot per possible row of >= 256 edges
     assert h.stemgnn_aggregate_hub_workspace(0, C.byref(need)) == 0 and need.value == 4 * 5
     assert h.stemgnn_aggregate_hub_workspace(1166243, C.byref(need)) == 0 and need.value == 4 * (4 + 1166243 // 256 + 1)
