@@ -88,3 +88,63 @@ def test_unsupported_options_raise():
         S.VectorQuantize(dim=8, codebook_size=4, stochastic_sample_codes=True)
     with pytest.raises(NotImplementedError):
         S.Encoder(8, 8, torch.nn.ReLU, 1, backbone="gat")
+
+
+def test_every_entry_point_validates_its_arguments_before_touching_the_device():
+    """Error behaviour of the boundary (no GPU needed: every check below precedes the first CUDA call):
+    a bad argument returns STEMGNN_EINVAL (-1) and leaves a message for stemgnn_last_error()."""
+    import ctypes as C
+    h = _lib.lib()
+    need = C.c_size_t(0)
+
+    def refused(rc, *words):
+        msg = h.stemgnn_last_error().decode()
+        assert rc == -1, (rc, msg)
+        assert all(w in msg for w in words), msg
+
+    # K3 VQ assignment
+    a = _lib.VqAssignArgs(heads=1, embed_heads=1, rows=10, codes=8, dim=16, metric=0, path=0)
+    assert h.stemgnn_vq_assign_workspace(C.byref(a), C.byref(need)) == 0
+    for field, value, words in [("metric", 2, ("metric",)), ("path", 3, ("path",)), ("embed_heads", 3, ("embed_heads",)),
+                                ("codes", 0, ("bad sizes",)), ("codes", 1 << 24, ("too large",)),
+                                ("rows", 2 ** 31, ("2^31",))]:
+        b = _lib.VqAssignArgs(heads=1, embed_heads=1, rows=10, codes=8, dim=16, metric=0, path=0)
+        setattr(b, field, value)
+        refused(h.stemgnn_vq_assign_workspace(C.byref(b), C.byref(need)), *words)
+    refused(h.stemgnn_vq_assign(C.byref(a), None, 0, None), "NULL")
+    # K7 BatchNorm: rows of float4, an empty batch has no statistics, dropout needs its seed
+    refused(h.stemgnn_bn_workspace(-1, 8, C.byref(need)), "bad arguments")
+    refused(h.stemgnn_bn_stats(16, 6, 16, 6, 16, 16, 16, 1 << 20, None), "multiple of 4")
+    refused(h.stemgnn_bn_stats(0, 8, 16, 8, 16, 16, 16, 1 << 20, None), "empty batch")
+    refused(h.stemgnn_bn_act_forward(4, 8, 16, 8, 16, 16, 16, 16, 1, 0.5, None, 16, 8, None), "seed")
+    refused(h.stemgnn_bn_act_forward(4, 8, 16, 8, 16, 16, 16, 16, 1, 1.0, 16, 16, 8, None), "[0, 1)")
+    refused(h.stemgnn_bn_act_backward_apply(8, 8, 16, 8, 16, 8, 16, 16, 16, 16, 0, 0.0, None, 16, 16, 4, 16, 8, None),
+            "batch_rows")
+    # K9 augmentations
+    refused(h.stemgnn_dropout_adj_workspace(2 ** 31, C.byref(need)), "2^31")
+    refused(h.stemgnn_dropout_adj_count(16, 10, None, 16, 1.5, 0, 16, 16, 1 << 20, None), "between 0 and 1")
+    refused(h.stemgnn_dropout_adj_count(16, 10, None, None, 0.5, 0, 16, 16, 1 << 20, None), "rand or seed")
+    refused(h.stemgnn_mask_fill(4, 6, 16, 6, None, None, 0.0, None, 0.0, 16, 6, None, None), "multiples of 4")
+    # K10 sampler: fan-outs
+    fan = (C.c_int32 * 2)(10, 10)
+    nc, ec = C.c_int64(0), C.c_int64(0)
+    assert h.stemgnn_neighbor_sample_bounds(1024, 1000, 5000, 2, fan, C.byref(nc), C.byref(ec), C.byref(need)) == 0
+    assert nc.value >= 1024 and ec.value >= 1024 * 10 and need.value > 0
+    refused(h.stemgnn_neighbor_sample_bounds(1024, 1000, 5000, 17, fan, C.byref(nc), C.byref(ec), C.byref(need)),
+            "num_hops")
+    refused(h.stemgnn_neighbor_sample_bounds(-1, 1000, 5000, 2, fan, C.byref(nc), C.byref(ec), C.byref(need)),
+            "negative")
+    # K12 negative sampling
+    refused(h.stemgnn_negative_sampling_workspace(-1, 10, C.byref(need)), "negative size")
+    refused(h.stemgnn_negative_sampling(16, 10, 1, 10, 10, 16, 16, 16, 16, 1 << 20, None), "two nodes")
+    # K1 aggregation
+    refused(h.stemgnn_aggregate(None, None), "NULL")
+    g = _lib.AggregateArgs(n_rows=4, n_gather_rows=4, num_edges=3, feat=8, rowptr=16, col=16, gathered=16, out=16,
+                           edge_feat=16, edge_weight=16, perm=16)
+    refused(h.stemgnn_aggregate(C.byref(g), None), "cannot be combined")
+    g = _lib.AggregateArgs(n_rows=4, n_gather_rows=4, num_edges=3, feat=8, rowptr=16, col=16, gathered=16, out=16,
+                           backward=1, act=1)
+    refused(h.stemgnn_aggregate(C.byref(g), None), "row_x")
+    g = _lib.AggregateArgs(n_rows=4, n_gather_rows=4, num_edges=3, feat=8, rowptr=16, col=16, gathered=16, out=16,
+                           out_ld=4)
+    refused(h.stemgnn_aggregate(C.byref(g), None), "out_ld")
