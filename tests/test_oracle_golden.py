@@ -207,3 +207,42 @@ def test_kmeans_init_oracle_matches_reference_golden(golden_dir, name):
     np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-7)
     for k in ("embed", "embed_avg", "cluster_size"):
         np.testing.assert_allclose(state[k].numpy(), g["after._codebook." + k], rtol=1e-5, atol=1e-6)
+
+
+def test_oracle_against_an_independent_sparse_formulation():
+    """The restated PyG arithmetic against scipy.sparse in float64 (a formulation that shares no code with
+    the oracle): mean aggregation = D^-1 A relu(x), its adjoint for the gradient, GCN = D^-1/2 (A + I') D^-1/2.
+    The graph has a 6,000-edge hub row and isolated nodes; fp32 sequential sums against float64: 1e-5 of the
+    output scale (the north-star bound), which also bounds what the order of additions can change."""
+    import scipy.sparse as sp
+    gen = torch.Generator().manual_seed(21)
+    n, e, f = 900, 20000, 24
+    ei = torch.randint(0, n, (2, e), generator=gen)
+    ei[1, :6000] = 17                                    # hub destination
+    ei[1][ei[1] == 5] = 6                                # node 5 isolated as a destination
+    x = torch.randn(n, f, generator=gen)
+    go = torch.randn(n, f, generator=gen)
+    src, dst = ei[0].numpy(), ei[1].numpy()
+    A = sp.coo_matrix((np.ones(e), (dst, src)), shape=(n, n)).tocsr()      # duplicates are summed: multi-edges count
+    deg = np.maximum(np.asarray(A.sum(1)).ravel(), 1.0)
+    x64 = x.double().numpy()
+    want = (A @ np.maximum(x64, 0.0)) / deg[:, None]
+    xc = x.clone().requires_grad_(True)
+    out = P.sage_propagate_ref(xc, ei, None, n, "mean")
+    out.backward(go)
+    scale = np.abs(want).max()
+    assert np.abs(out.detach().double().numpy() - want).max() <= 1e-5 * scale
+    assert np.all(out.detach().numpy()[5] == 0.0)
+    gwant = (A.T @ (go.double().numpy() / deg[:, None])) * (x64 > 0)
+    assert np.abs(xc.grad.double().numpy() - gwant).max() <= 1e-5 * np.abs(gwant).max()
+    # GCN: remaining self loops (existing loops keep their weight, the others get 1), symmetric normalisation
+    ei_sl, w = P.gcn_norm_ref(ei, n)
+    loops = src == dst
+    A2 = sp.coo_matrix((np.ones(int((~loops).sum())), (dst[~loops], src[~loops])), shape=(n, n)).tocsr()
+    A2 = A2 + sp.identity(n, format="csr")               # every node ends up with exactly one loop of weight 1
+    d2 = np.asarray(A2.sum(1)).ravel()
+    dis = 1.0 / np.sqrt(d2)
+    want_gcn = (sp.diags(dis) @ A2 @ sp.diags(dis)) @ x64
+    got = P.gcn_propagate_ref(x, ei, n)
+    assert np.abs(got.double().numpy() - want_gcn).max() <= 1e-5 * np.abs(want_gcn).max()
+    assert ei_sl.size(1) == int((~loops).sum()) + n and abs(float(w.double().sum()) - (sp.diags(dis) @ A2 @ sp.diags(dis)).sum()) < 1e-3
