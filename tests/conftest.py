@@ -13,6 +13,17 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")
 
 
+def pytest_sessionstart(session):
+    """A clean checkout has no libstemgnn_b200.so / liboracle_agg.so (they are git-ignored): build them
+    once before the first test (a no-op when they are newer than their sources).  A failing build is
+    reported by the tests that need the library, with its own message."""
+    try:
+        import __graft_entry__ as G
+        G.build()
+    except Exception as exc:  # noqa: BLE001
+        print(f"conftest: build() failed: {exc}", file=sys.stderr)
+
+
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
