@@ -148,3 +148,27 @@ def test_every_entry_point_validates_its_arguments_before_touching_the_device():
     g = _lib.AggregateArgs(n_rows=4, n_gather_rows=4, num_edges=3, feat=8, rowptr=16, col=16, gathered=16, out=16,
                            out_ld=4)
     refused(h.stemgnn_aggregate(C.byref(g), None), "out_ld")
+
+
+def test_model_shim_serves_the_reference_import_names(tmp_path):
+    """`shim/` in front of a reference checkout: `model.encoder` / `model.vq` are ours, the rest of the
+    reference's `model/` package (pt_model.py, ft_model.py) is still found in the checkout."""
+    import subprocess
+    import sys
+    ref = tmp_path / "checkout" / "model"
+    ref.mkdir(parents=True)
+    (ref / "__init__.py").write_text("")
+    (ref / "encoder.py").write_text("raise ImportError('the reference encoder must be shadowed')\n")
+    (ref / "pt_model.py").write_text("from model.encoder import Encoder\nfrom model.vq import VectorQuantize\nMARK = 41\n")
+    code = (
+        "import sys\n"
+        f"sys.path[:0] = [{os.path.join(ROOT, 'shim')!r}, {ROOT!r}, {str(tmp_path / 'checkout')!r}]\n"
+        "import stemgnn_b200 as S\n"
+        "from model.encoder import Encoder, MySAGEConv, MixtureSageLayer, InnerProductDecoder\n"
+        "from model.vq import VectorQuantize, EuclideanCodebook, CosineSimCodebook\n"
+        "import model.pt_model as pt\n"
+        "assert Encoder is S.Encoder and VectorQuantize is S.VectorQuantize and MySAGEConv is S.MySAGEConv\n"
+        "assert pt.MARK == 41 and pt.Encoder is S.Encoder and pt.VectorQuantize is S.VectorQuantize\n"
+        "print('shim ok')\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "shim ok" in r.stdout, r.stderr[-1500:]
