@@ -172,3 +172,22 @@ def test_model_shim_serves_the_reference_import_names(tmp_path):
         "print('shim ok')\n")
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "shim ok" in r.stdout, r.stderr[-1500:]
+
+
+def test_header_is_plain_c_and_links_from_c(tmp_path):
+    """include/stemgnn_b200.h compiled as C99 (-pedantic, warnings are errors) by a plain-C consumer that
+    links the shared library and makes host-only calls: the boundary has no C++ or torch types in it."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    _lib.lib()                                      # the library exists
+    exe = str(tmp_path / "abi_probe")
+    libdir = os.path.dirname(_lib.SO_PATH)
+    cc = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+                         os.path.join(ROOT, "examples", "abi_probe.c"), "-o", exe, "-L", libdir, "-lstemgnn_b200",
+                         f"-Wl,-rpath,{libdir}"], capture_output=True, text=True, timeout=120)
+    assert cc.returncode == 0, cc.stderr[-2000:]
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert run.returncode == 0, run.stdout + run.stderr
+    assert f"abi {_lib.ABI_VERSION}" in run.stdout and "launches so far 0" in run.stdout
