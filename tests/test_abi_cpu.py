@@ -191,3 +191,18 @@ def test_header_is_plain_c_and_links_from_c(tmp_path):
     run = subprocess.run([exe], capture_output=True, text=True, timeout=60)
     assert run.returncode == 0, run.stdout + run.stderr
     assert f"abi {_lib.ABI_VERSION}" in run.stdout and "launches so far 0" in run.stdout
+
+
+def test_library_depends_on_the_cuda_runtime_only():
+    """The boundary library links libcudart and the C/C++ runtimes -- no libtorch, no libc10, no Python:
+    PyTorch sits above the C-ABI (device memory, streams), not inside it."""
+    import shutil
+    import subprocess
+    if shutil.which("ldd") is None:
+        pytest.skip("no ldd")
+    _lib.lib()
+    out = subprocess.run(["ldd", _lib.SO_PATH], capture_output=True, text=True, timeout=60).stdout
+    names = [l.split()[0] for l in out.splitlines() if l.strip()]
+    assert any(n.startswith("libcudart") for n in names), out
+    for bad in ("libtorch", "libc10", "libpython", "libnccl", "libcublas", "libcudnn"):
+        assert not any(n.startswith(bad) for n in names), (bad, out)
