@@ -101,3 +101,37 @@ def test_dropout_adj_argument_errors():
     assert y is x and m.dtype == torch.bool and bool(m.all())
     with pytest.raises(S.StemGnnError):
         S.mask_feature(x, p=0.3)                                   # CPU tensor: no fallback
+
+
+def test_oracle_properties_on_random_cases():
+    """Randomised (hypothesis) invariants of the restatements, whatever the draw: dropout_adj keeps a
+    sub-multiset of the edges in order (and, undirected, a symmetric list built from row <= col edges only);
+    the CSR restatement is a stable grouping; a full-fan-out sample contains every in-edge of its frontier."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.integers(1, 30), st.integers(0, 120), st.floats(0.0, 1.0), st.integers(0, 2 ** 31 - 1))
+    def run(n, e, p, seed):
+        g = torch.Generator().manual_seed(seed)
+        ei = torch.randint(0, n, (2, e), generator=g)
+        rand = torch.rand(e, generator=g)
+        out, _, eid = dropout_adj_ref(ei, None, rand, p, False)
+        assert torch.equal(out, ei[:, eid]) and (eid[1:] > eid[:-1]).all() and torch.equal(eid, (rand >= p).nonzero().view(-1))
+        und, _, eid_u = dropout_adj_ref(ei, None, rand, p, True)
+        half = und.size(1) // 2
+        assert und.size(1) == 2 * half and torch.equal(und[:, :half], und[:, half:].flip(0))
+        assert (und[0, :half] <= und[1, :half]).all() and torch.equal(und[:, :half], ei[:, eid_u[:half]])
+        # stable grouping
+        rowptr, col, perm, deg = graph_ref.csr_build_ref(ei.numpy(), n, 1)
+        assert np.array_equal(perm, np.argsort(ei[1].numpy(), kind="stable")) and np.array_equal(col, ei[0].numpy()[perm])
+        assert np.array_equal(deg, np.bincount(ei[1].numpy(), minlength=n)) and rowptr[-1] == e
+        # full fan-out, one hop: every in-edge of every seed, seeds first in n_id
+        seeds = torch.randperm(n, generator=g)[: max(1, n // 3)]
+        n_id, src_l, dst_l, e_id, _ = neighbor_sample_ref(rowptr, col, perm, seeds.tolist(), [-1], None)
+        assert n_id[: seeds.numel()].tolist() == seeds.tolist()
+        want = torch.isin(ei[1], seeds).nonzero().view(-1)
+        assert sorted(e_id.tolist()) == want.tolist()
+        assert np.array_equal(n_id[src_l], ei[0].numpy()[e_id]) and np.array_equal(n_id[dst_l], ei[1].numpy()[e_id])
+        check_sample(ei.numpy(), n, rowptr, seeds.tolist(), [-1], n_id, src_l, dst_l, e_id)
+
+    run()
