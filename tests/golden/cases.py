@@ -54,3 +54,39 @@ def strided_sample_fn(samples, num):
     n = samples.shape[1]
     idx = (torch.arange(num, device=samples.device) * 7) % n
     return samples[:, idx]
+
+
+# BASELINE configs[1] (ogbn-arxiv-shaped) at its real codebook shape -- K = 512, D = 256, one head, no
+# projection -- in both variants SURVEY.md 8 names.  The fixtures are COMPACT (indices, loss, marginal sums
+# of every float output): inputs and the initial codebook are regenerated from seeds by c2_inputs(), whose
+# result is checked against checksums stored at generation time.
+VQ_C2_CASES = {
+    "vq_c2_euclid_ema": dict(dim=256, codebook_size=512, decay=0.8, commitment_weight=1.0),
+    "vq_c2_cosine_learnable": dict(dim=256, codebook_size=512, use_cosine_sim=True, ema_update=False,
+                                   learnable_codebook=True, commitment_weight=0.25),
+}
+VQ_C2_ROWS = 1536
+
+
+def c2_inputs(cfg):
+    """(x, initial codebook state) exactly as the reference module holds them after
+    `torch.manual_seed(0); VectorQuantize(**cfg)` (model/vq.py:54-57 uniform_init = kaiming_uniform_ on an
+    empty [1, K, D]; l2-normalised for cosine, vq.py:542; embed_avg = embed.clone(), cluster_size zeros for
+    Euclid :291-293 / zeros for cosine :562) followed by `x = torch.randn(rows, dim)`."""
+    import torch
+    import torch.nn.functional as F
+    torch.manual_seed(0)
+    t = torch.empty(1, cfg["codebook_size"], cfg["dim"])
+    torch.nn.init.kaiming_uniform_(t)
+    if cfg.get("use_cosine_sim"):
+        t = F.normalize(t, p=2, dim=-1)
+    state = dict(embed=t.clone(), embed_avg=t.clone(), cluster_size=torch.zeros(1, cfg["codebook_size"]))
+    x = torch.randn(VQ_C2_ROWS, cfg["dim"])
+    return x, state
+
+
+def marginals(a):
+    """Row and column sums in float64: a compact stand-in for a [rows, cols] float matrix."""
+    import numpy as np
+    a = np.asarray(a, dtype=np.float64).reshape(-1, a.shape[-1])
+    return a.sum(1), a.sum(0)

@@ -26,7 +26,8 @@ warnings.filterwarnings("ignore")
 from model.vq import VectorQuantize  # noqa: E402  (the reference's own module)
 from model.encoder import Encoder, InnerProductDecoder  # noqa: E402  (the reference's own module, on the shim)
 
-from tests.golden.cases import DEC_CASES, ENC_CASES, KMEANS_CASES, VQ_CASES, strided_sample_fn  # noqa: E402
+from tests.golden.cases import (DEC_CASES, ENC_CASES, KMEANS_CASES, VQ_C2_CASES, VQ_C2_ROWS, VQ_CASES,  # noqa: E402
+                                c2_inputs, marginals, strided_sample_fn)
 
 
 def gen_vq(name, cfg):
@@ -63,6 +64,34 @@ def gen_vq(name, cfg):
         out["after." + k] = v.detach().numpy()
     np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
     print(name, {k: v.shape for k, v in out.items() if not k.startswith(("before", "after"))})
+
+
+def gen_vq_c2(name, cfg):
+    """The reference module at BASELINE configs[1]'s codebook shape; compact fixture (see cases.py)."""
+    torch.manual_seed(0)
+    vq = VectorQuantize(**cfg)
+    vq.train()
+    x = torch.randn(VQ_C2_ROWS, cfg["dim"])
+    x2, state = c2_inputs(cfg)
+    assert torch.equal(x, x2), "c2_inputs() does not regenerate the reference's input"
+    for k in ("embed", "embed_avg", "cluster_size"):
+        assert torch.equal(getattr(vq._codebook, k).detach(), state[k]), f"c2_inputs() state mismatch: {k}"
+    x.requires_grad_(True)
+    q, ind, loss, oq = vq(x)
+    g = torch.randn(q.shape, generator=torch.Generator().manual_seed(2))
+    ((q * g).sum() + loss.sum()).backward()
+    out = dict(embed_ind=ind.numpy(), loss=loss.detach().numpy(),
+               x_check=np.array([x.detach().double().sum().item(), x.detach().double().abs().sum().item()]),
+               embed_check=np.array([state["embed"].double().sum().item(), state["embed"].double().abs().sum().item()]))
+    for key, t in (("quantize", q), ("g_x", x.grad), ("after.embed", vq._codebook.embed),
+                   ("after.embed_avg", vq._codebook.embed_avg)):
+        out[key + ".rows"], out[key + ".cols"] = marginals(t.detach().numpy())
+    out["after.cluster_size"] = vq._codebook.cluster_size.detach().numpy()
+    emb = vq._codebook.embed
+    if isinstance(emb, nn.Parameter) and emb.grad is not None:
+        out["g_embed.rows"], out["g_embed.cols"] = marginals(emb.grad.numpy())
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+    print(name, ind.shape, float(loss), int(np.unique(ind.numpy()).size), "codes used")
 
 
 def gen_kmeans(name, cfg):
@@ -142,6 +171,10 @@ if __name__ == "__main__":
         for k, v in KMEANS_CASES.items():
             gen_kmeans(k, v)
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "vq_c2":    # only the configs[1]-shaped VQ fixtures (added later)
+        for k, v in VQ_C2_CASES.items():
+            gen_vq_c2(k, v)
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "dec":      # only the decoder fixtures (added later)
         for k, v in DEC_CASES.items():
             gen_dec(k, v)
@@ -154,3 +187,5 @@ if __name__ == "__main__":
         gen_dec(k, v)
     for k, v in KMEANS_CASES.items():
         gen_kmeans(k, v)
+    for k, v in VQ_C2_CASES.items():
+        gen_vq_c2(k, v)

@@ -13,6 +13,7 @@ from oracle import propagate_ref as P
 from oracle.encoder_ref import EncoderRef
 from oracle.vq_ref import vq_forward_ref
 from oracle.decoder_ref import edge_dot_grad_ref, edge_dot_ref
+from tests.golden.cases import VQ_C2_CASES, c2_inputs, marginals  # noqa: E402
 from tests.golden.cases import DEC_CASES, ENC_CASES, VQ_CASES
 
 
@@ -246,3 +247,40 @@ def test_oracle_against_an_independent_sparse_formulation():
     got = P.gcn_propagate_ref(x, ei, n)
     assert np.abs(got.double().numpy() - want_gcn).max() <= 1e-5 * np.abs(want_gcn).max()
     assert ei_sl.size(1) == int((~loops).sum()) + n and abs(float(w.double().sum()) - (sp.diags(dis) @ A2 @ sp.diags(dis)).sum()) < 1e-3
+
+
+@pytest.mark.parametrize("name", sorted(VQ_C2_CASES))
+def test_vq_oracle_at_the_baseline_codebook_shape(golden_dir, name):
+    """BASELINE configs[1]'s real codebook shape (K = 512, D = 256; Euclid + EMA 0.8 and cosine +
+    learnable): the oracle against the reference's own VectorQuantize.  Compact fixture: code indices and
+    loss in full, row / column sums of every float matrix; inputs regenerated from seeds and checked."""
+    cfg = dict(VQ_C2_CASES[name])
+    g = _load(golden_dir, name)
+    x, state = c2_inputs(cfg)
+    np.testing.assert_allclose([x.double().sum().item(), x.double().abs().sum().item()], g["x_check"], rtol=0, atol=0)
+    np.testing.assert_allclose([state["embed"].double().sum().item(), state["embed"].double().abs().sum().item()],
+                               g["embed_check"], rtol=0, atol=0)
+    kw = vq_kwargs(cfg)
+    if cfg.get("learnable_codebook"):
+        state["embed"].requires_grad_(True)
+    x.requires_grad_(True)
+    q, ind, loss, _ = vq_forward_ref(x, state, training=True, **kw)
+    assert np.array_equal(ind.numpy(), g["embed_ind"])
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-8)
+    gq = torch.randn(q.shape, generator=torch.Generator().manual_seed(2))
+    ((q * gq).sum() + loss.sum()).backward()
+
+    def close(t, key):
+        rows, cols = marginals(t.detach().numpy())
+        scale = max(np.abs(g[key + ".rows"]).max(), 1e-12)
+        np.testing.assert_allclose(rows, g[key + ".rows"], rtol=0, atol=2e-5 * scale)
+        np.testing.assert_allclose(cols, g[key + ".cols"], rtol=0, atol=2e-5 * max(np.abs(g[key + ".cols"]).max(), 1e-12))
+
+    close(q, "quantize")
+    close(x.grad, "g_x")
+    close(state["embed"], "after.embed")
+    close(state["embed_avg"], "after.embed_avg")
+    np.testing.assert_allclose(state["cluster_size"].detach().numpy(), g["after.cluster_size"], rtol=1e-6, atol=1e-7)
+    if "g_embed.rows" in g:
+        close(state["embed"].grad, "g_embed")
+    assert np.unique(g["embed_ind"]).size > 400            # the case exercises most of the codebook
