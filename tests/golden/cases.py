@@ -90,3 +90,32 @@ def marginals(a):
     import numpy as np
     a = np.asarray(a, dtype=np.float64).reshape(-1, a.shape[-1])
     return a.sum(1), a.sum(0)
+
+
+# The shipped configuration at its real shape (pretrain.py:105-119 / finetune.py:132-146: cosine, 4 separate
+# heads x 128 codes x 768, 768 -> 3072 -> 768 projections, learnable codebook through the orthogonal loss),
+# which BASELINE configs[0] and configs[2] use.  Compact fixture like the C2 ones.
+VQ_SHIPPED_FULL = dict(dim=768, codebook_size=128, codebook_dim=768, heads=4, separate_codebook_per_head=True,
+                       decay=0.8, commitment_weight=10, use_cosine_sim=True, orthogonal_reg_weight=1,
+                       orthogonal_reg_max_codes=32, orthogonal_reg_active_codes_only=False, kmeans_init=False,
+                       ema_update=False)
+VQ_SHIPPED_ROWS = 384
+
+
+def shipped_inputs():
+    """(x, project_in, project_out, codebook state) as `torch.manual_seed(0); VectorQuantize(**VQ_SHIPPED_FULL)`
+    leaves them (model/vq.py:738-739 the two nn.Linear, then the codebook's l2norm(uniform_init) :542),
+    followed by `x = torch.randn(rows, 768)`."""
+    import torch
+    import torch.nn as nn
+    import torch.nn.functional as F
+    c = VQ_SHIPPED_FULL
+    torch.manual_seed(0)
+    inner = c["codebook_dim"] * c["heads"]
+    pin, pout = nn.Linear(c["dim"], inner), nn.Linear(inner, c["dim"])
+    t = torch.empty(c["heads"], c["codebook_size"], c["codebook_dim"])
+    nn.init.kaiming_uniform_(t)
+    t = F.normalize(t, p=2, dim=-1)
+    state = dict(embed=t.clone(), embed_avg=t.clone(), cluster_size=torch.zeros(c["heads"], c["codebook_size"]))
+    x = torch.randn(VQ_SHIPPED_ROWS, c["dim"])
+    return x, pin, pout, state

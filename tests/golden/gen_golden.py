@@ -27,7 +27,8 @@ from model.vq import VectorQuantize  # noqa: E402  (the reference's own module)
 from model.encoder import Encoder, InnerProductDecoder  # noqa: E402  (the reference's own module, on the shim)
 
 from tests.golden.cases import (DEC_CASES, ENC_CASES, KMEANS_CASES, VQ_C2_CASES, VQ_C2_ROWS, VQ_CASES,  # noqa: E402
-                                c2_inputs, marginals, strided_sample_fn)
+                                VQ_SHIPPED_FULL, VQ_SHIPPED_ROWS, c2_inputs, marginals, shipped_inputs,
+                                strided_sample_fn)
 
 
 def gen_vq(name, cfg):
@@ -92,6 +93,34 @@ def gen_vq_c2(name, cfg):
         out["g_embed.rows"], out["g_embed.cols"] = marginals(emb.grad.numpy())
     np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
     print(name, ind.shape, float(loss), int(np.unique(ind.numpy()).size), "codes used")
+
+
+def gen_vq_shipped_full():
+    """The reference module in the shipped configuration at its real shape; compact fixture."""
+    torch.manual_seed(0)
+    vq = VectorQuantize(**VQ_SHIPPED_FULL)
+    vq.train()
+    x = torch.randn(VQ_SHIPPED_ROWS, VQ_SHIPPED_FULL["dim"])
+    x2, pin, pout, state = shipped_inputs()
+    assert torch.equal(x, x2), "shipped_inputs() does not regenerate the reference's input"
+    assert torch.equal(vq.project_in.weight, pin.weight) and torch.equal(vq.project_in.bias, pin.bias)
+    assert torch.equal(vq.project_out.weight, pout.weight) and torch.equal(vq.project_out.bias, pout.bias)
+    for k in ("embed", "embed_avg", "cluster_size"):
+        assert torch.equal(getattr(vq._codebook, k).detach(), state[k]), f"shipped_inputs() state mismatch: {k}"
+    x.requires_grad_(True)
+    torch.manual_seed(1)                                   # the randperm of the orthogonal loss (vq.py:1024)
+    q, ind, loss, oq = vq(x)
+    g = torch.randn(q.shape, generator=torch.Generator().manual_seed(2))
+    ((q * g).sum() + loss.sum()).backward()
+    out = dict(embed_ind=ind.numpy(), loss=loss.detach().numpy(),
+               x_check=np.array([x.detach().double().sum().item(), x.detach().double().abs().sum().item()]),
+               embed_check=np.array([state["embed"].double().sum().item(), state["embed"].double().abs().sum().item()]),
+               pin_check=np.array([pin.weight.double().sum().item(), pout.weight.double().abs().sum().item()]))
+    for key, t in (("quantize", q), ("orig_quantize", oq), ("g_x", x.grad), ("g_embed", vq._codebook.embed.grad),
+                   ("g_project_in", vq.project_in.weight.grad), ("g_project_out", vq.project_out.weight.grad)):
+        out[key + ".rows"], out[key + ".cols"] = marginals(t.detach().numpy())
+    np.savez_compressed(os.path.join(OUT, "vq_shipped_full.npz"), **out)
+    print("vq_shipped_full", ind.shape, float(loss), [int(np.unique(ind[:, h].numpy()).size) for h in range(4)], "codes used per head")
 
 
 def gen_kmeans(name, cfg):
@@ -174,6 +203,7 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "vq_c2":    # only the configs[1]-shaped VQ fixtures (added later)
         for k, v in VQ_C2_CASES.items():
             gen_vq_c2(k, v)
+        gen_vq_shipped_full()
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "dec":      # only the decoder fixtures (added later)
         for k, v in DEC_CASES.items():
@@ -189,3 +219,4 @@ if __name__ == "__main__":
         gen_kmeans(k, v)
     for k, v in VQ_C2_CASES.items():
         gen_vq_c2(k, v)
+    gen_vq_shipped_full()

@@ -13,7 +13,7 @@ from oracle import propagate_ref as P
 from oracle.encoder_ref import EncoderRef
 from oracle.vq_ref import vq_forward_ref
 from oracle.decoder_ref import edge_dot_grad_ref, edge_dot_ref
-from tests.golden.cases import VQ_C2_CASES, c2_inputs, marginals  # noqa: E402
+from tests.golden.cases import VQ_C2_CASES, VQ_SHIPPED_FULL, c2_inputs, marginals, shipped_inputs  # noqa: E402
 from tests.golden.cases import DEC_CASES, ENC_CASES, VQ_CASES
 
 
@@ -284,3 +284,30 @@ def test_vq_oracle_at_the_baseline_codebook_shape(golden_dir, name):
     if "g_embed.rows" in g:
         close(state["embed"].grad, "g_embed")
     assert np.unique(g["embed_ind"]).size > 400            # the case exercises most of the codebook
+
+
+def test_vq_oracle_in_the_shipped_configuration_at_full_shape(golden_dir):
+    """The configuration the reference ships (pretrain.py:105-119): cosine, 4 separate heads x 128 codes x 768,
+    768 -> 3072 -> 768 projections, orthogonal loss on 32 random codes, commitment weight 10 -- at its real
+    shape, the oracle against the reference's own module (compact golden `vq_shipped_full.npz`)."""
+    cfg = dict(VQ_SHIPPED_FULL)
+    g = _load(golden_dir, "vq_shipped_full")
+    x, pin, pout, state = shipped_inputs()
+    np.testing.assert_allclose([x.double().sum().item(), x.double().abs().sum().item()], g["x_check"], rtol=0, atol=0)
+    np.testing.assert_allclose([state["embed"].double().sum().item(), state["embed"].double().abs().sum().item()],
+                               g["embed_check"], rtol=0, atol=0)
+    np.testing.assert_allclose([pin.weight.double().sum().item(), pout.weight.double().abs().sum().item()],
+                               g["pin_check"], rtol=0, atol=0)
+    state["embed"].requires_grad_(True)
+    x.requires_grad_(True)
+    torch.manual_seed(1)
+    q, ind, loss, oq = vq_forward_ref(x, state, training=True, project_in=pin, project_out=pout, **vq_kwargs(cfg))
+    assert tuple(ind.shape) == (x.size(0), 4) and np.array_equal(ind.numpy(), g["embed_ind"])
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-8)
+    gq = torch.randn(q.shape, generator=torch.Generator().manual_seed(2))
+    ((q * gq).sum() + loss.sum()).backward()
+    for key, t in (("quantize", q), ("orig_quantize", oq), ("g_x", x.grad), ("g_embed", state["embed"].grad),
+                   ("g_project_in", pin.weight.grad), ("g_project_out", pout.weight.grad)):
+        rows, cols = marginals(t.detach().numpy())
+        np.testing.assert_allclose(rows, g[key + ".rows"], rtol=0, atol=2e-5 * max(np.abs(g[key + ".rows"]).max(), 1e-12))
+        np.testing.assert_allclose(cols, g[key + ".cols"], rtol=0, atol=2e-5 * max(np.abs(g[key + ".cols"]).max(), 1e-12))
