@@ -119,3 +119,35 @@ def shipped_inputs():
     state = dict(embed=t.clone(), embed_avg=t.clone(), cluster_size=torch.zeros(c["heads"], c["codebook_size"]))
     x = torch.randn(VQ_SHIPPED_ROWS, c["dim"])
     return x, pin, pout, state
+
+
+# The encoder at BASELINE configs[1]'s widths (2-layer SAGE 128 -> 256 -> 256, BatchNorm, dropout off for
+# determinism) on a 3,000-node / 21,000-edge graph with a 2,000-edge hub row.  Parameters are OVERWRITTEN with
+# seeded values in state_dict order on both sides (seeded_parameters), so the fixture carries outputs only.
+ENC_C2 = dict(backbone="sage", normalize="batch", in_dim=128, hid=256, layers=2, n=3000, e=21000)
+
+
+def enc_c2_inputs():
+    import torch
+    g = torch.Generator().manual_seed(31)
+    c = ENC_C2
+    x = torch.randn(c["n"], c["in_dim"], generator=g)
+    ei = torch.randint(0, c["n"], (2, c["e"]), generator=g)
+    ei[1, :2000] = 11                    # hub destination
+    ei[1][ei[1] == 5] = 6                # node 5 has no in-edge
+    gz = torch.randn(c["n"], c["hid"], generator=g)
+    return x, ei, gz
+
+
+def seeded_parameters(module, seed=32):
+    """Overwrites every floating-point parameter / buffer of `module` in state_dict order with seeded values
+    (weights ~ 0.05 N(0,1); running_var kept positive); returns the module."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for k, v in module.state_dict().items():
+            if not v.dtype.is_floating_point:
+                continue
+            r = torch.randn(v.shape, generator=g) * 0.05
+            v.copy_(r.abs() + 0.5 if k.endswith("running_var") or k.endswith("norms.0.weight") or k.endswith("norms.1.weight") else r)
+    return module

@@ -27,8 +27,8 @@ from model.vq import VectorQuantize  # noqa: E402  (the reference's own module)
 from model.encoder import Encoder, InnerProductDecoder  # noqa: E402  (the reference's own module, on the shim)
 
 from tests.golden.cases import (DEC_CASES, ENC_CASES, KMEANS_CASES, VQ_C2_CASES, VQ_C2_ROWS, VQ_CASES,  # noqa: E402
-                                VQ_SHIPPED_FULL, VQ_SHIPPED_ROWS, c2_inputs, marginals, shipped_inputs,
-                                strided_sample_fn)
+                                ENC_C2, VQ_SHIPPED_FULL, VQ_SHIPPED_ROWS, c2_inputs, enc_c2_inputs, marginals,
+                                seeded_parameters, shipped_inputs, strided_sample_fn)
 
 
 def gen_vq(name, cfg):
@@ -123,6 +123,30 @@ def gen_vq_shipped_full():
     print("vq_shipped_full", ind.shape, float(loss), [int(np.unique(ind[:, h].numpy()).size) for h in range(4)], "codes used per head")
 
 
+def gen_enc_c2():
+    """The reference Encoder (on oracle/pyg_shim) at configs[1]'s widths; compact fixture."""
+    c = ENC_C2
+    enc = Encoder(c["in_dim"], c["hid"], nn.ReLU, c["layers"], backbone=c["backbone"], normalize=c["normalize"],
+                  dropout=0.0)
+    seeded_parameters(enc).train()
+    x, ei, gz = enc_c2_inputs()
+    x.requires_grad_(True)
+    z = enc(x, ei)
+    (z * gz).sum().backward()
+    out = dict(keys=np.array(sorted(enc.state_dict())))
+    out["z.rows"], out["z.cols"] = marginals(z.detach().numpy())
+    out["g_x.rows"], out["g_x.cols"] = marginals(x.grad.numpy())
+    out["z.sample"] = z.detach().numpy()[[0, 5, 11, 1234, 2999]]
+    out["g_x.sample"] = x.grad.numpy()[[0, 5, 11, 1234, 2999]]
+    for k, p in enc.named_parameters():
+        if p.grad is not None:
+            out["grad." + k + ".rows"], out["grad." + k + ".cols"] = marginals(p.grad.numpy().reshape(p.shape[0], -1))
+    for k in ("norms.0.running_mean", "norms.0.running_var", "norms.1.running_mean", "norms.1.running_var"):
+        out["after." + k] = enc.state_dict()[k].numpy()
+    np.savez_compressed(os.path.join(OUT, "enc_c2.npz"), **out)
+    print("enc_c2", z.shape, float(z.abs().mean()))
+
+
 def gen_kmeans(name, cfg):
     """First training forward of a kmeans_init module: init_embed_ runs the reference's own kmeans()."""
     torch.manual_seed(0)
@@ -204,6 +228,7 @@ if __name__ == "__main__":
         for k, v in VQ_C2_CASES.items():
             gen_vq_c2(k, v)
         gen_vq_shipped_full()
+        gen_enc_c2()
         sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "dec":      # only the decoder fixtures (added later)
         for k, v in DEC_CASES.items():
@@ -220,3 +245,4 @@ if __name__ == "__main__":
     for k, v in VQ_C2_CASES.items():
         gen_vq_c2(k, v)
     gen_vq_shipped_full()
+    gen_enc_c2()

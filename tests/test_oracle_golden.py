@@ -13,7 +13,8 @@ from oracle import propagate_ref as P
 from oracle.encoder_ref import EncoderRef
 from oracle.vq_ref import vq_forward_ref
 from oracle.decoder_ref import edge_dot_grad_ref, edge_dot_ref
-from tests.golden.cases import VQ_C2_CASES, VQ_SHIPPED_FULL, c2_inputs, marginals, shipped_inputs  # noqa: E402
+from tests.golden.cases import (ENC_C2, VQ_C2_CASES, VQ_SHIPPED_FULL, c2_inputs, enc_c2_inputs, marginals,  # noqa: E402
+                                seeded_parameters, shipped_inputs)
 from tests.golden.cases import DEC_CASES, ENC_CASES, VQ_CASES
 
 
@@ -311,3 +312,33 @@ def test_vq_oracle_in_the_shipped_configuration_at_full_shape(golden_dir):
         rows, cols = marginals(t.detach().numpy())
         np.testing.assert_allclose(rows, g[key + ".rows"], rtol=0, atol=2e-5 * max(np.abs(g[key + ".rows"]).max(), 1e-12))
         np.testing.assert_allclose(cols, g[key + ".cols"], rtol=0, atol=2e-5 * max(np.abs(g[key + ".cols"]).max(), 1e-12))
+
+
+def test_encoder_oracle_at_the_baseline_widths(golden_dir):
+    """The reference's Encoder (model/encoder.py on oracle/pyg_shim) at BASELINE configs[1]'s widths -- 2-layer
+    SAGE 128 -> 256 -> 256 with BatchNorm -- on 3,000 nodes / 21,000 edges with a 2,000-edge hub row: the oracle
+    gives the same bits (sampled rows) and the same marginal sums; parameters seeded identically on both sides."""
+    c = ENC_C2
+    g = _load(golden_dir, "enc_c2")
+    enc = EncoderRef(c["in_dim"], c["hid"], nn.ReLU, c["layers"], backbone=c["backbone"], normalize=c["normalize"],
+                     dropout=0.0)
+    assert sorted(enc.state_dict()) == g["keys"].tolist(), "state_dict keys (and so the seeded values) must match"
+    seeded_parameters(enc).train()
+    x, ei, gz = enc_c2_inputs()
+    x.requires_grad_(True)
+    z = enc(x, ei)
+    (z * gz).sum().backward()
+    rows = [0, 5, 11, 1234, 2999]
+    np.testing.assert_array_equal(z.detach().numpy()[rows], g["z.sample"])          # same ops, same order
+    np.testing.assert_array_equal(x.grad.numpy()[rows], g["g_x.sample"])
+    for key, t in (("z", z.detach().numpy()), ("g_x", x.grad.numpy())):
+        r, cl = marginals(t)
+        np.testing.assert_allclose(r, g[key + ".rows"], rtol=0, atol=1e-9 * max(np.abs(g[key + ".rows"]).max(), 1))
+        np.testing.assert_allclose(cl, g[key + ".cols"], rtol=0, atol=1e-9 * max(np.abs(g[key + ".cols"]).max(), 1))
+    for k, p in enc.named_parameters():
+        if "grad." + k + ".rows" in g:
+            r, cl = marginals(p.grad.numpy().reshape(p.shape[0], -1))
+            np.testing.assert_allclose(r, g["grad." + k + ".rows"], rtol=0, atol=1e-5 * max(np.abs(g["grad." + k + ".rows"]).max(), 1e-9))
+            np.testing.assert_allclose(cl, g["grad." + k + ".cols"], rtol=0, atol=1e-5 * max(np.abs(g["grad." + k + ".cols"]).max(), 1e-9))
+    for k in ("norms.0.running_mean", "norms.0.running_var", "norms.1.running_mean", "norms.1.running_var"):
+        np.testing.assert_allclose(enc.state_dict()[k].numpy(), g["after." + k], rtol=1e-6, atol=1e-7)
