@@ -2,11 +2,16 @@
 from /root/reference (only available in the build container, never on the GPU box):
 
 * vq_*.npz  -- /root/reference/STEM-GNN/model/vq.py VectorQuantize (imports torch + einops only)
+* vq_c2_*.npz, vq_shipped_full.npz -- the same module at BASELINE configs[1]'s codebook shape (512 x 256) and in
+               the shipped configuration at its real shape (4 x 128 x 768 + projections); COMPACT fixtures:
+               inputs / initial state are regenerated from seeds by tests/golden/cases.py (checked here), outputs
+               are stored as indices, loss and row / column sums
+* enc_c2.npz -- Encoder at configs[1]'s widths (128 -> 256 -> 256), seeded parameters, compact outputs
 * enc_*.npz, dec_*.npz -- /root/reference/STEM-GNN/model/encoder.py Encoder / InnerProductDecoder,
                executed on oracle/pyg_shim
                (torch_geometric / torch_scatter are not installable here; see oracle/__init__.py)
 
-Run:  python tests/golden/gen_golden.py      (CPU, fp32, seeded; a few seconds)
+Run:  python tests/golden/gen_golden.py [kmeans | dec | vq_c2]     (CPU, fp32, seeded; a few seconds)
 """
 import os
 import sys
