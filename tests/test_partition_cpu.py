@@ -123,6 +123,14 @@ def _bn_worker(rank, world, port, n, f, ret):
         xr = x.clone().requires_grad_(True)
         torch.nn.functional.batch_norm(xr, None, None, training=True, eps=1e-5).backward(gy)
         assert torch.allclose(gx_l, xr.grad[lo:hi], rtol=1e-9, atol=1e-11)
+        # VectorQuantize follows the reference's rule for its statistics all-reduce (model/vq.py:771-772): on by
+        # default exactly when a process group with more than one rank exists; several codebooks with a
+        # distributed k-means init are refused like the reference's assert (vq.py:285)
+        import stemgnn_b200 as S
+        assert S.VectorQuantize(dim=8, codebook_size=4)._codebook.use_ddp is True
+        assert S.VectorQuantize(dim=8, codebook_size=4, sync_codebook=False)._codebook.use_ddp is False
+        with pytest.raises(NotImplementedError):
+            S.VectorQuantize(dim=8, codebook_size=4, heads=2, separate_codebook_per_head=True, kmeans_init=True)
         ret[rank] = 1
     finally:
         dist.destroy_process_group()
