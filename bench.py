@@ -228,11 +228,37 @@ def roofline_of(kern, name, pk, x_fits_l2=None, codes=None):
 
 
 def cpu_baseline_step_fn(w, threads):
-    """The oracle's restatement of the same step (CPU, fp32, all host threads)."""
-    from oracle.encoder_ref import EncoderRef
-    from oracle.vq_ref import vq_forward_ref
+    """The same step on the host cores (fp32, all host threads).  Returns (step, kind, what).
+
+    kind "reference": the reference's OWN modules -- model/vq.py VectorQuantize and model/encoder.py Encoder,
+    unmodified, imported from /root/reference or from the archive oracle/make_ref.py packed into the git-ignored
+    oracle/_ref/ (the GPU box has no /root/reference).  encoder.py runs on oracle/pyg_shim when torch_geometric is
+    not importable (it is not installable here).  kind "port": oracle/'s restatement, when neither is present."""
     torch.set_num_threads(threads)
     torch.manual_seed(0)
+    try:
+        from oracle import ref_loader
+        ref = ref_loader.load(("vq", "encoder"))
+    except (FileNotFoundError, ImportError):
+        ref = None
+    if ref is not None:
+        enc = ref.encoder.Encoder(w["f"], w["hid"], nn.ReLU, w["layers"], backbone="sage", normalize="batch",
+                                  dropout=0.15).train()
+        vq = ref.vq.VectorQuantize(dim=w["hid"], codebook_size=w["codes"], decay=0.8, commitment_weight=1.0).train()
+        opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
+
+        def step(x, ei):
+            opt.zero_grad(set_to_none=True)
+            z = enc(x, ei)
+            q, ind, vq_loss, _ = vq(z)
+            loss = q.square().mean() + vq_loss.sum()
+            loss.backward()
+            opt.step()
+            return float(loss.detach())
+        return step, "reference", (f"the reference's own model/vq.py + model/encoder.py ({ref.kind}), "
+                                   f"message passing underneath from {ref.pyg}")
+    from oracle.encoder_ref import EncoderRef
+    from oracle.vq_ref import vq_forward_ref
     enc = EncoderRef(w["f"], w["hid"], nn.ReLU, w["layers"], backbone="sage", normalize="batch",
                      dropout=0.15).train()
     opt = torch.optim.AdamW(enc.parameters(), lr=1e-4)
@@ -250,7 +276,7 @@ def cpu_baseline_step_fn(w, threads):
         loss.backward()
         opt.step()
         return float(loss.detach())
-    return step
+    return step, "port", "oracle/ restatement of the reference step (oracle/_ref absent)"
 
 
 def cpu_sample(w, frac):
@@ -268,7 +294,7 @@ def run_reference(args, w):
         return
     threads = os.cpu_count() or 1
     ws, sample = cpu_sample(w, args.cpu_frac)
-    step = cpu_baseline_step_fn(ws, threads)
+    step, kind, what = cpu_baseline_step_fn(ws, threads)
     x, ei = synth_graph(ws, 1)
     for _ in range(args.warmup):
         step(x, ei)
@@ -283,9 +309,8 @@ def run_reference(args, w):
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
                 data="synthetic", vq_nodes_per_s=nodes,
                 config=dict(workload=w["desc"], layers=w["layers"], nodes=w["n"], edges=w["e"], sample=sample),
-                cpu_baseline=dict(value=val, unit="edges/s", cores=threads, kind="port",
-                                  sample=sample + "; oracle/ restatement of the reference step "
-                                  "(PyG/torch_scatter are not installable here)"),
+                cpu_baseline=dict(value=val, unit="edges/s", cores=threads, kind=kind,
+                                  sample=sample + "; " + what),
                 e2e=dict(value=val, unit="edges/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
     print(json.dumps(line), flush=True)
@@ -486,7 +511,7 @@ def run_ours(args, w):
     if world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         ws, sample = cpu_sample(w, args.cpu_frac)
-        cstep = cpu_baseline_step_fn(ws, threads)
+        cstep, ckind, cwhat = cpu_baseline_step_fn(ws, threads)
         xc, eic = synth_graph(ws, 1)
         cstep(xc, eic)
         t0, n = time.perf_counter(), 0
@@ -494,8 +519,8 @@ def run_ours(args, w):
             cstep(xc, eic); n += 1
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = dict(value=ws["layers"] * ws["e"] * n / dt, unit="edges/s",
-                                    cores=threads, kind="port",
-                                    sample=f"{n} steps of {sample}; oracle/ restatement, torch CPU fp32")
+                                    cores=threads, kind=ckind,
+                                    sample=f"{n} steps of {sample}; {cwhat}; torch CPU fp32")
     print(json.dumps(line), flush=True)
     finish()
 

@@ -146,8 +146,27 @@ def stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+# STEMGNN_WS_POISON = ff | 00 | rand: fill every workspace before the call (debugging aid for
+# tests/test_gpu_vq_stability.py and scripts/vq_stability.py: a kernel that reads workspace bytes it
+# did not write shows up as a run-to-run difference).  Unset: plain torch.empty.
+_POISON = os.environ.get("STEMGNN_WS_POISON", "")
+
+
+def set_workspace_poison(mode):
+    """mode: "", "ff", "00" or "rand" (see STEMGNN_WS_POISON)."""
+    global _POISON
+    if mode not in ("", "ff", "00", "rand"):
+        raise ValueError("poison mode must be '', 'ff', '00' or 'rand'")
+    _POISON = mode
+
+
 def workspace(nbytes, device):
-    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+    n = max(int(nbytes), 1)
+    if not _POISON:
+        return torch.empty(n, dtype=torch.uint8, device=device)
+    if _POISON == "rand":
+        return torch.randint(0, 256, (n,), dtype=torch.uint8, device=device)
+    return torch.full((n,), 255 if _POISON == "ff" else 0, dtype=torch.uint8, device=device)
 
 
 # ------------------------------------------------------------------ per-call device timing
