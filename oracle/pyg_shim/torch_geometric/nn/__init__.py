@@ -16,14 +16,14 @@ from .dense.linear import Linear
 
 def global_mean_pool(x, batch, size=None):
     size = int(batch.max()) + 1 if size is None else size
-    out = torch.zeros(size, x.size(1), dtype=x.dtype).index_add_(0, batch, x)
-    cnt = torch.zeros(size, dtype=x.dtype).index_add_(0, batch, torch.ones_like(batch, dtype=x.dtype))
+    out = torch.zeros(size, x.size(1), dtype=x.dtype, device=x.device).index_add_(0, batch, x)
+    cnt = torch.zeros(size, dtype=x.dtype, device=x.device).index_add_(0, batch, torch.ones_like(batch, dtype=x.dtype))
     return out / cnt.clamp(min=1).view(-1, 1)
 
 
 def global_add_pool(x, batch, size=None):
     size = int(batch.max()) + 1 if size is None else size
-    return torch.zeros(size, x.size(1), dtype=x.dtype).index_add_(0, batch, x)
+    return torch.zeros(size, x.size(1), dtype=x.dtype, device=x.device).index_add_(0, batch, x)
 
 
 def global_max_pool(x, batch, size=None):
