@@ -92,6 +92,9 @@ def synth_graph(w, seed, device="cpu"):
 
 # --------------------------------------------------------------------------------- clocks
 class ClockSampler:
+    """nvidia-smi polled every 20 ms beside the run; summaries are taken over wall-clock windows (the timed
+    region is tens of milliseconds at the driver's --steps 20, so the sampler is started before the
+    sustained warm-up that precedes it and the timed window is reported next to the warm-up's)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -102,7 +105,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -110,20 +113,18 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        for ln in self.lines:
+    def summary(self, t0=None, t1=None):
+        sm, pw, mx, reasons = [], [], None, set()
+        for ts, ln in self.lines:
+            if (t0 is not None and ts < t0) or (t1 is not None and ts > t1 + 0.03):
+                continue
             c = [t.strip() for t in ln.split(",")]
             if len(c) < 9:
                 continue
             try:
-                sm.append(float(c[1])); mx = float(c[2])
+                sm.append(float(c[1])); mx = float(c[2]); pw.append(float(c[3]))
             except ValueError:
                 continue
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
@@ -131,9 +132,18 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(name)
         sm.sort()
-        # samples under load: the upper half (idle gaps between steps pull the clock down)
-        med = sm[len(sm) // 2] if sm else None
-        return {"sm_mhz": med, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw) if pw else None}
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        out = self.summary(t0, t1)
+        if out["samples"] == 0:            # a window shorter than the polling period: nearest samples either side
+            out = self.summary(None if t0 is None else t0 - 0.05, None if t1 is None else t1 + 0.05)
+        return out
 
 
 # --------------------------------------------------------------------------------- our arm

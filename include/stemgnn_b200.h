@@ -34,7 +34,7 @@ const char* stemgnn_last_error(void);
 /* Layout version of the argument structs below; a binding checks it at load time.
  * 2: out_ld / row_x_ld in stemgnn_aggregate_args; 3: stemgnn_bn_act_backward_apply and the loop-side
  * entry points (augmentations, sampler, l2norm, negative sampling); 4: hub_ws / hub_ws_bytes appended to
- * stemgnn_aggregate_args. */
+ * stemgnn_aggregate_args; 5: accumulate appended to stemgnn_aggregate_args. */
 int stemgnn_abi_version(void);
 /* number of CUDA kernels this library has launched in this process (all entry points) */
 uint64_t stemgnn_launch_count(void);
@@ -98,6 +98,12 @@ typedef struct {
     int64_t row_x_ld;        /* row stride of row_x in floats; 0 = feat */
     void* hub_ws;            /* device scratch of stemgnn_aggregate_hub_workspace(num_edges) bytes, or NULL.  ABI 4 */
     size_t hub_ws_bytes;
+    int accumulate;          /* ABI 5.  1: every row sum STARTS from the value already in out[r] (the additions of this
+                              * call follow it, in edge order) instead of 0 -- one aggregation cut into several calls
+                              * over disjoint edge subsets (source-owner blocks of a partitioned graph, aggregated
+                              * as their halo blocks land).  Pass row_cnt / the backward relu mask (act with
+                              * backward=1) only in the LAST call of such a chain: both apply to the finished sum. */
+    int reserved;
 } stemgnn_aggregate_args;
 
 int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t stream);

@@ -34,5 +34,5 @@ int sm_count() {
 }  // namespace stemgnn
 
 extern "C" const char* stemgnn_last_error(void) { return stemgnn::g_err; }
-extern "C" int stemgnn_abi_version(void) { return 4; }
+extern "C" int stemgnn_abi_version(void) { return 5; }
 extern "C" uint64_t stemgnn_launch_count(void) { return stemgnn::launches(); }

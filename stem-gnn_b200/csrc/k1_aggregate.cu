@@ -27,6 +27,10 @@ template <> struct Vec<4> {
         float4 t = __ldg(reinterpret_cast<const float4*>(p));
         v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
     }
+    __device__ __forceinline__ void load_plain(const float* p) {      // coherent load (data this stream wrote before)
+        float4 t = *reinterpret_cast<const float4*>(p);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
     __device__ __forceinline__ void store(float* p) const {
         *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
     }
@@ -34,6 +38,7 @@ template <> struct Vec<4> {
 template <> struct Vec<1> {
     float v[1];
     __device__ __forceinline__ void load(const float* p) { v[0] = __ldg(p); }
+    __device__ __forceinline__ void load_plain(const float* p) { v[0] = *p; }
     __device__ __forceinline__ void store(float* p) const { *p = v[0]; }
 };
 
@@ -47,6 +52,8 @@ struct AggParams {
     int64_t out_ld, row_x_ld;   // row strides (floats) of out / row_x: column slices of wider matrices
     int* hub;                   // [0] big hubs, [1] small hubs, [2] next work item, [3] CTAs done, [4..] row ids; or NULL
     int hub_cap;                // slots of the row list: big hubs from the front, small ones from the back
+    int accumulate;             // row sums start from out[r] instead of 0 (ABI 5)
+    int hints;                  // L2 cache-policy hints on the streaming accesses (A/B switch)
 };
 
 // Rows with at least this many edges ("hubs": ogbn-arxiv's largest in-degree is 13,155, ogbn-products'
@@ -168,6 +175,7 @@ aggregate_kernel(const AggParams a) {
         for (int c = 0; c < CH; ++c) {
 #pragma unroll
             for (int k = 0; k < VEC; ++k) { acc[c].v[k] = 0.f; rx[c].v[k] = 0.f; }
+            if (a.accumulate && fok[c]) acc[c].load_plain(a.out + row * a.out_ld + foff[c]);
             if (BWD && MODE != MODE_W && RELU && fok[c]) rx[c].load(a.row_x + row * a.row_x_ld + foff[c]);
         }
 
@@ -191,6 +199,147 @@ aggregate_kernel(const AggParams a) {
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Plain mode (message = the gathered row, relu at most; no per-edge data), 64 < F <= 1024: the
+// row-walking kernel with STAGED NEIGHBOUR INDICES.
+//
+// aggregate_kernel above gives every row to one warp that then leaves: rowptr -> col -> gathered
+// rows are three dependent memory round trips per row, and with the 7 edges per row of the
+// arxiv-shaped graph those round trips, not bytes, set the launch time (ncu round 1: issue active
+// 42 %, long scoreboard, 91 instructions per edge-warp).  Here a warp owns STREAM_ROWS consecutive
+// rows, i.e. one contiguous run of the CSR: its rowptr values come in one coalesced load (one per
+// lane) and the col entries of the whole run travel through a two-register window per lane
+// (2 x 32 indices, 128-byte aligned coalesced loads, the next 32 fetched while the current ones
+// are used) and reach the lanes by shuffle.  Per row only the gather round trip is left.
+// The streaming accesses (rowptr, col, out) carry an L2 evict-first policy and skip L1, so the
+// 126 MB L2 keeps the gathered matrix instead of the output stream (round 1 measured 279 MB of DRAM
+// traffic for 179 MB of compulsory bytes at F = 128 although X fits L2).
+// Additions stay in edge order, one by one, separately rounded: same bits as aggregate_kernel.
+constexpr int STREAM_ROWS = 8;
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ int ld_stream_i32(const int32_t* p, uint64_t pol, bool hints) {
+    int v;
+    if (hints) asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.b32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol));
+    else v = __ldg(p);
+    return v;
+}
+__device__ __forceinline__ void st_stream_f4(float* p, const float (&v)[4], uint64_t pol, bool hints) {
+    if (hints)
+        asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(p), "f"(v[0]), "f"(v[1]),
+                     "f"(v[2]), "f"(v[3]), "l"(pol)
+                     : "memory");
+    else *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+template <int CH, bool RELU_MSG, bool MASK_END, int OCC>
+__global__ void __launch_bounds__(256, OCC)
+aggregate_stream_kernel(const AggParams a) {
+    constexpr int U = CH <= 1 ? 8 : (CH <= 2 ? 4 : (CH <= 4 ? 2 : 1));
+    const int lane = threadIdx.x & 31;
+    const int64_t r0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * STREAM_ROWS;
+    if (r0 >= a.n_rows) return;
+    const int nr = (int)(a.n_rows - r0 < STREAM_ROWS ? a.n_rows - r0 : STREAM_ROWS);
+    const int F = a.F;
+    const bool hints = a.hints != 0;
+    const uint64_t pol = policy_evict_first();
+    const int E = (int)a.num_edges;
+
+    int rp = 0;
+    if (lane <= nr) rp = ld_stream_i32(a.rowptr + r0 + lane, pol, hints);
+    int foff[CH];
+    bool fok[CH];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+        foff[c] = (c * 32 + lane) * 4;
+        fok[c] = foff[c] < F;
+    }
+    // index window: w0 holds col[wb + lane], w1 holds col[wb + 32 + lane]
+    int wb = __shfl_sync(0xffffffffu, rp, 0) & ~31;
+    int w0 = wb + lane < E ? ld_stream_i32(a.col + wb + lane, pol, hints) : 0;
+    int w1 = wb + 32 + lane < E ? ld_stream_i32(a.col + wb + 32 + lane, pol, hints) : 0;
+
+    for (int r = 0; r < nr; ++r) {
+        const int beg = __shfl_sync(0xffffffffu, rp, r), end = __shfl_sync(0xffffffffu, rp, r + 1);
+        const int64_t row = r0 + r;
+        if (a.hub != nullptr && end - beg >= HUB_ROW_EDGES) {
+            if (lane == 0) {
+                if (end - beg >= HUB_BIG_EDGES) a.hub[4 + atomicAdd(a.hub, 1)] = (int)row;
+                else a.hub[4 + a.hub_cap - 1 - atomicAdd(a.hub + 1, 1)] = (int)row;
+            }
+            continue;
+        }
+        Vec<4> acc[CH];
+        Vec<4> rx[CH];
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { acc[c].v[k] = 0.f; rx[c].v[k] = 0.f; }
+            if (a.accumulate && fok[c]) acc[c].load_plain(a.out + row * a.out_ld + foff[c]);
+            if (MASK_END && fok[c]) rx[c].load(a.row_x + row * a.row_x_ld + foff[c]);
+        }
+        for (int p = beg; p < end; p += U) {
+            if (p >= wb + 32) {                       // [p, p + U) must lie inside the window; move it early
+                if (p >= wb + 64) {
+                    wb = p & ~31;
+                    w0 = wb + lane < E ? ld_stream_i32(a.col + wb + lane, pol, hints) : 0;
+                } else {
+                    w0 = w1;
+                    wb += 32;
+                }
+                w1 = wb + 32 + lane < E ? ld_stream_i32(a.col + wb + 32 + lane, pol, hints) : 0;
+            }
+            int cidx[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = p + u - wb;             // warp-uniform
+                const int v = __shfl_sync(0xffffffffu, i < 32 ? w0 : w1, i & 31);
+                cidx[u] = p + u < end ? v : -1;
+            }
+            Vec<4> g[U][CH];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const float* gp = a.gathered + (int64_t)cidx[u] * F;
+#pragma unroll
+                for (int c = 0; c < CH; ++c)
+                    if (cidx[u] >= 0 && fok[c]) g[u][c].load(gp + foff[c]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (cidx[u] < 0) continue;
+#pragma unroll
+                for (int c = 0; c < CH; ++c) {
+                    if (!fok[c]) continue;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float m = g[u][c].v[k];
+                        if (RELU_MSG) m = m > 0.f ? m : 0.f;
+                        acc[c].v[k] = __fadd_rn(acc[c].v[k], m);
+                    }
+                }
+            }
+        }
+        float rc = 1.f;
+        if (a.row_cnt) rc = __ldg(a.row_cnt + row);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            if (!fok[c]) continue;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float v = acc[c].v[k];
+                if (a.row_cnt) v = __fdiv_rn(v, rc);
+                if (MASK_END) v = rx[c].v[k] > 0.f ? v : 0.f;
+                acc[c].v[k] = v;
+            }
+            st_stream_f4(a.out + row * a.out_ld + foff[c], acc[c].v, pol, hints);
+        }
+    }
+}
 
 // Hub rows.  A work item is (hub row, slice of feature columns): columns are independent, so slicing
 // keeps every column's additions in edge order while a row spreads over several CTAs.  In a CTA 256
@@ -259,7 +408,7 @@ aggregate_hub_kernel(const AggParams a) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) rx.v[k] = 0.f;
         if (loader && BWD && MODE == MODE_XE && RELU && fok) rx.load(a.row_x + row * a.row_x_ld + foff);
-        float acc = 0.f;
+        float acc = (a.accumulate && col_ok) ? a.out[row * a.out_ld + f0 + c] : 0.f;
         // the slot indices of a tile are fetched while the rows of the tile before it are in flight, so a
         // tile costs one memory round trip instead of two dependent ones
         int cidx[U];
@@ -469,7 +618,7 @@ aggregate_hub_ring_kernel(const AggParams a) {
         issue(1);
         load_idx(2);
 
-        float acc = 0.f;
+        float acc = (a.accumulate && col_ok) ? a.out[row * a.out_ld + f0 + c] : 0.f;
         for (int t = 0; t < n_tiles; ++t) {
             cp_async_wait<NST - 2>();   // this thread's copies of tile t have landed
             __syncthreads();            // ... everyone's have, and tile t - 1 has been summed
@@ -566,9 +715,45 @@ static void launch(const AggParams& p, cudaStream_t s) {
     if (VEC == 4 && p.hub != nullptr) launch_hub<MODE, BWD, RELU>(p, s);
 }
 
+template <int CH, bool BWD, bool RELU>
+static void launch_stream(const AggParams& p, cudaStream_t s) {
+    constexpr int ROWS_PER_BLOCK = 8 * STREAM_ROWS;
+    unsigned grid = (unsigned)((p.n_rows + ROWS_PER_BLOCK - 1) / ROWS_PER_BLOCK);
+    // resident 256-thread blocks the register allocation must allow; one 16 B chunk per lane (F <= 128) is
+    // measured at 4 (64 registers, a few spilled words) against 3 -- STEMGNN_AGG_STREAM_OCC picks for the A/B
+    static const int occ1 = [] { const char* e = getenv("STEMGNN_AGG_STREAM_OCC"); return e ? atoi(e) : 3; }();
+    bool done = false;
+    if constexpr (CH == 1) {
+        if (occ1 == 4) {
+            SG_LAUNCH(aggregate_stream_kernel<CH, !BWD && RELU, BWD && RELU, 4><<<grid, 256, 0, s>>>(p));
+            done = true;
+        }
+    }
+    if (!done) SG_LAUNCH(aggregate_stream_kernel<CH, !BWD && RELU, BWD && RELU, (CH <= 6 ? 3 : 2)><<<grid, 256, 0, s>>>(p));
+    if (p.hub != nullptr) launch_hub<MODE_PLAIN, BWD, RELU>(p, s);
+}
+
+// STEMGNN_AGG_STREAM=0 keeps every shape on aggregate_kernel (A/B switch for scripts/agg_bench.py)
+static bool stream_enabled() {
+    static const bool on = [] { const char* e = getenv("STEMGNN_AGG_STREAM"); return e ? atoi(e) != 0 : true; }();
+    return on;
+}
+
 template <int MODE, bool BWD, bool RELU>
 static void dispatch_shape(const AggParams& p, bool vec4, cudaStream_t s) {
     if (!vec4) { launch<1, 32, 8, MODE, BWD, RELU>(p, s); return; }
+    if constexpr (MODE == MODE_PLAIN) {
+        if (stream_enabled() && p.F > 64 && p.F <= 1024 && !(BWD && p.gather_cnt)) {
+            const int ch = (p.F + 127) / 128;
+            if (ch <= 1) launch_stream<1, BWD, RELU>(p, s);
+            else if (ch <= 2) launch_stream<2, BWD, RELU>(p, s);
+            else if (ch <= 3) launch_stream<3, BWD, RELU>(p, s);
+            else if (ch <= 4) launch_stream<4, BWD, RELU>(p, s);
+            else if (ch <= 6) launch_stream<6, BWD, RELU>(p, s);
+            else launch_stream<8, BWD, RELU>(p, s);
+            return;
+        }
+    }
     const int f4 = p.F / 4;
     if (f4 <= 8) launch<4, 8, 1, MODE, BWD, RELU>(p, s);
     else if (f4 <= 16) launch<4, 16, 1, MODE, BWD, RELU>(p, s);
@@ -655,6 +840,9 @@ extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream
         p.hub = static_cast<int*>(a->hub_ws);
         p.hub_cap = (int)(a->num_edges / HUB_ROW_EDGES + 1);
     }
+    p.accumulate = a->accumulate != 0;
+    static const bool hints_on = [] { const char* e = getenv("STEMGNN_AGG_HINTS"); return e ? atoi(e) != 0 : true; }();
+    p.hints = hints_on;
     const int mode = has_w ? MODE_W : (has_xe ? MODE_XE : MODE_PLAIN);
     // a backward pass with neither a per-edge division nor a relu mask is the plain sum over the
     // transposed structure: the forward kernel

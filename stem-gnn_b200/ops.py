@@ -26,7 +26,7 @@ def _f32c(t, name):
 
 def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_cnt=None,
                     edge_feat=None, type_table=None, edge_type=None, edge_weight=None, row_x=None,
-                    act=ACT_NONE, backward=False, out_cols=None, gathered_rows=None):
+                    act=ACT_NONE, backward=False, out_cols=None, gathered_rows=None, accumulate=False):
     """One stemgnn_aggregate call.  `out_cols=(lo, hi)` writes columns [lo, hi) of the wider `out`
     (and reads the same columns of `row_x`): the feature-sliced halo pipeline."""
     per_edge = edge_feat is not None or edge_type is not None or edge_weight is not None
@@ -37,7 +37,7 @@ def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_c
         gathered=_lib.ptr(gathered), row_cnt=_lib.ptr(row_cnt), gather_cnt=_lib.ptr(gather_cnt),
         edge_feat=_lib.ptr(edge_feat), type_table=_lib.ptr(type_table),
         edge_type=_lib.ptr(edge_type), edge_weight=_lib.ptr(edge_weight), row_x=_lib.ptr(row_x),
-        act=act, backward=int(backward), out=_lib.ptr(out))
+        act=act, backward=int(backward), out=_lib.ptr(out), accumulate=int(accumulate))
     hub = getattr(csr, "hub", None)
     if hub is not None and os.environ.get("STEMGNN_AGG_NO_HUB") != "1":      # A/B switch for scripts/agg_bench.py
         a.hub_ws, a.hub_ws_bytes = hub.data_ptr(), hub.numel()

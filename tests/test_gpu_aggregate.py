@@ -244,3 +244,39 @@ def test_row_scale_then_sum_equals_per_edge_division(n, e, f):
     assert torch.equal(scaled, go / cnt[:, None])
     ops._aggregate_call(bwd, n, scaled, b, backward=True)
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("f", [36, 100, 256])
+@pytest.mark.parametrize("bwd_mask", [False, True])
+def test_accumulate_chain_is_the_block_ordered_sum(f, bwd_mask):
+    """ABI 5 `accumulate`: one aggregation cut into calls over disjoint edge subsets (here: by source block, as the
+    partitioned path does while halo blocks land), each starting from the sums the previous call left, the mean
+    division / backward relu mask only in the last call.  The result is the sequential sum over the edges taken
+    block by block -- bit for bit, hub rows (>= 256 edges inside one block) included."""
+    from stemgnn_b200 import ops
+    from stemgnn_b200.graph import CSR
+    n, e, blocks = 900, 30000, 3
+    g = torch.Generator().manual_seed(41)
+    ei = _hub_graph(n, e, 41, {17: 1500, 300: 290})
+    x = torch.randn(n, f, generator=g)
+    rowx = torch.randn(n, f, generator=g)
+    per = n // blocks
+    order = torch.cat([((ei[0] // per) == b).nonzero().view(-1) for b in range(blocks)])
+    ei_blockwise = ei[:, order]
+    xj = x.index_select(0, ei_blockwise[0])
+    msg = xj if bwd_mask else torch.relu(xj)
+    ref = P._scatter_sum(msg, ei_blockwise[1], n)
+    cnt = torch.bincount(ei[1], minlength=n).clamp(min=1).to(torch.float32)
+    ref = torch.where(rowx > 0, ref, torch.zeros(())) if bwd_mask else ref / cnt.view(-1, 1)
+
+    xd, out = x.to(DEV), torch.full((n, f), 7.0, device=DEV)
+    for b in range(blocks):
+        sub = ei[:, (ei[0] // per) == b].to(DEV)
+        csr = CSR(sub, n, 1)
+        last = b == blocks - 1
+        ops._aggregate_call(csr, n, xd, out, accumulate=b > 0,
+                            row_cnt=cnt.to(DEV) if (last and not bwd_mask) else None,
+                            row_x=rowx.to(DEV) if (last and bwd_mask) else None,
+                            act=(ops.ACT_RELU if (not bwd_mask or last) else ops.ACT_NONE),
+                            backward=bool(bwd_mask and last))
+    np.testing.assert_array_equal(out.cpu().numpy(), ref.numpy())
