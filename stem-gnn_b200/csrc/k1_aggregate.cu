@@ -252,6 +252,8 @@ aggregate_stream_kernel(const AggParams a) {
 
     int rp = 0;
     if (lane <= nr) rp = ld_stream_i32(a.rowptr + r0 + lane, pol, hints);
+    float cnt_l = 1.f;                          // this lane's row's clamped count: one coalesced load per warp
+    if (a.row_cnt && lane < nr) cnt_l = __ldg(a.row_cnt + r0 + lane);
     int foff[CH];
     bool fok[CH];
 #pragma unroll
@@ -324,8 +326,7 @@ aggregate_stream_kernel(const AggParams a) {
                 }
             }
         }
-        float rc = 1.f;
-        if (a.row_cnt) rc = __ldg(a.row_cnt + row);
+        const float rc = __shfl_sync(0xffffffffu, cnt_l, r);
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
             if (!fok[c]) continue;
@@ -733,17 +734,26 @@ static void launch_stream(const AggParams& p, cudaStream_t s) {
     if (p.hub != nullptr) launch_hub<MODE_PLAIN, BWD, RELU>(p, s);
 }
 
-// STEMGNN_AGG_STREAM=0 keeps every shape on aggregate_kernel (A/B switch for scripts/agg_bench.py)
-static bool stream_enabled() {
-    static const bool on = [] { const char* e = getenv("STEMGNN_AGG_STREAM"); return e ? atoi(e) != 0 : true; }();
-    return on;
+// Widths above this take aggregate_stream_kernel.  Measured on B200 (profiles/r02_agg_stream_ab.log): F = 256
+// 210 -> 179 us forward / 255 -> 224 backward on the arxiv-shaped graph, F = 512 839 -> 750; one 16 B chunk per
+// lane (F <= 128) gains nothing (124 us either way) and loses 19 % on 25-edge rows at F = 100 (2,122 -> 2,528 us,
+// products-sized half graph), so those widths stay on aggregate_kernel.  STEMGNN_AGG_STREAM=0 keeps every shape
+// there, =1 moves the threshold down to 64, =<n> to n (A/B switch for scripts/agg_bench.py).
+static int stream_min_f() {
+    static const int f = [] {
+        const char* e = getenv("STEMGNN_AGG_STREAM");
+        if (!e) return 128;
+        const int v = atoi(e);
+        return v == 0 ? (1 << 30) : (v == 1 ? 64 : v);
+    }();
+    return f;
 }
 
 template <int MODE, bool BWD, bool RELU>
 static void dispatch_shape(const AggParams& p, bool vec4, cudaStream_t s) {
     if (!vec4) { launch<1, 32, 8, MODE, BWD, RELU>(p, s); return; }
     if constexpr (MODE == MODE_PLAIN) {
-        if (stream_enabled() && p.F > 64 && p.F <= 1024 && !(BWD && p.gather_cnt)) {
+        if (p.F > stream_min_f() && p.F <= 1024 && !(BWD && p.gather_cnt)) {
             const int ch = (p.F + 127) / 128;
             if (ch <= 1) launch_stream<1, BWD, RELU>(p, s);
             else if (ch <= 2) launch_stream<2, BWD, RELU>(p, s);

