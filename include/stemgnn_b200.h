@@ -243,6 +243,20 @@ int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* args_host, void* works
 int stemgnn_bn_workspace(int64_t rows, int64_t feat, size_t* bytes_host);
 int stemgnn_bn_stats(int64_t rows, int64_t feat, const float* x, int64_t ldx, float* mean, float* var,
                      void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+/* stemgnn_bn_stats without a caller workspace and without any allocation.  No counterpart in the
+ * reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, arithmetic
+ * and results (bit for bit) as stemgnn_bn_stats; the per-block partial sums live in a 4 MiB
+ * `static __device__` array inside the library (held by every GPU that loads it until the process
+ * exits), whose device address is looked up once per device with cudaGetSymbolAddress.  Limit: the
+ * partials, 2 * feat floats for each of at most 3 * SM-count row blocks, must fit the 4 MiB -- any row
+ * count with feat <= 1,180 on a 148-SM B200 (wider only while rows <= 64 * 4 MiB / (8 * feat));
+ * beyond it the call returns STEMGNN_EINVAL and says so.  The call makes no cudaMalloc / cudaFree /
+ * allocating library call.  Every call on a device shares the one array: it carries the last call's
+ * partials (nothing in it needs to start at zero -- each call overwrites every word it reads), and two
+ * calls that may overlap on the GPU (different streams without an ordering between them) race on it. */
+int stemgnn_bn_stats_static(int64_t rows, int64_t feat, const float* x, int64_t ldx, float* mean, float* var,
+                            stemgnn_stream_t stream);
 int stemgnn_bn_act_forward(int64_t rows, int64_t feat, const float* x, int64_t ldx, const float* mean,
                            const float* invstd, const float* gamma, const float* beta, int relu, float p,
                            const uint64_t* seed, float* out, int64_t ldo, stemgnn_stream_t stream);

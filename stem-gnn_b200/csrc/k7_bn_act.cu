@@ -305,3 +305,58 @@ extern "C" int stemgnn_bn_act_backward_apply(int64_t rows, int64_t feat, const f
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }
+
+// ---- stemgnn_bn_stats_static: the same statistics with the block partials in library-owned memory ----
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses without cudaMalloc).
+// The scratch is a file-scope __device__ array: every GPU that loads the library holds its 4 MiB until
+// the process exits.  In host code `bn_static_scratch` is only a host-side stand-in for the symbol, not
+// a device address, so the address each device gave it is looked up once per device (with that device
+// current) through cudaGetSymbolAddress and that pointer is what the kernels get.
+#define STEMGNN_BN_STATIC_SCRATCH_BYTES (4u << 20)
+static __device__ __align__(256) float bn_static_scratch[STEMGNN_BN_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* bn_static_ptr[kMaxDevices];   // device address of bn_static_scratch, per device; written once
+int bn_static_scratch_address(float** out) {
+    int dev = -1;
+    SG_CHECK_CUDA(cudaGetDevice(&dev));
+    SG_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "device ordinal beyond 63");
+    float* p = __atomic_load_n(&bn_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        // set-up, once per device, the device being current; two threads racing here get the same address
+        SG_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), bn_static_scratch));
+        SG_CHECK_ARG(p != nullptr, "cudaGetSymbolAddress returned NULL");
+        __atomic_store_n(&bn_static_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return STEMGNN_OK;
+}
+}  // namespace
+
+extern "C" int stemgnn_bn_stats_static(int64_t rows, int64_t feat, const float* x, int64_t ldx, float* mean,
+                                       float* var, stemgnn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (int rc = bn_check(rows, feat, x, ldx)) return rc;
+    SG_CHECK_ARG(rows > 0, "batch statistics of an empty batch");
+    if (feat == 0) return STEMGNN_OK;
+    SG_CHECK_ARG(mean && var, "mean/var NULL");
+    const BnPlan pl = bn_plan(rows, feat);
+    const size_t need = (size_t)pl.blocks * 2 * (size_t)feat * sizeof(float);
+    if (need > STEMGNN_BN_STATIC_SCRATCH_BYTES) {
+        set_error("stemgnn_bn_stats_static: %d row blocks x 2 x %lld columns need %zu bytes of block partials, the "
+                  "built-in scratch holds %u (feat <= %lld at this row count); use stemgnn_bn_stats with a caller "
+                  "workspace", pl.blocks, (long long)feat, need, (unsigned)STEMGNN_BN_STATIC_SCRATCH_BYTES,
+                  (long long)(STEMGNN_BN_STATIC_SCRATCH_BYTES / (8 * (size_t)pl.blocks) / 4 * 4));
+        return STEMGNN_EINVAL;
+    }
+    float* part = nullptr;
+    if (int rc = bn_static_scratch_address(&part)) return rc;
+    // nothing in the scratch has to start at zero: col_reduce writes every partial col_final reads
+    bn::Cols none{nullptr, nullptr, nullptr, nullptr};
+    SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
+                                                                      none, 0, 0.f, 1.f, nullptr, part));
+    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), 256, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
+    SG_CHECK_LAUNCH();
+    return STEMGNN_OK;
+}
