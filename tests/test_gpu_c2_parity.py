@@ -84,14 +84,19 @@ def test_c2_arxiv_whole_step_vs_oracle():
     z_r = ref(xr, ei)
     z_r.retain_grad()
     q_r, ind_r, vl_r, _ = vq_forward_ref(z_r, state, training=True, ema_update=True, decay=0.8, commitment_weight=1.0)
-    loss_r = q_r.square().mean() + vl_r.sum()
+    # The bench's loss mean(q^2) + commitment has d/dz = 2z/(N*D) whatever the codes are (the straight-through term
+    # and the commitment term cancel), and z = BatchNorm(h) with gamma = 1, beta = 0 is its own xhat: BatchNorm's
+    # backward removes exactly that direction, so every gradient in front of it is eps/var of rounding noise -- not a
+    # comparison.  The upstream gradient here is a fixed random functional of q instead (same kernels, conditioned).
+    gq = torch.randn(n, hid, generator=torch.Generator().manual_seed(5))
+    loss_r = (q_r * gq).sum() + vl_r.sum()
     loss_r.backward()
 
     xg = x.to(DEV).requires_grad_(True)
     z = enc(xg, ei.to(DEV))
     z.retain_grad()
     q, ind, vl, _ = vq(z)
-    loss = q.square().mean() + vl.sum()
+    loss = (q * gq.to(DEV)).sum() + vl.sum()
     loss.backward()
 
     _close(z, z_r, what="z")
@@ -101,7 +106,7 @@ def test_c2_arxiv_whole_step_vs_oracle():
     # one rounding at the magnitude of x; the library returns the code row itself -> compared on the scale of x
     assert float((q[same.to(DEV)].cpu() - q_r.detach()[same]).abs().max()) <= 1e-6 * float(z_r.detach().abs().max())
     assert torch.equal(q[same.to(DEV)].cpu(), embed0[ind_r.view(-1)[same]])
-    _close(loss, loss_r, 1e-5 + 1e-5 * n_bad, "loss")
+    _close(vl, vl_r, 1e-5 + 1e-5 * n_bad, "commitment loss")
     _close(z.grad[same.to(DEV)], z_r.grad[same], 1e-5, "g_z (VQ backward)")
     # EMA state: a near-tie row moves one count between two codes, and (1 - decay)/count of its row
     cs, cs_r = vq._codebook.cluster_size.cpu(), state["cluster_size"]
