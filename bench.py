@@ -153,7 +153,8 @@ def build_models(w, device, S):
                     dropout=0.15).to(device).train()
     vq = S.VectorQuantize(dim=w["hid"], codebook_size=w["codes"], decay=0.8,
                           commitment_weight=1.0).to(device).train()
-    opt = torch.optim.AdamW(enc.parameters(), lr=1e-4, capturable=True)   # graph-capturable: same math
+    # graph-capturable, one fused multi-tensor kernel per step instead of ~16 foreach launches: same math
+    opt = torch.optim.AdamW(enc.parameters(), lr=1e-4, capturable=True, fused=True)
     return enc, vq, opt
 
 
@@ -185,8 +186,8 @@ def summarize_trace(trace, steps, pk, n_feat_bytes_l2):
     for name, nbytes, flops, launches, e0, e1 in trace:
         ms = e0.elapsed_time(e1)
         key = "aggregate" if name.startswith("aggregate") else name
-        d = fam.setdefault(key, dict(ms=0.0, calls=0, bytes_min=0, bytes_gather=0, bytes_alg=0, flops=0))
-        d["ms"] += ms; d["calls"] += 1; d["flops"] += flops
+        d = fam.setdefault(key, dict(ms=0.0, calls=0, bytes_min=0, bytes_gather=0, bytes_alg=0, flops=0, launches=0))
+        d["ms"] += ms; d["calls"] += 1; d["flops"] += flops; d["launches"] += launches
         if isinstance(nbytes, tuple):
             d["bytes_min"] += nbytes[0]; d["bytes_gather"] += nbytes[1]; d["bytes_alg"] += nbytes[2]
         else:
@@ -194,10 +195,13 @@ def summarize_trace(trace, steps, pk, n_feat_bytes_l2):
     out = {}
     for k, d in fam.items():
         sec = d["ms"] / 1e3
-        o = dict(ms_per_step=d["ms"] / steps, calls_per_step=d["calls"] / steps)
+        o = dict(ms_per_step=d["ms"] / steps, calls_per_step=d["calls"] / steps,
+                 launches_per_step=d["launches"] / steps)
         if sec > 0:
             o["gbps_alg"] = d["bytes_alg"] / sec / 1e9
             o["alg_bytes_per_call"] = d["bytes_alg"] / d["calls"]
+            o["bytes_min_per_call"] = d["bytes_min"] / d["calls"]
+            o["bytes_gather_per_call"] = d["bytes_gather"] / d["calls"]
             o["gbps_alg_min"] = d["bytes_min"] / sec / 1e9
             o["gbps_alg_gather"] = d["bytes_gather"] / sec / 1e9
             if d["flops"]:
@@ -231,10 +235,35 @@ def roofline_of(kern, name, pk, x_fits_l2=None, codes=None):
                     peak_source=pk["src"] + " bf16 dense / 2 = tf32 rate (sustained)",
                     flops_model="algorithmic 2*M*N*K per call; 3 tf32 MMAs per product are executed")
     a = k["gbps_alg"]
-    return dict(kernel=name, bound="hbm", achieved=a, peak=pk["hbm"], unit="GB/s", frac=a / pk["hbm"],
-                traffic=None, peak_source=pk["src"], alg_bytes_per_launch=k["alg_bytes_per_call"],
-                bytes_model="per launch: compulsory bytes (every row once) while the gathered matrix "
-                            "fits the 126 MB L2, else one source row per edge (SURVEY.md 8d)")
+    r = dict(kernel=name, bound="hbm", achieved=a, peak=pk["hbm"], unit="GB/s", frac=a / pk["hbm"],
+             traffic=None, peak_source=pk["src"], alg_bytes_per_launch=k["alg_bytes_per_call"],
+             achieved_basis="algorithmic bytes per call / live CUDA-event time of the call")
+    if name == "aggregate":
+        # two byte models per call: B_min = every row once (its rule while the gathered matrix fits
+        # the 126 MB L2: configs C1, C2), B_gather = one source row per edge.  Neither is what the DRAM moves once
+        # part of the gathers hit L2, so when an ncu capture of this configuration exists (`traffic`, attached by
+        # the caller) `achieved` / `frac` are restated from the MEASURED DRAM bytes and the models stay beside them.
+        r.update(frac_model_min=k["gbps_alg_min"] / pk["hbm"], frac_model_gather=k["gbps_alg_gather"] / pk["hbm"],
+                 alg_bytes_per_launch=k["bytes_min_per_call"], alg_bytes_gather_per_launch=k["bytes_gather_per_call"],
+                 bytes_model="B_min per call: (gathered rows + produced rows [x2 with the backward relu mask]) * F * 4 "
+                             "+ E * 4 + (N + 1) * 4 + N * 4; B_gather: E * F * 4 in place of the gathered rows")
+    return r
+
+
+def attach_traffic(r, k, t, pk):
+    """`traffic` = dram__bytes_read.sum + dram__bytes_write.sum per call from the ncu --set full capture of this
+    configuration (profiles/traffic.json, written by scripts/ncu_traffic.py from the raw CSV beside it).  For the
+    HBM-bound families the line's achieved / frac become measured DRAM bytes over the live CUDA-event time."""
+    r["traffic"] = t["bytes_per_launch"]
+    r["traffic_source"] = t["source"]
+    if r["bound"] == "hbm" and k["ms_per_step"] > 0:
+        gbps = t["bytes_per_launch"] * k["calls_per_step"] / (k["ms_per_step"] / 1e3) / 1e9
+        r.update(achieved=gbps, frac=gbps / pk["hbm"],
+                 achieved_basis="measured DRAM bytes per call (ncu dram__bytes_read + write, `traffic`) / live "
+                                "CUDA-event time of the call")
+        if r.get("alg_bytes_per_launch"):
+            r["traffic_over_alg"] = t["bytes_per_launch"] / r["alg_bytes_per_launch"]
+    return r
 
 
 def cpu_baseline_step_fn(w, threads):
@@ -484,11 +513,30 @@ def run_ours(args, w):
     sync_all()
     launches = (_lib.launch_count() - l0) / args.steps
     trace, _lib.TRACE = _lib.TRACE, None
+    if args.dump_sequence and rank == 0:
+        # the C-ABI calls of ONE step in launch order with the kernels each launched: scripts/ncu_traffic.py
+        # aligns an ncu launch list of the same step with it
+        per = len(trace) // args.steps
+        json.dump([[r[0], r[3], r[4].elapsed_time(r[5])] for r in trace[-per:]], open(args.dump_sequence, "w"))
 
     t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
+    # ---------------- the north_star multi-GPU mode, in the same process: BASELINE configs[3] (products-shaped,
+    # 3-layer) on a 1-D destination partition over these `world` ranks, strong scaling.  The top-level line stays
+    # the configs[1] step (replicas for N > 1); this record rides along on every line, N = 1 included.
+    part = None
+    if not args.no_partition:
+        del flush
+        torch.cuda.empty_cache()
+        try:
+            part = measure_partition(dict(WORKLOADS["products"]), dev, rank, world, args.partition_steps, 3)
+            if part is not None:
+                part.pop("_extra", None)
+        except Exception as exc:                                      # noqa: BLE001 -- the headline line must still print
+            part = dict(error=f"{type(exc).__name__}: {exc}".splitlines()[0][:300])
+
     def finish():
         if world > 1:
             torch.cuda.synchronize()
@@ -517,8 +565,7 @@ def run_ours(args, w):
             continue
         r = roofline_of(kern, name, pk, codes=w["codes"])
         if name in traffic:
-            r["traffic"] = traffic[name]["bytes_per_launch"]
-            r["traffic_source"] = traffic[name]["source"]
+            attach_traffic(r, kern[name], traffic[name], pk)
         rooflines[name] = r
     roof = rooflines[top]
     line = dict(metric=METRIC, value=value, unit="edges/s", n_gpus=world, steps=args.steps,
@@ -537,7 +584,8 @@ def run_ours(args, w):
                             if world > 1 else "single GPU"),
                 e2e=dict(value=e2e_v, unit="edges/s", ms_per_step=ms_e2e / args.steps,
                          h2d_bytes_per_step=x_h.numel() * 4 + ei_h.numel() * 8, d2h_bytes_per_step=4),
-                gpu_launches=launches, roofline=roof, rooflines=rooflines, kernels=kern, clocks=clocks)
+                gpu_launches=launches, roofline=roof, rooflines=rooflines, kernels=kern, clocks=clocks,
+                partition=part)
     if world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         ws, sample = cpu_sample(w, args.cpu_frac)
@@ -555,26 +603,30 @@ def run_ours(args, w):
     finish()
 
 
-def run_partitioned(args, w):
-    """Strong scaling of one full-batch step on a 1-D destination-partitioned graph (BASELINE
-    configs[3], ogbn-products-shaped): every rank owns N/world nodes, their in-edges (forward) and
-    out-edges (backward); per layer one NCCL all-gather of the row blocks (halo exchange) forward
-    and one of the g_out blocks backward; SyncBatchNorm statistics, EMA code statistics and dense
-    gradients are all-reduced.  The graph is static (full-batch training), so K0 runs once."""
+PARTITION_N1_FILE = os.path.join(os.environ.get("TMPDIR", "/tmp"), "stemgnn_b200_partition_n1.json")
+
+
+def partition_modes(world):
+    """(label, halo_mode, wire dtype, transport) measured by the partition leg.  One rank has no exchange."""
+    if world == 1:
+        return [("single GPU (no exchange)", "gather", None, "p2p")]
+    modes = [("all-gather, fp32 wire (bit-identical to one GPU)", "gather", None, "p2p"),
+             ("owner blocks overlapped, pairwise send/recv, fp32 wire", "blocks", None, "p2p"),
+             ("owner blocks overlapped, pairwise send/recv, bf16 wire", "blocks", "bf16", "p2p")]
+    if os.environ.get("STEMGNN_HALO_BCAST", "0") == "1":
+        modes += [("owner blocks overlapped, broadcasts, fp32 wire", "blocks", None, "bcast"),
+                  ("owner blocks overlapped, broadcasts, bf16 wire", "blocks", "bf16", "bcast")]
+    return modes
+
+
+def measure_partition(w, dev, rank, world, steps, warmup, want_e2e=False):
+    """Strong scaling of one full-batch step on a 1-D destination-partitioned graph (BASELINE configs[3],
+    ogbn-products-shaped): every rank owns N/world nodes, their in-edges (forward) and out-edges (backward); per
+    layer one halo exchange of the row blocks forward and one of the g_out blocks backward; BatchNorm statistics,
+    EMA code statistics and dense gradients are all-reduced.  The graph is static (full-batch training), so K0
+    runs once.  Every mode of `partition_modes` is timed on the same graph and model; returns (on rank 0) the
+    record the bench line carries, None elsewhere."""
     import torch.distributed as dist
-    import __graft_entry__ as G
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    if rank == 0:
-        G.build()
-    if world > 1:
-        dist.barrier()
     import stemgnn_b200 as S
     from stemgnn_b200 import _lib
     g = torch.Generator().manual_seed(4)
@@ -594,8 +646,7 @@ def run_partitioned(args, w):
     x_all = torch.randn(n, w["f"], generator=g)
     x_h = x_all[lo:hi].contiguous().pin_memory()
     del x_all
-    pg = S.PartitionedGraph(None, n, rank=rank, world=world,
-                            pre_split=(torch.cat(fwd_parts, 1), torch.cat(bwd_parts, 1)))
+    split = (torch.cat(fwd_parts, 1), torch.cat(bwd_parts, 1))
     del fwd_parts, bwd_parts
     # BatchNorm statistics over ALL ranks' rows come from the library (K7 + norm_act.BatchSync: a
     # gather of (mean, var, n) forward, an all-reduce of the two column sums backward), not from
@@ -603,20 +654,22 @@ def run_partitioned(args, w):
     enc, vq, opt = build_models(w, dev, S)
     params = list(enc.parameters())
 
-    def step(x):
-        opt.zero_grad(set_to_none=True)
-        z = enc(x, pg)
-        q, ind, vq_loss, _ = vq(z)
-        loss = (q.square().sum() / (n * q.size(1))) + vq_loss.sum() * ((hi - lo) / n)
-        loss.backward()
-        if world > 1:
-            flat = torch.cat([p.grad.reshape(-1) for p in params])
-            dist.all_reduce(flat)
-            o = 0
-            for p in params:
-                p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
-        opt.step()
-        return loss
+    def make_step(pg):
+        def step(x):
+            opt.zero_grad(set_to_none=True)
+            z = enc(x, pg)
+            q, ind, vq_loss, _ = vq(z)
+            loss = (q.square().sum() / (n * q.size(1))) + vq_loss.sum() * ((hi - lo) / n)
+            loss.backward()
+            if world > 1:
+                flat = torch.cat([p.grad.reshape(-1) for p in params])
+                dist.all_reduce(flat)
+                o = 0
+                for p in params:
+                    p.grad.copy_(flat[o:o + p.numel()].view_as(p)); o += p.numel()
+            opt.step()
+            return loss
+        return step
 
     def sync_all():
         torch.cuda.synchronize()
@@ -625,74 +678,125 @@ def run_partitioned(args, w):
             torch.cuda.synchronize()
 
     x_d = x_h.to(dev)
-    for _ in range(max(args.warmup, 3)):
-        step(x_d)
-    sync_all()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    _lib.TRACE = []
-    l0 = _lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step(x_d)
-    e1.record()
-    sync_all()
-    ms = e0.elapsed_time(e1)
-    launches = (_lib.launch_count() - l0) / args.steps
-    trace, _lib.TRACE = _lib.TRACE, None
-    x_s = torch.empty_like(x_d)
-    loss_h = torch.empty(1).pin_memory()
-    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e2.record()
-    for _ in range(args.steps):
-        x_s.copy_(x_h, non_blocking=True)
-        loss_h.copy_(step(x_s).detach().reshape(1), non_blocking=True)
-    e3.record()
-    sync_all()
-    ms_e2e = e2.elapsed_time(e3)
-    clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
-    if rank == 0:
-        pk = peaks()
-        kern = summarize_trace(trace, args.steps, pk, False)
-        roof = roofline_of(kern, "aggregate", pk, False)
-        units = w["layers"] * e
-        line = dict(metric=METRIC, value=units * args.steps / (ms / 1e3), unit="edges/s", n_gpus=world,
-                    steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=ms / args.steps,
-                    higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
-                    data="synthetic", vq_nodes_per_s=n * args.steps / (ms / 1e3),
-                    config=dict(workload=w["desc"], layers=w["layers"], nodes=n, edges=e,
-                                l2="working set (N x F fp32 >= 980 MB) exceeds the 126 MB L2",
-                                parallelism=f"1-D destination partition x{world}, NCCL halo all-gather per layer"),
-                    e2e=dict(value=units * args.steps / (ms_e2e / 1e3), unit="edges/s",
-                             ms_per_step=ms_e2e / args.steps,
-                             h2d_bytes_per_step=x_h.numel() * 4 * world, d2h_bytes_per_step=4 * world),
-                    gpu_launches=launches, roofline=roof, kernels=kern, clocks=clocks)
-        print(json.dumps(line), flush=True)
-    # optional A/B of the halo exchange on the same graph: STEMGNN_HALO_SWEEP="2:f32,4:f32,1:bf16"
-    # (feature slices : wire dtype); results go to stderr, the JSON line above stays the only stdout line
-    for item in filter(None, os.environ.get("STEMGNN_HALO_SWEEP", "").split(",")):
-        sl, dt = item.split(":")
-        pg.halo_slices, pg.halo_dtype = int(sl), (torch.bfloat16 if dt == "bf16" else None)
-        for _ in range(2):
+    pk = peaks()
+    out_modes, extra = [], {}
+    for label, mode, wire, transport in partition_modes(world):
+        pg = S.PartitionedGraph(None, n, rank=rank, world=world, pre_split=split, halo_mode=mode,
+                                halo_transport=transport, halo_dtype=torch.bfloat16 if wire == "bf16" else None)
+        step = make_step(pg)
+        for _ in range(max(warmup, 3)):
             step(x_d)
         sync_all()
+        _lib.TRACE = []
+        l0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(args.steps):
+        for _ in range(steps):
             step(x_d)
         e1.record()
         sync_all()
-        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        launches = (_lib.launch_count() - l0) / steps
+        trace, _lib.TRACE = _lib.TRACE, None
+        times = [e0.elapsed_time(e1)]
+        if want_e2e and not out_modes:
+            x_s = torch.empty_like(x_d)
+            loss_h = torch.empty(1).pin_memory()
+            e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e2.record()
+            for _ in range(steps):
+                x_s.copy_(x_h, non_blocking=True)
+                loss_h.copy_(step(x_s).detach().reshape(1), non_blocking=True)
+            e3.record()
+            sync_all()
+            times.append(e2.elapsed_time(e3))
+        t = torch.tensor(times, dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        if rank == 0:
-            print(json.dumps(dict(sweep=item, n_gpus=world, ms_per_step=float(t[0]) / args.steps)),
-                  file=sys.stderr, flush=True)
+        kern = summarize_trace(trace, steps, pk, False)
+        ms_of = lambda *names: sum(kern[k]["ms_per_step"] for k in names if k in kern)
+        halo_bytes = sum(r[1] for r in trace if r[0] == "halo_wait") / steps
+        rec = dict(mode=label, halo_mode=mode, wire="bf16" if wire == "bf16" else "f32", transport=transport,
+                   ms_per_step=float(t[0]) / steps, halo_wait_ms=ms_of("halo_wait"), aggregate_ms=ms_of("aggregate"),
+                   dense_ms=ms_of("linear", "linear_wgrad"), batchnorm_ms=ms_of("bn_stats", "bn_act_forward", "bn_act_backward"),
+                   vq_ms=ms_of("vq_assign", "vq_code_stats", "vq_ema_apply", "vq_backward"),
+                   halo_bytes_received_per_rank_per_step=halo_bytes, gpu_launches=launches,
+                   note="per-family times are CUDA events around each C-ABI call on rank 0's compute stream in "
+                        "the timed steps themselves; halo_wait is what the compute stream waited for")
+        out_modes.append(rec)
+        if not extra:
+            extra = dict(kern=kern, launches=launches, ms_e2e=float(t[1]) if len(times) > 1 else None,
+                         h2d=x_h.numel() * 4 * world)
+        del pg, step
+        torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    fp32 = [m for m in out_modes if m["wire"] == "f32"]
+    best = min(fp32, key=lambda m: m["ms_per_step"])
+    rec = dict(workload=w["desc"], config="BASELINE configs[3]", scaling="strong", n_gpus=world, layers=w["layers"],
+               nodes=n, edges=e, steps=steps, warmup=max(warmup, 3), ms_per_step=best["ms_per_step"],
+               headline_mode=best["mode"] + " (fastest fp32-wire mode)",
+               value=w["layers"] * e / (best["ms_per_step"] / 1e3), unit="edges/s",
+               halo_wait_ms=best["halo_wait_ms"], aggregate_ms=best["aggregate_ms"], dense_ms=best["dense_ms"],
+               wire=best["wire"], halo_bytes_received_per_rank_per_step=best["halo_bytes_received_per_rank_per_step"],
+               modes=out_modes,
+               parity="all-gather mode: bit-identical to one GPU; owner-block modes: same terms summed block by block, "
+                      "<= 1e-5 of the output scale on the fp32 wire (tests/test_gpu_partition.py, "
+                      "scripts/check_partition_multi.py); bf16 wire: 2^-9 relative per gathered feature, opt-in",
+               l2="working set (N x F fp32 >= 980 MB) exceeds the 126 MB L2")
+    try:
+        if world == 1:
+            json.dump(dict(ms_per_step=rec["ms_per_step"], nodes=n, edges=e, layers=w["layers"]), open(PARTITION_N1_FILE, "w"))
+        elif os.path.exists(PARTITION_N1_FILE):
+            n1 = json.load(open(PARTITION_N1_FILE))
+            if (n1["nodes"], n1["edges"], n1["layers"]) == (n, e, w["layers"]):
+                rec["n1_ms_per_step"] = n1["ms_per_step"]
+                rec["efficiency_vs_n1"] = n1["ms_per_step"] / (world * rec["ms_per_step"])
+                rec["n1_source"] = "this bench's own 1-GPU partition leg, run earlier on this box (" + PARTITION_N1_FILE + ")"
+    except (OSError, ValueError, KeyError):
+        pass
+    rec["_extra"] = extra
+    return rec
+
+
+def run_partitioned(args, w):
+    """`--partition` / `--workload products`: the partition leg as the whole bench line (strong scaling)."""
+    import torch.distributed as dist
+    import __graft_entry__ as G
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    if rank == 0:
+        G.build()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    rec = measure_partition(w, dev, rank, world, args.steps, args.warmup, want_e2e=True)
+    clocks = sampler.stop() if rank == 0 else None
+    if rank == 0:
+        pk = peaks()
+        extra = rec.pop("_extra")
+        kern = extra["kern"]
+        roof = roofline_of(kern, "aggregate", pk, False)
+        first = rec["modes"][0]
+        units = w["layers"] * w["e"]
+        line = dict(metric=METRIC, value=rec["value"], unit="edges/s", n_gpus=world,
+                    steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=rec["ms_per_step"],
+                    higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f32",
+                    data="synthetic", vq_nodes_per_s=w["n"] / (rec["ms_per_step"] / 1e3),
+                    config=dict(workload=w["desc"], layers=w["layers"], nodes=w["n"], edges=w["e"],
+                                l2=rec["l2"], parallelism=f"1-D destination partition x{world}: " + rec["headline_mode"]),
+                    e2e=dict(value=units * args.steps / (extra["ms_e2e"] / 1e3), unit="edges/s",
+                             ms_per_step=extra["ms_e2e"] / args.steps, mode=first["mode"],
+                             h2d_bytes_per_step=extra["h2d"], d2h_bytes_per_step=4 * world),
+                    gpu_launches=extra["launches"], roofline=roof, kernels=kern, partition=rec, clocks=clocks)
+        print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -700,7 +804,8 @@ def run_partitioned(args, w):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=None,
+                    help="timed steps; default 300 (~1 s of timed region at 3.5 ms per step), 20 for --impl reference")
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="arxiv", choices=sorted(WORKLOADS))
@@ -709,6 +814,11 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--warm-seconds", type=float, default=1.0,
                     help="untimed sustained run of the same step right before the K timed steps")
+    ap.add_argument("--no-partition", action="store_true",
+                    help="skip the nested `partition` record (configs[3] on a 1-D partition over the same ranks)")
+    ap.add_argument("--partition-steps", type=int, default=5, help="timed steps per mode of the partition record")
+    ap.add_argument("--dump-sequence", default=None,
+                    help="write the C-ABI call sequence of one step (name, kernels launched, ms) to this JSON file")
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--partition", action="store_true",
                     help="1-D destination partition across the ranks (strong scaling, static graph)")
@@ -716,6 +826,8 @@ def main():
                     help="in-degree distribution of the synthetic graph: uniform endpoints (the headline "
                          "configuration) or SURVEY.md 8d's power-law variant with hubs of up to ~17,000 in-edges")
     args = ap.parse_args()
+    if args.steps is None:
+        args.steps = 20 if args.impl == "reference" else (300 if args.workload == "arxiv" and not args.partition else 20)
     w = dict(WORKLOADS[args.workload])
     if args.degree == "zipf":
         w["degree"] = "zipf"

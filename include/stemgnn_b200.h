@@ -50,6 +50,16 @@ int stemgnn_csr_build(const int64_t* edge_index, int64_t num_edges, int64_t num_
                       int group_row, int32_t* rowptr, int32_t* col, int32_t* perm, float* cnt,
                       void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
 
+/* Both groupings of ONE edge_index in the same launches (index 0: grouped by edge_index[0], the transposed
+ * structure the backward pass walks; index 1: grouped by edge_index[1], the forward structure): what a training
+ * step needs of every fresh mini-batch edge list (STEM-GNN/pretrain.py:41-45,151-153 hand the encoder a new
+ * edge_index per batch; model/encoder.py:82 and its autograd consume both orders).  Same outputs, bit for bit,
+ * as two stemgnn_csr_build calls; 4 kernel launches instead of 8 for 18-bit node ids. */
+int stemgnn_csr_build_pair_workspace(int64_t num_edges, int64_t num_nodes, size_t* bytes_host);
+int stemgnn_csr_build_pair(const int64_t* edge_index, int64_t num_edges, int64_t num_nodes,
+                           int32_t* const rowptr[2], int32_t* const col[2], int32_t* const perm[2],
+                           float* const cnt[2], void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+
 /* GCNConv.gcn_norm (torch_geometric 2.3.0, called from model/encoder.py:197): given the
  * edge list WITH remaining self loops already appended (edge_index_sl; the host side builds
  * it with integer mask/concat ops) and the CSR rowptr grouped by destination,

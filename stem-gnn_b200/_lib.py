@@ -64,6 +64,9 @@ SIGNATURES = {
     "stemgnn_launch_count": (C.c_uint64, []),
     "stemgnn_csr_build_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
     "stemgnn_csr_build": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "stemgnn_csr_build_pair_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
+    "stemgnn_csr_build_pair": (_i32, [_vp, _i64, _i64, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                                      _vp, C.c_size_t, _vp]),
     "stemgnn_gcn_edge_weight": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "stemgnn_aggregate": (_i32, [C.POINTER(AggregateArgs), _vp]),
     "stemgnn_aggregate_hub_workspace": (_i32, [_i64, C.POINTER(C.c_size_t)]),
@@ -188,12 +191,14 @@ class traced:
 
     def __enter__(self):
         if self.rec is not None:
+            self.rec[3] = -launch_count()
             self.rec[4].record()
         return self
 
     def __exit__(self, *exc):
         if self.rec is not None:
             self.rec[5].record()
+            self.rec[3] += launch_count()      # kernels this call launched, counted at the launch sites
             TRACE.append(self.rec)
         return False
 

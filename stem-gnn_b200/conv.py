@@ -15,12 +15,52 @@ from . import dense
 from .ops import aggregate
 
 
+def _sparse_coo(adj_t):
+    """(row, col) int64 of a sparse adjacency in row-major order, or None if `adj_t` is not one.  Accepted: torch
+    sparse CSR / COO tensors and anything with torch_sparse.SparseTensor's `.coo()` (row, col, value sorted by
+    (row, col)).  Values are dropped: the reference's fused path removes them (`adj_t.set_value(None)`,
+    model/encoder.py:99-102)."""
+    if isinstance(adj_t, Tensor):
+        if adj_t.layout == torch.sparse_csr:
+            crow, col = adj_t.crow_indices(), adj_t.col_indices()
+            row = torch.repeat_interleave(torch.arange(crow.numel() - 1, device=col.device), crow[1:] - crow[:-1])
+            return row.to(torch.int64), col.to(torch.int64)
+        if adj_t.layout == torch.sparse_coo:
+            idx = adj_t.coalesce().indices()
+            return idx[0], idx[1]
+        return None
+    coo = getattr(adj_t, "coo", None)
+    if callable(coo):
+        row, col = coo()[:2]
+        return row.to(torch.int64), col.to(torch.int64)
+    return None
+
+
 def _graph(edge_index, num_nodes):
+    """The aggregation structure of whatever the caller passed as `edge_index` (PyG's `Adj`): an int64 [2, E]
+    tensor, a GraphStructure / PartitionedGraph, or a sparse TRANSPOSED adjacency `adj_t` (rows = targets, columns
+    = sources: what PyG's ToSparseTensor produces and `message_and_aggregate` consumes, model/encoder.py:99-102).
+    A sparse adjacency becomes the edge list (col -> row) in its row-major order, so the K0 structure sums a row's
+    neighbours in column order like spmm does, and carries `fused = True`: PyG then skips `message` (no relu, no
+    edge features) and computes spmm(adj_t, x, reduce)."""
     if isinstance(edge_index, (GraphStructure, PartitionedGraph)):
         return edge_index
-    if not isinstance(edge_index, Tensor):
-        raise NotImplementedError("SparseTensor adjacency is not supported; pass edge_index [2,E]")
-    return structure_of(edge_index, num_nodes)
+    if isinstance(edge_index, Tensor) and edge_index.layout == torch.strided:
+        return structure_of(edge_index, num_nodes)
+    cached = getattr(edge_index, "_stemgnn_structure", None)
+    if cached is not None and cached.num_nodes == int(num_nodes):
+        return cached
+    rc = _sparse_coo(edge_index)
+    if rc is None:
+        raise TypeError("edge_index must be an int64 [2, E] tensor, a GraphStructure / PartitionedGraph, or a "
+                        f"sparse adjacency (torch sparse CSR / COO, torch_sparse.SparseTensor); got {type(edge_index)}")
+    g = GraphStructure(torch.stack([rc[1], rc[0]]).contiguous(), num_nodes)
+    g.fused = True
+    try:
+        edge_index._stemgnn_structure = g          # torch_sparse.SparseTensor is a plain Python object
+    except (AttributeError, RuntimeError):
+        pass
+    return g
 
 
 class MySAGEConv(nn.Module):
@@ -65,7 +105,11 @@ class MySAGEConv(nn.Module):
         if self.project:
             x = self.lin(x).relu()
         g = _graph(edge_index, x.size(0))
-        if isinstance(edge_attr, tuple):          # (type_table [T,F], edge_type [E]) fast form
+        if getattr(g, "fused", False):
+            # sparse adj_t: PyG's propagate takes message_and_aggregate = spmm(adj_t, x, reduce) and never calls
+            # message(): no relu, xe unused (model/encoder.py:99-102)
+            out = aggregate(x, g, reduce=self.aggr, act="none")
+        elif isinstance(edge_attr, tuple):          # (type_table [T,F], edge_type [E]) fast form
             out = aggregate(x, g, reduce=self.aggr, act="relu", type_table=edge_attr[0],
                             edge_type=edge_attr[1])
         else:

@@ -386,17 +386,19 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __rest
         __syncthreads();
     }
 }
-__global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ part, int blocks, int n,
-                                                           float* __restrict__ out) {
-    // one block per 32 columns; the 8 warps take every 8th
-    // partial row (coalesced 128 B reads), then add their sums in warp order
-    __shared__ float sh[8][32];
+constexpr int CSF_WARPS = 32;
+__global__ void __launch_bounds__(CSF_WARPS * 32) colsum_final_kernel(const float* __restrict__ part, int blocks, int n,
+                                                                      float* __restrict__ out) {
+    // one block per 32 columns; the 32 warps take every 32nd partial row (coalesced 128 B reads, all of a warp's
+    // loads in flight at once), then their sums are added in warp order
+    __shared__ float sh[CSF_WARPS][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
     float s0 = 0.f, s1 = 0.f;
     if (c < n) {
         int b = w;
-        for (; b + 8 < blocks; b += 16) { s0 += part[(int64_t)b * n + c]; s1 += part[(int64_t)(b + 8) * n + c]; }
+#pragma unroll 8
+        for (; b + CSF_WARPS < blocks; b += 2 * CSF_WARPS) { s0 += part[(int64_t)b * n + c]; s1 += part[(int64_t)(b + CSF_WARPS) * n + c]; }
         if (b < blocks) s0 += part[(int64_t)b * n + c];
     }
     sh[w][lane] = s0 + s1;
@@ -404,7 +406,7 @@ __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restri
     if (w == 0 && c < n) {
         float r = sh[0][lane];
 #pragma unroll
-        for (int i = 1; i < 8; ++i) r += sh[i][lane];
+        for (int i = 1; i < CSF_WARPS; ++i) r += sh[i][lane];
         out[c] = r;
     }
 }
@@ -533,7 +535,7 @@ extern "C" int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* a, void* wo
         const int64_t rpb = (a->m + pl.cs_blocks - 1) / pl.cs_blocks;
         const int blocks = (int)((a->m + rpb - 1) / rpb);
         SG_LAUNCH(wgrad::colsum_partial_kernel<<<blocks, 256, 0, stream>>>(a->g, a->ldg, a->m, (int)a->n, rpb, cs_part));
-        SG_LAUNCH(wgrad::colsum_final_kernel<<<(unsigned)((a->n + 31) / 32), 256, 0, stream>>>(cs_part, blocks, (int)a->n, a->gbias));
+        SG_LAUNCH(wgrad::colsum_final_kernel<<<(unsigned)((a->n + 31) / 32), wgrad::CSF_WARPS * 32, 0, stream>>>(cs_part, blocks, (int)a->n, a->gbias));
         SG_CHECK_LAUNCH();
     }
     return STEMGNN_OK;

@@ -110,24 +110,27 @@ col_reduce_kernel(const float* __restrict__ x, int64_t ldx, const float* __restr
 
 // sums the block partials per column in block order.  MODE 0 writes mean and biased variance,
 // MODE 1 writes the two sums.
+// 32 warps per 32 columns: with ~444 block partials a warp sums 14 of them, all 28 loads in flight at once (8
+// warps walked 55 partials each in dependent batches: 14 us per launch, six launches per bench step).
+constexpr int CF_WARPS = 32;
 template <int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(CF_WARPS * 32)
 col_final_kernel(const float* __restrict__ part, int blocks, int feat, int64_t rows, const float* __restrict__ x,
                  float* __restrict__ out0, float* __restrict__ out1) {
-    __shared__ float sh[2][8][32];
+    __shared__ float sh[2][CF_WARPS][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
     float a = 0.f, b = 0.f;
     if (c < feat) {
-#pragma unroll 8
-        for (int i = w; i < blocks; i += 8) { a += part[((int64_t)i * 2) * feat + c]; b += part[((int64_t)i * 2 + 1) * feat + c]; }
+#pragma unroll 16
+        for (int i = w; i < blocks; i += CF_WARPS) { a += part[((int64_t)i * 2) * feat + c]; b += part[((int64_t)i * 2 + 1) * feat + c]; }
     }
     sh[0][w][lane] = a; sh[1][w][lane] = b;
     __syncthreads();
     if (w == 0 && c < feat) {
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { s1 += sh[0][i][lane]; s2 += sh[1][i][lane]; }
+        for (int i = 0; i < CF_WARPS; ++i) { s1 += sh[0][i][lane]; s2 += sh[1][i][lane]; }
         if (MODE == 0) {
             const float n = (float)rows, m1 = s1 / n;
             out0[c] = __ldg(x + c) + m1;
@@ -232,7 +235,7 @@ extern "C" int stemgnn_bn_stats(int64_t rows, int64_t feat, const float* x, int6
     bn::Cols none{nullptr, nullptr, nullptr, nullptr};
     SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
                                                                       none, 0, 0.f, 1.f, nullptr, part));
-    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), 256, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
+    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }
@@ -275,7 +278,7 @@ extern "C" int stemgnn_bn_act_backward(int64_t rows, int64_t feat, const float* 
     const float inv_keep = 1.f / (1.f - p);
     SG_LAUNCH(bn::col_reduce_kernel<1><<<pl.blocks, 256, 0, stream>>>(x, ldx, gy, ldg, rows, (int)feat, pl.rows_per_block, cc,
                                                                       relu, p, inv_keep, seed, part));
-    SG_LAUNCH(bn::col_final_kernel<1><<<(unsigned)((feat + 31) / 32), 256, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, sum_g, sum_gx));
+    SG_LAUNCH(bn::col_final_kernel<1><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, sum_g, sum_gx));
     if (gx) {
         SG_CHECK_ARG(ldgx >= feat && ldgx % 4 == 0, "ldgx");
         SG_LAUNCH(bn::apply_kernel<true><<<ew_grid(rows * (feat / 4)), 256, 0, stream>>>(
@@ -356,7 +359,7 @@ extern "C" int stemgnn_bn_stats_static(int64_t rows, int64_t feat, const float* 
     bn::Cols none{nullptr, nullptr, nullptr, nullptr};
     SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
                                                                       none, 0, 0.f, 1.f, nullptr, part));
-    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), 256, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
+    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

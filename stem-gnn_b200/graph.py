@@ -20,7 +20,7 @@ class CSR:
     (>= 256 edges) in -- one per CSR, so aggregations over one CSR must be ordered on one stream."""
     __slots__ = ("rowptr", "col", "perm", "cnt", "n", "e", "hub")
 
-    def __init__(self, edge_index, num_nodes, group_row):
+    def __init__(self, edge_index, num_nodes, group_row, _build=True):
         L = _lib.lib()
         dev = edge_index.device
         E, N = edge_index.size(1), int(num_nodes)
@@ -32,12 +32,30 @@ class CSR:
         need = C.c_size_t(0)
         _lib.check(L.stemgnn_aggregate_hub_workspace(E, C.byref(need)))
         self.hub = torch.zeros(need.value, dtype=torch.uint8, device=dev)     # zeroed once; each call leaves it so
+        if not _build:
+            return
         _lib.check(L.stemgnn_csr_build_workspace(E, N, C.byref(need)))
         ws = _lib.workspace(need.value, dev)
         with _lib.traced("csr_build", E * (16 + 12) + (2 * N + 1) * 4, 0):
             _lib.check(L.stemgnn_csr_build(_lib.ptr(edge_index), E, N, group_row, _lib.ptr(self.rowptr),
                                            _lib.ptr(self.col), _lib.ptr(self.perm), _lib.ptr(self.cnt),
                                            _lib.ptr(ws), need.value, _lib.stream()))
+
+
+def build_pair(edge_index, num_nodes):
+    """{0: CSR grouped by edge_index[0], 1: CSR grouped by edge_index[1]} from ONE stemgnn_csr_build_pair call:
+    both groupings share their launches (what a training step needs of a fresh edge_index)."""
+    L = _lib.lib()
+    E, N = edge_index.size(1), int(num_nodes)
+    pair = [CSR(edge_index, N, r, _build=False) for r in (0, 1)]
+    need = C.c_size_t(0)
+    _lib.check(L.stemgnn_csr_build_pair_workspace(E, N, C.byref(need)))
+    ws = _lib.workspace(need.value, edge_index.device)
+    arr = lambda name: (C.c_void_p * 2)(*[_lib.ptr(getattr(c, name)) for c in pair])
+    with _lib.traced("csr_build", 2 * (E * (16 + 12) + (2 * N + 1) * 4), 0):
+        _lib.check(L.stemgnn_csr_build_pair(_lib.ptr(edge_index), E, N, arr("rowptr"), arr("col"), arr("perm"),
+                                            arr("cnt"), _lib.ptr(ws), need.value, _lib.stream()))
+    return {0: pair[0], 1: pair[1]}
 
 
 class GraphStructure:
@@ -58,6 +76,13 @@ class GraphStructure:
         if row not in self._csr:
             self._csr[row] = CSR(self.edge_index, self.num_nodes, row)
         return self._csr[row]
+
+    def prepare_training(self):
+        """Both groupings from ONE stemgnn_csr_build_pair call (the forward walks one, its autograd the other).
+        Called by `ops.aggregate` while grad mode is on -- inside an autograd Function's forward it is off, so
+        the lazy `grouped_by` alone would build them one by one."""
+        if not self._csr:
+            self._csr.update(build_pair(self.edge_index, self.num_nodes))
 
     @property
     def by_dst(self):

@@ -120,6 +120,17 @@ class _PartAggregate(torch.autograd.Function):
 
     @staticmethod
     def _run(pg, csr, local, out, row_cnt, row_x, act, backward):
+        if pg.halo_mode == "blocks":
+            # overlapped exchange: the own block first, every other owner block as it lands, accumulated into
+            # `out`; the count division / backward relu mask belong to the finished sum, i.e. to the last call
+            csrs = pg.block_csrs(backward)
+            last = pg.world - 1
+            for i, (b, blk) in enumerate(pg.exchange_blocks(local)):
+                fin = i == last
+                _aggregate_call(csrs[b], blk.size(0), blk, out, row_cnt=row_cnt if fin else None,
+                                row_x=row_x if (fin and backward) else None,
+                                act=act if (fin or not backward) else ACT_NONE, backward=backward, accumulate=i > 0)
+            return
         F = local.size(1)
         slices = pg.feature_slices(F)
         if len(slices) == 1:
@@ -189,6 +200,8 @@ def aggregate(x, graph, *, to_row=1, reduce="mean", act="none", edge_attr=None, 
         raise ValueError("edge_weight must have one entry per edge")
     r = {"mean": REDUCE_MEAN, "sum": REDUCE_SUM, "add": REDUCE_SUM}[reduce]
     a = {"none": ACT_NONE, "relu": ACT_RELU}[act]
+    if torch.is_grad_enabled():
+        graph.prepare_training()            # a training step walks both groupings: one build for the pair
     return _Aggregate.apply(x, graph, to_row, r, a, edge_attr, type_table, edge_type, edge_weight)
 
 

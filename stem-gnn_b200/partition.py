@@ -49,6 +49,29 @@ def local_edges(edge_index: torch.Tensor, lo: int, hi: int, owner_row: int) -> T
     return loc.contiguous(), eid
 
 
+def block_edges(edges: torch.Tensor, per: int, world: int, other_row: int) -> List[Tuple[torch.Tensor, torch.Tensor]]:
+    """Cut a rank's local edge list by the OWNER BLOCK of the other endpoint (row `other_row`, global ids):
+    [(edges of block b with that row shifted to ids inside the block, positions in `edges`)] for b in
+    range(world).  Inside a block the edges keep their relative order."""
+    out = []
+    owner = torch.div(edges[other_row], max(per, 1), rounding_mode="floor")
+    for b in range(world):
+        pos = (owner == b).nonzero(as_tuple=False).view(-1)
+        sub = edges[:, pos].clone()
+        sub[other_row] -= b * per
+        out.append((sub.contiguous(), pos))
+    return out
+
+
+def exchange_order(rank: int, world: int, transport: str) -> List[int]:
+    """Owner blocks in the order a rank consumes them in the overlapped exchange: its own block first (no wire),
+    then in order of arrival -- round k of the pairwise exchange brings the block of rank - k; the broadcasts
+    arrive in rank order."""
+    if transport == "p2p":
+        return [(rank - k) % world for k in range(world)]
+    return [rank] + [b for b in range(world) if b != rank]
+
+
 class PartitionedGraph:
     """This rank's share of a 1-D destination-partitioned graph.  Accepted wherever the drop-in
     layers take `edge_index` (like GraphStructure).
@@ -63,7 +86,8 @@ class PartitionedGraph:
                  world: Optional[int] = None, group=None,
                  gather: Optional[Callable[[torch.Tensor], torch.Tensor]] = None, pre_split=None,
                  halo_slices: Optional[int] = None, halo_dtype: Optional[torch.dtype] = None,
-                 stat_gather=None, stat_reduce=None):
+                 stat_gather=None, stat_reduce=None, halo_mode: str = "gather", halo_transport: str = "p2p",
+                 blocks: Optional[Callable[[torch.Tensor], List[torch.Tensor]]] = None):
         if world is None:
             world = dist.get_world_size(group) if dist.is_initialized() else 1
         if rank is None:
@@ -87,6 +111,17 @@ class PartitionedGraph:
         self.halo_slices, self.halo_dtype = halo_slices, halo_dtype
         if halo_dtype not in (None, torch.float32, torch.bfloat16):
             raise ValueError("halo_dtype must be None, torch.float32 or torch.bfloat16")
+        # halo_mode "gather": one blocking all-gather per exchange, then ONE aggregation over the rank's CSR --
+        #   every row's edges in original order, bit-identical to one GPU (the default, and what parity tests use).
+        # halo_mode "blocks": the overlapped exchange.  The rank's CSR is cut by source-owner block (K0, once per
+        #   graph); the row blocks travel one by one (pairwise send/recv rounds or broadcasts, all issued up front
+        #   on the collective's own stream) and block b is aggregated into `out` (stemgnn_aggregate, accumulate = 1)
+        #   as soon as it has landed, the rank's own block first -- while the later blocks are still on the wire.
+        #   A row's sum then runs block by block instead of in edge order: same terms, different order,
+        #   |difference| <= a few fp32 roundings of the row's partial sums (tests hold 1e-5 of the output scale).
+        if halo_mode not in ("gather", "blocks") or halo_transport not in ("p2p", "bcast"):
+            raise ValueError("halo_mode is 'gather' or 'blocks'; halo_transport is 'p2p' or 'bcast'")
+        self.halo_mode, self.halo_transport, self._blocks = halo_mode, halo_transport, blocks
 
     def batch_sync(self):
         """Collectives for full-batch BatchNorm over the partition (norm_act.BatchSync), or None when
@@ -108,6 +143,58 @@ class PartitionedGraph:
         if "b" not in self._csr:
             self._csr["b"] = CSR(self.bwd_edges, self.num_nodes, 0)
         return self._csr["b"]
+
+    def block_csrs(self, backward: bool) -> List[CSR]:
+        """The rank's CSR cut by owner block of the gathered endpoint: entry b holds the edges whose source
+        (forward) / destination (backward) rank b owns, col = row inside b's block."""
+        key = "bb" if backward else "fb"
+        if key not in self._csr:
+            edges, own_row = (self.bwd_edges, 0) if backward else (self.fwd_edges, 1)
+            self._csr[key] = [CSR(sub, self.num_nodes, own_row)
+                              for sub, _ in block_edges(edges, self.per, self.world, 1 - own_row)]
+        return self._csr[key]
+
+    def exchange_blocks(self, local: torch.Tensor):
+        """Start the exchange of this rank's row block and yield (owner b, block [per, F] fp32) in
+        `exchange_order`: the own block at once, every other one after its transfer has completed (the wait is
+        stream-ordered for NCCL: the host does not block)."""
+        blk = self._padded_block(local)
+        order = exchange_order(self.rank, self.world, self.halo_transport)
+        if self._blocks is not None:                       # tests: the other ranks' blocks are known
+            got = self._blocks(blk)
+            for b in order:
+                yield b, (blk if b == self.rank else got[b])
+            return
+        if self.world == 1:
+            yield self.rank, blk
+            return
+        wire = blk if self.halo_dtype in (None, torch.float32) else blk.to(self.halo_dtype)
+        wire = wire.contiguous()
+        nbytes = wire.numel() * wire.element_size()
+        ranks = dist.get_process_group_ranks(self.group) if self.group is not None else list(range(self.world))
+        pending = []
+        if self.halo_transport == "p2p":
+            for k in range(1, self.world):
+                src, dst = (self.rank - k) % self.world, (self.rank + k) % self.world
+                buf = torch.empty_like(wire)
+                ops = [dist.P2POp(dist.isend, wire, ranks[dst], self.group),
+                       dist.P2POp(dist.irecv, buf, ranks[src], self.group)]
+                pending.append((src, buf, dist.batch_isend_irecv(ops)))
+        else:
+            for b in range(self.world):
+                buf = wire if b == self.rank else torch.empty_like(wire)
+                work = dist.broadcast(buf, ranks[b], group=self.group, async_op=True)
+                if b != self.rank:
+                    pending.append((b, buf, [work]))
+                else:
+                    pending.append((None, None, [work]))
+        yield self.rank, blk
+        for b, buf, works in pending:
+            with _lib.traced("halo_wait", nbytes if b is not None else 0, 0, 0):
+                for w in works:
+                    w.wait()
+            if b is not None:
+                yield b, (buf if buf.dtype == torch.float32 else buf.float())
 
     def feature_slices(self, f: int) -> List[Tuple[int, int]]:
         """Column ranges the halo exchange of an [n, f] matrix is pipelined over (16-byte aligned)."""

@@ -36,6 +36,53 @@ def _batched_sample_vectors(samples, num):
     return torch.stack(out, dim=0)
 
 
+def _sample_multinomial(total_count, probs):
+    """model/vq.py:120-134: split `total_count` draws over the ranks in proportion to `probs` (sequential
+    binomials on the CPU, like the reference)."""
+    device = probs.device
+    probs = probs.cpu()
+    total = probs.new_full((), total_count)
+    remainder = probs.new_ones(())
+    sample = torch.empty_like(probs, dtype=torch.long)
+    for i, p in enumerate(probs):
+        s = torch.binomial(total, (p / remainder).clamp(0, 1))
+        sample[i] = s
+        total = total - s
+        remainder = remainder - p
+    return sample.to(device)
+
+
+def _sample_vectors_distributed(samples, num, group=None):
+    """model/vq.py:158-180 (sample_vectors_distributed): the `num` initial means are drawn from ALL ranks' rows --
+    rank 0 splits `num` multinomially by the ranks' row counts, every rank draws its share locally, the shares
+    are exchanged (one broadcast per rank, sizes known from the split) and concatenated in rank order, so every
+    rank ends with the same [1, num, D] tensor.  One codebook only (the reference asserts the same, vq.py:285)."""
+    if samples.size(0) != 1:
+        raise NotImplementedError("distributed kmeans init with several codebooks (model/vq.py:285)")
+    local = samples[0]
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    ranks = dist.get_process_group_ranks(group) if group is not None else list(range(world))
+    size = torch.tensor([local.size(0)], dtype=torch.long, device=local.device)
+    sizes = [torch.empty_like(size) for _ in range(world)]
+    dist.all_gather(sizes, size, group=group)
+    sizes = torch.cat(sizes)
+    if rank == 0:
+        per_rank = _sample_multinomial(num, sizes / sizes.sum())
+    else:
+        per_rank = torch.empty_like(sizes)
+    dist.broadcast(per_rank, src=ranks[0], group=group)
+    per_rank = per_rank.tolist()
+    mine = _batched_sample_vectors(local.unsqueeze(0), per_rank[rank])[0] if per_rank[rank] > 0 \
+        else local.new_empty((0, local.size(1)))
+    parts = []
+    for r, cnt in enumerate(per_rank):
+        t = mine.contiguous() if r == rank else local.new_empty((cnt, local.size(1)))
+        if cnt > 0:
+            dist.broadcast(t, src=ranks[r], group=group)
+        parts.append(t)
+    return torch.cat(parts, dim=0).unsqueeze(0)
+
+
 class _Codebook(nn.Module):
     """State holder shared by the Euclidean (model/vq.py:241-514) and cosine (model/vq.py:516-688)
     codebooks: buffers initted (1,), cluster_size (Hc,K), embed_avg (Hc,K,D) and embed (Hc,K,D;
@@ -44,13 +91,16 @@ class _Codebook(nn.Module):
 
     def __init__(self, dim, codebook_size, num_codebooks=1, kmeans_init=False, kmeans_iters=10,
                  decay=0.8, eps=1e-5, use_ddp=False, learnable_codebook=False, ema_update=True,
-                 path=ops.PATH_AUTO):
+                 path=ops.PATH_AUTO, sync_kmeans=True):
         super().__init__()
         self.dim, self.codebook_size, self.num_codebooks = dim, codebook_size, num_codebooks
         self.kmeans_iters, self.decay, self.eps = kmeans_iters, decay, eps
         self.use_ddp, self.learnable_codebook, self.ema_update = use_ddp, learnable_codebook, ema_update
         self.path = path
-        self.sample_fn = _batched_sample_vectors                  # like the reference's attribute (vq.py:287)
+        # model/vq.py:287-288: with use_ddp and sync_kmeans the initial means are drawn from every rank's rows and
+        # the k-means statistics are all-reduced; with sync_kmeans off the init is local (no collective at all)
+        self.sync_kmeans = bool(use_ddp and sync_kmeans)
+        self.sample_fn = _sample_vectors_distributed if self.sync_kmeans else _batched_sample_vectors
         if kmeans_init:
             embed = torch.zeros(num_codebooks, codebook_size, dim)
         else:
@@ -91,17 +141,13 @@ class _Codebook(nn.Module):
         Hc, K, D = self.embed.shape
         rows = x.view(x.size(0), heads, D).permute(1, 0, 2) if Hc == heads else x.reshape(1, -1, D)
         means = self.sample_fn(rows, K).contiguous()              # vq.py:192
-        if self.use_ddp:
-            # every rank must start from the same means (counts and sums are all-reduced below).  The
-            # reference draws a multinomial share of them on every rank and gathers (vq.py:158-180);
-            # here rank 0's sample is broadcast -- a valid k-means start, not the same draw.
-            dist.broadcast(means, src=0)
         counts = None
         for _ in range(self.kmeans_iters):
             ind, _, _, _ = ops.vq_assign_raw(x, means, heads, self.metric, ops.PATH_EXACT,
                                              want_sq_err=False)
             counts, sums, flat = ops.vq_code_stats(x, ind, (Hc, K, D), heads)
-            self._all_reduce(flat)
+            if self.sync_kmeans:                                   # kmeans_all_reduce_fn (vq.py:288)
+                dist.all_reduce(flat)
             empty = counts == 0
             new = sums / counts.masked_fill(empty, 1).unsqueeze(-1)
             if self.cosine:
@@ -201,7 +247,7 @@ class VectorQuantize(nn.Module):
         self._codebook = cls(dim=codebook_dim, codebook_size=codebook_size,
                              num_codebooks=heads if separate_codebook_per_head else 1,
                              kmeans_init=kmeans_init, kmeans_iters=kmeans_iters, decay=decay, eps=eps,
-                             use_ddp=sync_codebook,
+                             use_ddp=sync_codebook, sync_kmeans=sync_kmeans,
                              learnable_codebook=self.has_codebook_orthogonal_loss or learnable_codebook,
                              ema_update=ema_update, path=assign_path)
         self.in_place_codebook_optimizer = None

@@ -36,6 +36,40 @@ def test_csr_build_bit_exact(n, e, hub):
         assert np.array_equal(c.cnt.cpu().numpy(), np.maximum(deg, 1).astype(np.float32))
 
 
+@pytest.mark.parametrize("n,e,hub", [(1, 0, 0), (3, 1, 0), (300, 5000, 0), (512, 40000, 9000), (513, 3000, 0),
+                                     (5000, 70000, 9000), (40000, 300000, 21000), (169343, 1166243, 0),
+                                     (600000, 2000000, 30000), (2449029 // 4, 61859140 // 16, 0)])
+def test_csr_single_and_pair_builds_bit_exact(n, e, hub):
+    """Every plan of the round-2 build: no upper pass (N <= 512), one upper pass of 256 / 512 bins, two upper
+    passes (N > 2^18), segments of several chunks (hubs), both through stemgnn_csr_build (no_grad: one grouping per
+    call) and stemgnn_csr_build_pair (grad enabled: both groupings in one set of launches)."""
+    ei = _graph(n, e, 3, hub)
+    ei_d = ei.to(DEV)
+    refs = [graph_ref.csr_build_ref(ei.numpy(), n, by) for by in (0, 1)]
+    with torch.no_grad():
+        g1 = S.GraphStructure(ei_d, n)
+        single = [g1.grouped_by(0), g1.grouped_by(1)]
+    g2 = S.GraphStructure(ei_d, n)
+    g2.prepare_training()
+    assert set(g2._csr) == {0, 1}                       # one call built both
+    pair = [g2.grouped_by(0), g2.grouped_by(1)]
+    if e:
+        x = torch.randn(n, 4, device=DEV, requires_grad=True)
+        g3 = S.GraphStructure(ei_d, n)
+        c0 = S._lib.launch_count()
+        S.aggregate(x, g3, reduce="sum")                # grad mode on: the op asks for the pair up front
+        assert set(g3._csr) == {0, 1}
+        if n == 169343:                                 # 18-bit ids: hist, scan, scatter, bucket + the aggregation's two
+            assert S._lib.launch_count() - c0 == 6
+    for by in (0, 1):
+        rowptr, col, perm, deg = refs[by]
+        for c in (single[by], pair[by]):
+            assert np.array_equal(c.rowptr.cpu().numpy(), rowptr)
+            assert np.array_equal(c.perm.cpu().numpy(), perm)
+            assert np.array_equal(c.col.cpu().numpy(), col)
+            assert np.array_equal(c.cnt.cpu().numpy(), np.maximum(deg, 1).astype(np.float32))
+
+
 def _check(x, ei, n, *, reduce, act, xe=None, table=None, etype=None, exact=True):
     xc = x.clone().requires_grad_(True)
     xe_full = xe if xe is not None else (table[etype] if table is not None else None)

@@ -131,6 +131,24 @@ def _bn_worker(rank, world, port, n, f, ret):
         assert S.VectorQuantize(dim=8, codebook_size=4, sync_codebook=False)._codebook.use_ddp is False
         with pytest.raises(NotImplementedError):
             S.VectorQuantize(dim=8, codebook_size=4, heads=2, separate_codebook_per_head=True, kmeans_init=True)
+        # k-means init (model/vq.py:287-288): sync_kmeans on -> the initial means come from EVERY rank's rows
+        # (multinomial split on rank 0, local draws, exchange) and are the same tensor on all ranks; off -> the
+        # local sampler and no collective
+        from stemgnn_b200 import vq as V
+        cb = S.VectorQuantize(dim=8, codebook_size=4, kmeans_init=True)._codebook
+        assert cb.sync_kmeans is True and cb.sample_fn is V._sample_vectors_distributed
+        cb = S.VectorQuantize(dim=8, codebook_size=4, kmeans_init=True, sync_kmeans=False)._codebook
+        assert cb.sync_kmeans is False and cb.sample_fn is V._batched_sample_vectors
+        torch.manual_seed(100 + rank)
+        rows = torch.arange((rank + 1) * 300, dtype=torch.float32).view(-1, 1).repeat(1, 3) + 10000 * rank
+        means = V._sample_vectors_distributed(rows.unsqueeze(0), 64)     # rank 0 owns 300 rows, rank 1 600
+        assert means.shape == (1, 64, 3)
+        both = [torch.empty_like(means) for _ in range(world)]
+        dist.all_gather(both, means)
+        assert torch.equal(both[0], both[1])                              # identical on every rank
+        owner = (means[0, :, 0] >= 10000).long()
+        assert 0 < int(owner.sum()) < 64 and torch.all(owner[1:] >= owner[:-1])      # both ranks contribute, rank order
+        assert means[0, :, 0].unique().numel() == 64                      # without replacement
         ret[rank] = 1
     finally:
         dist.destroy_process_group()
@@ -152,3 +170,97 @@ def test_batchnorm_statistics_over_two_ranks_gloo():
         p.join(100)
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert dict(ret) == {0: 1, 1: 1}
+
+
+# ------------------------------------------------------------------ the overlapped exchange (halo_mode="blocks")
+def test_block_edges_cut_by_owner_block_and_keep_order():
+    from stemgnn_b200.partition import block_edges, block_size, exchange_order, local_edges, partition_1d
+    g = torch.Generator().manual_seed(1)
+    n, e, world = 53, 900, 4
+    ei = torch.randint(0, n, (2, e), generator=g)
+    per = block_size(n, world)
+    for rank, (lo, hi) in enumerate(partition_1d(n, world)):
+        for own_row in (1, 0):                             # forward: owned destinations; backward: owned sources
+            loc, _ = local_edges(ei, lo, hi, own_row)
+            seen = torch.zeros(loc.size(1), dtype=torch.int64)
+            for b, (sub, pos) in enumerate(block_edges(loc, per, world, 1 - own_row)):
+                assert torch.all(pos[1:] > pos[:-1])                                # relative order kept
+                assert torch.equal(sub[own_row], loc[own_row, pos])
+                assert torch.equal(sub[1 - own_row] + b * per, loc[1 - own_row, pos])
+                assert sub.numel() == 0 or (0 <= int(sub[1 - own_row].min()) and int(sub[1 - own_row].max()) < per)
+                seen[pos] += 1
+            assert torch.all(seen == 1)
+        for tr in ("p2p", "bcast"):
+            order = exchange_order(rank, world, tr)
+            assert order[0] == rank and sorted(order) == list(range(world))
+
+
+def test_block_by_block_sum_equals_the_edge_order_sum_within_rounding():
+    """What stemgnn_aggregate(accumulate=1) computes over the owner-block CSRs, restated on the CPU: the row sums
+    run block by block (own block first) instead of in edge order -- 1e-5 of the output scale, not bit-identical."""
+    from oracle import propagate_ref as P
+    from stemgnn_b200.partition import block_edges, block_size, exchange_order, local_edges, partition_1d
+    g = torch.Generator().manual_seed(2)
+    n, e, f, world = 211, 6000, 16, 4
+    ei = torch.randint(0, n, (2, e), generator=g)
+    ei[1, :700] = 5
+    x = torch.randn(n, f, generator=g)
+    ref = P.sage_propagate_ref(x, ei, None, n, "mean")
+    per = block_size(n, world)
+    xp = torch.cat([x, x.new_zeros(world * per - n, f)])
+    deg = torch.bincount(ei[1], minlength=n).clamp(min=1).float()
+    for rank, (lo, hi) in enumerate(partition_1d(n, world)):
+        loc, _ = local_edges(ei, lo, hi, 1)
+        subs = block_edges(loc, per, world, 0)
+        acc = torch.zeros(hi - lo, f)
+        for b in exchange_order(rank, world, "p2p"):
+            sub = subs[b][0]
+            blk = xp[b * per:(b + 1) * per]
+            acc = acc.index_add(0, sub[1], torch.relu(blk.index_select(0, sub[0])))
+        out = acc / deg[lo:hi].view(-1, 1)
+        err = (out - ref[lo:hi]).abs().max() / ref.abs().max()
+        assert float(err) < 1e-5
+
+
+def _blocks_worker(rank, world, port, n, f, transport, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from stemgnn_b200.partition import PartitionedGraph, block_size, exchange_order, partition_1d
+        g = torch.Generator().manual_seed(7)
+        x = torch.randn(n, f, generator=g)
+        per = block_size(n, world)
+        lo, hi = partition_1d(n, world)[rank]
+        empty = torch.zeros(2, 0, dtype=torch.int64)
+        for wire in (None, torch.bfloat16):
+            pg = PartitionedGraph(None, n, rank=rank, world=world, pre_split=(empty, empty), halo_mode="blocks",
+                                  halo_transport=transport, halo_dtype=wire)
+            got = list(pg.exchange_blocks(x[lo:hi]))
+            assert [b for b, _ in got] == exchange_order(rank, world, transport)
+            for b, blk in got:
+                blo, bhi = partition_1d(n, world)[b]
+                want = torch.zeros(per, f)
+                want[:bhi - blo] = x[blo:bhi]
+                assert blk.shape == (per, f) and blk.dtype == torch.float32
+                if wire is None or b == rank:
+                    assert torch.equal(blk, want)                  # own block never crosses the wire
+                else:
+                    assert torch.equal(blk, want.to(torch.bfloat16).float())
+        ret[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("world,transport", [(2, "p2p"), (2, "bcast"), (3, "p2p"), (3, "bcast")])
+def test_block_exchange_delivers_every_owner_block_gloo(world, transport):
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 33500 + (os.getpid() % 2000) + 7 * world + (1 if transport == "p2p" else 0)
+    procs = [ctx.Process(target=_blocks_worker, args=(r, world, port, 103, 8, transport, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(150)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert dict(ret) == {r: 1 for r in range(world)}
