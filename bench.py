@@ -50,6 +50,15 @@ METRIC = "edges/sec encoder fwd+bwd & VQ nodes/sec"
 L2_FLUSH_BYTES = 256 << 20
 
 
+def init_nccl(dist, dev):
+    """One process per GPU over NCCL.  The collectives' stream is created at HIGH priority: in the overlapped halo
+    exchange (PartitionedGraph halo_mode='blocks') the send/recv kernels of the next block must get SMs while an
+    aggregation launch of thousands of CTAs is running -- measured on 4 B200s (profiles/r02_partition_prio_4gpu.log):
+    aggregation pair 5.88 -> 4.72 ms with it, against 5.67 ms for the blocking all-gather."""
+    opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+    dist.init_process_group("nccl", device_id=dev, pg_options=opts)
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -370,7 +379,7 @@ def run_ours(args, w):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        init_nccl(dist, dev)
     if rank == 0:
         G.build()
     if world > 1:
@@ -769,7 +778,7 @@ def run_partitioned(args, w):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        init_nccl(dist, dev)
     if rank == 0:
         G.build()
     if world > 1:

@@ -9,7 +9,10 @@ import stemgnn_b200 as S
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    opts = None
+    if os.environ.get("STEMGNN_NCCL_HIGH_PRIO", "0") == "1":       # collectives on a high-priority stream: their copy
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)   # kernels get SMs while an aggregation runs
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
     n, e, f = int(os.environ.get("N", 300000)), int(os.environ.get("E", 6000000)), int(os.environ.get("F", 100))
     g = torch.Generator().manual_seed(7)
     ei = torch.randint(0, n, (2, e), generator=g).cuda()

@@ -105,6 +105,14 @@ class MySAGEConv(nn.Module):
         if self.project:
             x = self.lin(x).relu()
         g = _graph(edge_index, x.size(0))
+        if x.size(1) % 4:
+            # a width like Cora's 1,433: pad the features (and per-edge features) once, so the aggregation runs the
+            # 128-bit kernels and the padded columns -- zeros all the way -- meet zero weight columns in the GEMM
+            x, x_r = dense.pad4(x), dense.pad4(x_r)
+            if isinstance(edge_attr, tuple):
+                edge_attr = (dense.pad4(edge_attr[0]), edge_attr[1])
+            elif edge_attr is not None:
+                edge_attr = dense.pad4(edge_attr)
         if getattr(g, "fused", False):
             # sparse adj_t: PyG's propagate takes message_and_aggregate = spmm(adj_t, x, reduce) and never calls
             # message(): no relu, xe unused (model/encoder.py:99-102)
@@ -114,16 +122,11 @@ class MySAGEConv(nn.Module):
                             edge_type=edge_attr[1])
         else:
             out = aggregate(x, g, reduce=self.aggr, act="relu", edge_attr=edge_attr)
-        if x.is_cuda and dense.supported(out.size(1), self.out_channels):
-            # lin_l(out) + lin_r(x_r) as ONE tensor-core GEMM over the concatenated K (K5/K6)
-            if self.root_weight:
-                out = dense.linear_sum([out, x_r], [self.lin_l.weight, self.lin_r.weight], self.lin_l.bias)
-            else:
-                out = dense.linear_sum([out], [self.lin_l.weight], self.lin_l.bias)
+        # lin_l(out) + lin_r(x_r) as ONE tensor-core GEMM over the concatenated K (K5/K6)
+        if self.root_weight:
+            out = dense.linear_sum([out, x_r], [self.lin_l.weight, self.lin_r.weight], self.lin_l.bias)
         else:
-            out = self.lin_l(out)
-            if self.root_weight:
-                out = out + self.lin_r(x_r)
+            out = dense.linear_sum([out], [self.lin_l.weight], self.lin_l.bias)
         if self.normalize:
             out = F.normalize(out, p=2.0, dim=-1)
         return out
@@ -163,11 +166,10 @@ class GCNConv(nn.Module):
             raise NotImplementedError("GCNConv on a partitioned graph (symmetric normalisation needs "
                                       "the degrees of remote sources) is not built yet")
         g_sl, w = g.gcn()
-        if x.is_cuda and dense.supported(self.in_channels, self.out_channels):
-            h = dense.linear_sum([x], [self.lin.weight], None)        # K5/K6 (tcgen05, fp32 accuracy)
-        else:
-            h = self.lin(x)
-        out = aggregate(h, g_sl, reduce="sum", edge_weight=w)
+        h = dense.linear_sum([x], [self.lin.weight], None)            # K5/K6 (tcgen05, fp32 accuracy)
+        fo = h.size(1)
+        out = aggregate(dense.pad4(h), g_sl, reduce="sum", edge_weight=w)
+        out = out[:, :fo] if out.size(1) != fo else out
         return out + self.bias if self.bias is not None else out
 
 
@@ -198,7 +200,9 @@ class GINConv(nn.Module):
         if size is not None and not isinstance(size, (tuple, list)):
             raise NotImplementedError("GINConv takes no edge features (model/encoder.py:311 passes "
                                       "edge_attr as `size`; use edge_attr=None with backbone='gin')")
-        out = aggregate(x, _graph(edge_index, x.size(0)), reduce="sum")
+        f = x.size(1)
+        out = aggregate(dense.pad4(x), _graph(edge_index, x.size(0)), reduce="sum")
+        out = out[:, :f] if out.size(1) != f else out
         return self.nn(out + (1 + self.eps) * x)
 
 
@@ -217,16 +221,13 @@ class MixtureSageLayer(nn.Module):
         nn.init.xavier_uniform_(self.weights)
 
     def forward(self, x: Tensor, edge_index, edge_attr: Optional[Tensor] = None) -> Tensor:
-        agg = aggregate(x, _graph(edge_index, x.size(0)), to_row=0, reduce="mean")
-        if x.is_cuda and dense.supported(self.in_dim, self.out_dim):
-            # einsum('nd,kdo->nko', [agg|x], W) for all experts as ONE two-source GEMM (K5/K6): the
-            # experts are stacked along the output dimension, [agg|x] is never concatenated
-            w_all = self.weights.permute(0, 2, 1).reshape(self.num_experts * self.out_dim, 2 * self.in_dim)
-            outputs = dense.linear_sum([agg, x], [w_all[:, :self.in_dim], w_all[:, self.in_dim:]], None)
-            outputs = outputs.view(x.size(0), self.num_experts, self.out_dim)
-        else:
-            combined = torch.cat([agg, x], dim=-1)
-            outputs = torch.einsum("nd,kdo->nko", combined, self.weights)
+        xp = dense.pad4(x)
+        agg = aggregate(xp, _graph(edge_index, x.size(0)), to_row=0, reduce="mean")
+        # einsum('nd,kdo->nko', [agg|x], W) for all experts as ONE two-source GEMM (K5/K6): the
+        # experts are stacked along the output dimension, [agg|x] is never concatenated
+        w_all = self.weights.permute(0, 2, 1).reshape(self.num_experts * self.out_dim, 2 * self.in_dim)
+        outputs = dense.linear_sum([agg, xp], [w_all[:, :self.in_dim], w_all[:, self.in_dim:]], None)
+        outputs = outputs.reshape(x.size(0), self.num_experts, self.out_dim)
         if self.residual:
             outputs = outputs + x.unsqueeze(1)
         return outputs

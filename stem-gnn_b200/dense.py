@@ -93,14 +93,26 @@ def linear_raw(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
     return out
 
 
+WGRAD_MAX_TILES = 64     # 256 x 256 weight tiles one stemgnn_linear_wgrad call takes (include/stemgnn_b200.h)
+
+
 def linear_wgrad_raw(g: torch.Tensor, srcs: Sequence[torch.Tensor], want_bias: bool = False):
-    """([g.T @ srcs[s] for s], g.sum(0) or None) in one stemgnn_linear_wgrad call."""
+    """([g.T @ srcs[s] for s], g.sum(0) or None) in one stemgnn_linear_wgrad call; weight matrices of more than
+    64 tiles of 256 x 256 are cut into blocks of output features (column slices of g), one call each."""
     ns = len(srcs)
     if ns not in (1, 2):
         raise ValueError("one or two sources")
     g = _rowmajor(_check(g, "grad"))
     srcs = [_rowmajor(_check(a, "src")) for a in srcs]
     m, n = g.shape
+    kbt = -(-sum(int(a.size(1)) for a in srcs) // 256)
+    if -(-n // 256) * kbt > WGRAD_MAX_TILES:
+        if kbt > WGRAD_MAX_TILES:
+            raise ValueError(f"sum of the source widths above {WGRAD_MAX_TILES * 256} columns")
+        nb = (WGRAD_MAX_TILES // kbt) * 256
+        parts = [linear_wgrad_raw(g[:, lo:min(n, lo + nb)], srcs, want_bias) for lo in range(0, n, nb)]
+        gws = [torch.cat([p[0][s] for p in parts], dim=0) for s in range(ns)]
+        return gws, (torch.cat([p[1] for p in parts]) if want_bias else None)
     if n % 4 or any(a.size(1) % 4 for a in srcs):
         raise ValueError("feature widths must be multiples of 4 (pad the layer)")
     if any(a.size(0) != m for a in srcs):
@@ -152,12 +164,31 @@ class _LinearSum(torch.autograd.Function):
         return (gb, *gxs, *gws)
 
 
+def pad4(t: torch.Tensor, rows: bool = False) -> torch.Tensor:
+    """Zero-pad the last dimension (and, with `rows`, the first) of a matrix / vector to a multiple of 4: the
+    kernels read 16-byte row segments.  Differentiable (the gradient of the padding is dropped)."""
+    rk = (-t.size(-1)) % 4
+    rn = (-t.size(0)) % 4 if rows and t.dim() == 2 else 0
+    if not (rk or rn):
+        return t
+    return torch.nn.functional.pad(t, (0, rk, 0, rn) if t.dim() == 2 else (0, rk))
+
+
 def linear_sum(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
                bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """sum_s srcs[s] @ weights[s].T + bias, differentiable w.r.t. everything (1 or 2 sources)."""
-    return _LinearSum.apply(bias, *srcs, *weights)
+    """sum_s srcs[s] @ weights[s].T + bias, differentiable w.r.t. everything (1 or 2 sources).  Widths that are
+    not multiples of 4 (Cora's 1,433 input features, BASELINE configs[0]) are zero-padded -- sources by columns,
+    weights by columns and output rows -- so they run the same tensor-core kernels; the padded output columns are
+    sliced off again (no torch GEMM fallback anywhere)."""
+    n = weights[0].size(0)
+    srcs = [pad4(a) for a in srcs]
+    weights = [pad4(w, rows=True) for w in weights]
+    if bias is not None:
+        bias = pad4(bias)
+    out = _LinearSum.apply(bias, *srcs, *weights)
+    return out[:, :n] if out.size(1) != n else out
 
 
 def supported(*widths: int) -> bool:
-    """Layer widths the tensor-core kernels take (16-byte row segments)."""
-    return all(w % 4 == 0 and w > 0 for w in widths)
+    """Layer widths the tensor-core path takes: any positive width (odd ones are padded by `linear_sum`)."""
+    return all(w > 0 for w in widths)

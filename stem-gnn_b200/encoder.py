@@ -181,8 +181,8 @@ class InnerProductDecoder(nn.Module):
         if not self.proj_z:
             return z
         w = self.lin.weight
-        if z.is_cuda and z.dtype == torch.float32 and z.dim() == 2 and dense.supported(w.size(0), w.size(1)):
-            return dense.linear_sum([z], [w], self.lin.bias)          # K5/K6 instead of torch's fp32 SGEMM
+        if z.dim() == 2:
+            return dense.linear_sum([z.float()], [w], self.lin.bias)  # K5/K6 instead of torch's fp32 SGEMM
         return self.lin(z)
 
     def forward(self, z: Tensor, edge_index: Tensor, sigmoid: bool = True) -> Tensor:

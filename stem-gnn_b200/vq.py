@@ -286,10 +286,8 @@ class VectorQuantize(nn.Module):
         heads, cb = self.heads, self._codebook
         h = self._project(self.project_in, x).reshape(-1, heads * cb.dim)   # 'b n (h d)' rows, heads in columns
         if cb.cosine:                                              # l2norm per head (vq.py:891)
-            if h.is_cuda and h.dtype == torch.float32 and cb.dim % 4 == 0:
-                h = ops.l2norm_rows(h.contiguous().view(-1, cb.dim)).view(-1, heads * cb.dim)     # K11
-            else:
-                h = _l2norm(h.view(-1, heads, cb.dim)).view(-1, heads * cb.dim)
+            hv = ops.l2norm_rows(dense.pad4(h.float().contiguous().view(-1, cb.dim)))             # K11 (zeros keep the norm)
+            h = (hv[:, :cb.dim] if hv.size(1) != cb.dim else hv).reshape(-1, heads * cb.dim)
         commit_to_embed = self.learnable_codebook and not freeze_codebook
         q, ind, mse = cb(h, heads, self.training, freeze_codebook, commit_to_embed)
         loss = torch.zeros(1, device=x.device, requires_grad=self.training)    # vq.py:983
@@ -315,12 +313,10 @@ class VectorQuantize(nn.Module):
     def _project(lin, t):
         """project_in / project_out (model/vq.py:738-739,881,1041) on the tensor cores at fp32 accuracy
         (K5/K6): with the shipped 768 <-> 4 x 768 widths the two fp32 SGEMMs and their
-        gradients were 2/3 of a pretrain mini-batch.  Widths the kernels do not take stay on nn.Linear."""
+        gradients were 2/3 of a pretrain mini-batch.  Odd widths are zero-padded, weight matrices of more than 64
+        tiles of 256 x 256 are cut into output blocks for the gradient product (dense.py)."""
         if not isinstance(lin, nn.Linear):
             return lin(t)
         n, k = lin.weight.shape
-        tiles = -(-n // 256) * -(-k // 256)
-        if not (t.is_cuda and t.dtype == torch.float32 and dense.supported(n, k) and tiles <= 64):
-            return lin(t)
-        out = dense.linear_sum([t.reshape(-1, k)], [lin.weight], lin.bias)
+        out = dense.linear_sum([t.float().reshape(-1, k)], [lin.weight], lin.bias)
         return out.view(*t.shape[:-1], n)
