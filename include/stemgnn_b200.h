@@ -34,7 +34,8 @@ const char* stemgnn_last_error(void);
 /* Layout version of the argument structs below; a binding checks it at load time.
  * 2: out_ld / row_x_ld in stemgnn_aggregate_args; 3: stemgnn_bn_act_backward_apply and the loop-side
  * entry points (augmentations, sampler, l2norm, negative sampling); 4: hub_ws / hub_ws_bytes appended to
- * stemgnn_aggregate_args; 5: accumulate appended to stemgnn_aggregate_args. */
+ * stemgnn_aggregate_args; 5: accumulate appended to stemgnn_aggregate_args; 6: row_div appended to
+ * stemgnn_linear_args, row_add / row_add_ld appended to stemgnn_aggregate_args. */
 int stemgnn_abi_version(void);
 /* number of CUDA kernels this library has launched in this process (all entry points) */
 uint64_t stemgnn_launch_count(void);
@@ -114,6 +115,12 @@ typedef struct {
                               * as their halo blocks land).  Pass row_cnt / the backward relu mask (act with
                               * backward=1) only in the LAST call of such a chain: both apply to the finished sum. */
     int reserved;
+    const float* row_add;    /* ABI 6.  [n_rows, F] (row stride row_add_ld floats, 0 = feat) or NULL: added to the
+                              * FINISHED row -- after the count division / backward relu mask -- with one rounding:
+                              * out[r] = finish(sum) + row_add[r].  The backward of a SAGE layer adds the lin_r term
+                              * g @ W_r to the aggregated one (autograd's accumulation into x.grad, reference
+                              * model/encoder.py:84-88) here instead of in a pass of its own; may alias out. */
+    int64_t row_add_ld;
 } stemgnn_aggregate_args;
 
 int stemgnn_aggregate(const stemgnn_aggregate_args* args_host, stemgnn_stream_t stream);
@@ -204,6 +211,10 @@ typedef struct {
     int64_t ldo;
     int32_t accumulate;   /* 1: out += product (round-to-nearest add in the epilogue) instead of out = */
     int32_t reserved;
+    const float* row_div; /* ABI 6.  [m] or NULL: out[m, :] = (product + bias) / row_div[m] (IEEE division) -- the
+                           * `g_out / count[dst]` of MeanAggregation's backward (stemgnn_row_scale) applied where the
+                           * backward-data product g @ lin_l.weight is written, same bits, one pass over the matrix
+                           * less.  Not with accumulate = 1. */
 } stemgnn_linear_args;
 
 int stemgnn_linear_workspace(const stemgnn_linear_args* args_host, size_t* bytes_host);

@@ -8,7 +8,7 @@ import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libstemgnn_b200.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 _i64, _i32, _vp, _f32, _f64 = C.c_int64, C.c_int, C.c_void_p, C.c_float, C.c_double
 
@@ -19,7 +19,8 @@ class AggregateArgs(C.Structure):
                 ("row_cnt", _vp), ("gather_cnt", _vp), ("edge_feat", _vp), ("type_table", _vp),
                 ("edge_type", _vp), ("edge_weight", _vp), ("row_x", _vp), ("act", _i32),
                 ("backward", _i32), ("out", _vp), ("out_ld", _i64), ("row_x_ld", _i64),
-                ("hub_ws", _vp), ("hub_ws_bytes", C.c_size_t), ("accumulate", _i32), ("reserved", _i32)]
+                ("hub_ws", _vp), ("hub_ws_bytes", C.c_size_t), ("accumulate", _i32), ("reserved", _i32),
+                ("row_add", _vp), ("row_add_ld", _i64)]
 
 
 class VqAssignArgs(C.Structure):
@@ -40,7 +41,7 @@ class VqCodeStatsArgs(C.Structure):
 class LinearArgs(C.Structure):
     _fields_ = [("m", _i64), ("n", _i64), ("n_src", _i32), ("w_transposed", _i32), ("a", _vp * 2),
                 ("lda", _i64 * 2), ("k", _i64 * 2), ("w", _vp * 2), ("ldw", _i64 * 2), ("bias", _vp),
-                ("out", _vp), ("ldo", _i64), ("accumulate", _i32), ("reserved", _i32)]
+                ("out", _vp), ("ldo", _i64), ("accumulate", _i32), ("reserved", _i32), ("row_div", _vp)]
 
 
 class LinearWgradArgs(C.Structure):

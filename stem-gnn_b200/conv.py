@@ -11,8 +11,12 @@ from torch import Tensor
 
 from .graph import GraphStructure, structure_of
 from .partition import PartitionedGraph
-from . import dense
+import os
+
+from . import dense, sage
 from .ops import aggregate
+
+_SAGE_FUSED = os.environ.get("STEMGNN_SAGE_FUSED", "1") != "0"      # A/B switch: 0 = the composed form
 
 
 def _sparse_coo(adj_t):
@@ -103,16 +107,23 @@ class MySAGEConv(nn.Module):
             raise NotImplementedError("size must be None or (N, N)")
         x_r = x
         if self.project:
-            x = self.lin(x).relu()
+            x = dense.linear_sum([x], [self.lin.weight], self.lin.bias).relu()
         g = _graph(edge_index, x.size(0))
         if x.size(1) % 4:
             # a width like Cora's 1,433: pad the features (and per-edge features) once, so the aggregation runs the
             # 128-bit kernels and the padded columns -- zeros all the way -- meet zero weight columns in the GEMM
-            x, x_r = dense.pad4(x), dense.pad4(x_r)
+            x_r = dense.pad4(x_r)
+            x = dense.pad4(x) if self.project else x_r
             if isinstance(edge_attr, tuple):
                 edge_attr = (dense.pad4(edge_attr[0]), edge_attr[1])
             elif edge_attr is not None:
                 edge_attr = dense.pad4(edge_attr)
+        if (_SAGE_FUSED and not self.project and x_r is x and x.size(1) == self.lin_l.weight.size(1)
+                and sage.fusable(x, g, edge_attr, self.out_channels, self.root_weight)):
+            # the whole layer as one autograd node (sage.py): count division and gradient accumulation ride on
+            # kernel epilogues, a partitioned graph overlaps its halo exchange with the dense products
+            out = sage.sage_layer(x, g, self.aggr, self.lin_l, self.lin_r if self.root_weight else None)
+            return F.normalize(out, p=2.0, dim=-1) if self.normalize else out
         if getattr(g, "fused", False):
             # sparse adj_t: PyG's propagate takes message_and_aggregate = spmm(adj_t, x, reduce) and never calls
             # message(): no relu, xe unused (model/encoder.py:99-102)

@@ -1,5 +1,6 @@
 // common.cu -- error string, ABI version, device attribute cache.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 #include <mutex>
@@ -31,8 +32,12 @@ int sm_count() {
     });
     return n;
 }
+bool l2_pingpong() {
+    static const bool on = [] { const char* e = getenv("STEMGNN_L2_PINGPONG"); return e ? atoi(e) != 0 : true; }();
+    return on;
+}
 }  // namespace stemgnn
 
 extern "C" const char* stemgnn_last_error(void) { return stemgnn::g_err; }
-extern "C" int stemgnn_abi_version(void) { return 5; }
+extern "C" int stemgnn_abi_version(void) { return 6; }
 extern "C" uint64_t stemgnn_launch_count(void) { return stemgnn::launches(); }

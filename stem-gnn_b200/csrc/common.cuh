@@ -12,6 +12,10 @@ namespace stemgnn {
 void set_error(const char* fmt, ...);
 int sm_count();  // cached per process (device of first use)
 void count_launch();  // process-wide launch counter behind stemgnn_launch_count()
+// Sweep direction of kernels that read a matrix the previous kernel of the step has just written / read front to
+// back: walking it back to front finds its tail (up to the 126 MB L2's worth) still cached instead of fetching all
+// of it from HBM again.  STEMGNN_L2_PINGPONG=0 switches the reversed sweeps off (A/B); results do not depend on it.
+bool l2_pingpong();
 
 // every kernel launch of the library goes through this so the count is a measurement
 #define SG_LAUNCH(...) (stemgnn::count_launch(), __VA_ARGS__)

@@ -416,9 +416,18 @@ k0_bucket_kernel(const K0Params P, const int final_buf, const int src_mode, cons
     }
     __syncthreads();
     const int s0 = seg[0], s1 = seg[1];
-    // ---- phase A: edges per node
-    for (int i = s0 + threadIdx.x; i < s1; i += RS_THREADS)
-        atomicAdd(&ncount[load_key(k64, kin, i) & mask], 1);
+    // ---- phase A: edges per node (a chunk's 16 keys per thread are all in flight before the first atomic)
+    for (int c0 = s0; c0 < s1; c0 += K0_BUCKET_CHUNK) {
+        int kk[K0_BUCKET_ITEMS];
+#pragma unroll
+        for (int r = 0; r < K0_BUCKET_ITEMS; ++r) {
+            const int i = c0 + r * RS_THREADS + threadIdx.x;
+            kk[r] = i < s1 ? (load_key(k64, kin, i) & mask) : -1;
+        }
+#pragma unroll
+        for (int r = 0; r < K0_BUCKET_ITEMS; ++r)
+            if (kk[r] >= 0) atomicAdd(&ncount[kk[r]], 1);
+    }
     __syncthreads();
     {
         // exclusive scan of the 512 counts (2 per thread), rowptr / cnt of this bucket's nodes

@@ -54,6 +54,8 @@ struct AggParams {
     int hub_cap;                // slots of the row list: big hubs from the front, small ones from the back
     int accumulate;             // row sums start from out[r] instead of 0 (ABI 5)
     int hints;                  // L2 cache-policy hints on the streaming accesses (A/B switch)
+    const float* row_add;       // added to the FINISHED row (after count division / relu mask), or NULL (ABI 6)
+    int64_t row_add_ld;
 };
 
 // Rows with at least this many edges ("hubs": ogbn-arxiv's largest in-degree is 13,155, ogbn-products'
@@ -193,6 +195,12 @@ aggregate_kernel(const AggParams a) {
                 if (!BWD && a.row_cnt) r = __fdiv_rn(r, rc);
                 if (BWD && MODE == MODE_PLAIN && RELU) r = rx[c].v[k] > 0.f ? r : 0.f;
                 acc[c].v[k] = r;
+            }
+            if (a.row_add) {
+                Vec<VEC> ad;
+                ad.load_plain(a.row_add + row * a.row_add_ld + foff[c]);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) acc[c].v[k] = __fadd_rn(acc[c].v[k], ad.v[k]);
             }
             acc[c].store(a.out + row * a.out_ld + foff[c]);
         }
@@ -336,6 +344,12 @@ aggregate_stream_kernel(const AggParams a) {
                 if (a.row_cnt) v = __fdiv_rn(v, rc);
                 if (MASK_END) v = rx[c].v[k] > 0.f ? v : 0.f;
                 acc[c].v[k] = v;
+            }
+            if (a.row_add) {
+                Vec<4> ad;
+                ad.load_plain(a.row_add + row * a.row_add_ld + foff[c]);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) acc[c].v[k] = __fadd_rn(acc[c].v[k], ad.v[k]);
             }
             st_stream_f4(a.out + row * a.out_ld + foff[c], acc[c].v, pol, hints);
         }
@@ -516,6 +530,7 @@ aggregate_hub_kernel(const AggParams a) {
             float r = acc;
             if (!BWD && a.row_cnt) r = __fdiv_rn(r, __ldg(a.row_cnt + row));
             if (BWD && MODE == MODE_PLAIN && RELU) r = __ldg(a.row_x + row * a.row_x_ld + f0 + c) > 0.f ? r : 0.f;
+            if (a.row_add) r = __fadd_rn(r, a.row_add[row * a.row_add_ld + f0 + c]);
             a.out[row * a.out_ld + f0 + c] = r;
         }
     }
@@ -666,6 +681,7 @@ aggregate_hub_ring_kernel(const AggParams a) {
             float r = acc;
             if (!BWD && a.row_cnt) r = __fdiv_rn(r, __ldg(a.row_cnt + row));
             if (BWD && RELU) r = __ldg(a.row_x + row * a.row_x_ld + f0 + c) > 0.f ? r : 0.f;
+            if (a.row_add) r = __fadd_rn(r, a.row_add[row * a.row_add_ld + f0 + c]);
             a.out[row * a.out_ld + f0 + c] = r;
         }
     }
@@ -840,8 +856,8 @@ extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream
     SG_CHECK_ARG(p.out_ld >= a->feat && p.row_x_ld >= a->feat, "out_ld / row_x_ld smaller than feat");
 
     bool vec4 = (a->feat % 4 == 0) && aligned16(a->gathered) && aligned16(a->out) &&
-                aligned16(a->edge_feat) && aligned16(a->type_table) && aligned16(a->row_x) &&
-                p.out_ld % 4 == 0 && p.row_x_ld % 4 == 0;
+                aligned16(a->edge_feat) && aligned16(a->type_table) && aligned16(a->row_x) && aligned16(a->row_add) &&
+                p.out_ld % 4 == 0 && p.row_x_ld % 4 == 0 && p.row_add_ld % 4 == 0;
     // hub rows (>= HUB_ROW_EDGES edges) go through the work list when the caller lends one; without it,
     // or on the unaligned scalar path, every row stays in the row-per-group kernel
     p.hub = nullptr; p.hub_cap = 0;
@@ -851,6 +867,9 @@ extern "C" int stemgnn_aggregate(const stemgnn_aggregate_args* a, stemgnn_stream
         p.hub_cap = (int)(a->num_edges / HUB_ROW_EDGES + 1);
     }
     p.accumulate = a->accumulate != 0;
+    p.row_add = a->row_add;
+    p.row_add_ld = a->row_add_ld ? a->row_add_ld : a->feat;
+    SG_CHECK_ARG(!a->row_add || p.row_add_ld >= a->feat, "row_add_ld smaller than feat");
     static const bool hints_on = [] { const char* e = getenv("STEMGNN_AGG_HINTS"); return e ? atoi(e) != 0 : true; }();
     p.hints = hints_on;
     const int mode = has_w ? MODE_W : (has_xe ? MODE_XE : MODE_PLAIN);

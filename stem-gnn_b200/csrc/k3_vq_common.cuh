@@ -31,7 +31,7 @@ __global__ void vq_scan_kernel(VqView q, const float* x2, const float* e2, const
                                const int32_t* row_count, int32_t* best_out);
 __global__ void vq_gather_kernel(VqView q, int32_t* best, const int32_t* cand, const float* e2,
                                  double* partials, int32_t* open_list, int32_t* open_count,
-                                 unsigned long long* stats);
+                                 unsigned long long* stats, int rev);
 __global__ void vq_rescan_kernel(VqView q, int32_t* best, const float* e2, double* partials, int nblk,
                                  const int32_t* open_list, const int32_t* open_count,
                                  unsigned long long* stats);

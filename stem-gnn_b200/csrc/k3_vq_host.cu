@@ -114,7 +114,7 @@ extern "C" int stemgnn_vq_assign(const stemgnn_vq_assign_args* a, void* workspac
     dim3 ggrid((unsigned)((p.nblk + 7) / 8), (unsigned)q.heads);      // one warp per entry of VQ_GATHER_ROWS rows
     SG_LAUNCH(vq_gather_kernel<<<ggrid, 256, 0, stream>>>(
         q, best, cand, e2, a->sq_err ? partials : nullptr, open_list, open_count,
-        reinterpret_cast<unsigned long long*>(a->stats)));
+        reinterpret_cast<unsigned long long*>(a->stats), l2_pingpong() ? 1 : 0));
     if (p.path == 2)      // rows the tensor-core search left to the exact scan (normally a handful)
         SG_LAUNCH(vq_rescan_kernel<<<(unsigned)sm_count(), 1024, 0, stream>>>(
             q, best, e2, a->sq_err ? partials : nullptr, (int)p.nblk, open_list, open_count,

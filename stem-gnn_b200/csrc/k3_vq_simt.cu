@@ -305,12 +305,14 @@ __global__ void __launch_bounds__(256, 3)
 vq_gather_kernel(VqView q, int32_t* __restrict__ best, const int32_t* __restrict__ cand,
                  const float* __restrict__ e2, double* __restrict__ partials,
                  int32_t* __restrict__ open_list, int32_t* __restrict__ open_count,
-                 unsigned long long* __restrict__ stats) {
+                 unsigned long long* __restrict__ stats, int rev) {
     constexpr int GR = VQ_GATHER_ROWS;
     const int w = threadIdx.x >> 5, lane = lane_id();
     const int64_t h = blockIdx.y;
     const int64_t nent = (q.rows + GR - 1) / GR;
-    const int64_t ent = (int64_t)blockIdx.x * 8 + w;
+    // rev: the first CTAs take the last rows -- the search kernel before this one swept x front to back, so the tail
+    // of x is what the L2 still holds (l2_pingpong); entries keep their index, the result does not depend on it
+    const int64_t ent = (int64_t)(rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * 8 + w;
     if (ent >= nent) return;
     const int64_t m0 = ent * GR;
     const int64_t eh = q.embed_heads == 1 ? 0 : h;

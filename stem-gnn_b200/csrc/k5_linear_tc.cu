@@ -69,6 +69,7 @@ struct LinParams {
     float* out;
     int64_t ldo;
     int accumulate;         // out += instead of out =
+    const float* row_div;   // out[m, :] = (product + bias) / row_div[m] (IEEE division), or NULL.  ABI 6
 };
 
 // byte offset of the 16 B unit j of row r in a 256-row SWIZZLE_64B image
@@ -295,7 +296,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lin_tc_kernel(const LinParams 
                     float* op = p.out + row_base * p.ldo + col;
                     const int nrow = (int)(p.m - row_base < 32 ? p.m - row_base : 32);
                     if (col_ok) {
-                        if (!p.accumulate) {
+                        if (p.row_div) {
+                            // MeanAggregation's backward wants g_agg[m, :] / max(deg(m), 1): the quotient of the value
+                            // this epilogue holds, so the K2a pass over the matrix is saved (same bits: one
+                            // round-to-nearest sum, one IEEE division)
+#pragma unroll 4
+                            for (int i = 0; i < nrow; ++i)
+                                op[(int64_t)i * p.ldo] = __fdiv_rn(st[i * 33 + lane] + b, __ldg(p.row_div + row_base + i));
+                        } else if (!p.accumulate) {
 #pragma unroll 4
                             for (int i = 0; i < nrow; ++i) op[(int64_t)i * p.ldo] = st[i * 33 + lane] + b;
                         } else {
@@ -371,6 +379,7 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
     const size_t need = (size_t)n_tiles * kct * lin::W_STAGE_BYTES + 256;
     SG_CHECK_ARG(workspace && workspace_bytes >= need, "workspace too small (stemgnn_linear_workspace)");
     SG_CHECK_ARG(a->out && a->ldo >= a->n, "out is NULL or ldo < n");
+    SG_CHECK_ARG(!(a->row_div && a->accumulate), "row_div divides the finished product: not with accumulate = 1");
     for (int s = 0; s < a->n_src; ++s) {
         SG_CHECK_ARG(a->a[s] && a->w[s], "a/w is NULL");
         SG_CHECK_ARG(lin_aligned16(a->a[s]), "a must be 16-byte aligned");
@@ -392,6 +401,7 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
 
     p.kct = kct; p.m = a->m; p.n = (int)a->n; p.n_tiles = n_tiles; p.wimg = img; p.bias = a->bias;
     p.out = a->out; p.ldo = a->ldo; p.accumulate = a->accumulate != 0;
+    p.row_div = a->row_div;
     // Tile shape (measured, scripts/lin_bench.py, M = 169,343): 128-row tiles with the double-buffered
     // accumulator win 10-17 % while the split weight image is small (N=256, K<=512: 114 / 196 us
     // against 136 / 218 us); once it reaches a few MB (N=512, K=1024: 4 MB) streaming it twice as

@@ -44,10 +44,13 @@ template <int MODE>
 __global__ void __launch_bounds__(256)
 col_reduce_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ gy, int64_t ldg,
                   int64_t rows, int feat, int64_t rows_per_block, Cols cc, int relu, float p, float inv_keep,
-                  const uint64_t* __restrict__ seed_p, float* __restrict__ part) {
+                  const uint64_t* __restrict__ seed_p, float* __restrict__ part, int rev) {
     __shared__ float4 sh[2][4][64];
     const int cu = threadIdx.x & 63, rl = threadIdx.x >> 6;
-    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+    // rev: the CTAs that start first take the LAST row ranges -- the tail of the matrix the previous kernel wrote
+    // front to back is still in L2 (l2_pingpong); the partial of a range keeps its place, so the sums do not change
+    const int bid = rev ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;
+    const int64_t r0 = (int64_t)bid * rows_per_block;
     const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
     const uint64_t seed = (MODE == 1 && p > 0.f) ? *seed_p : 0;
     const int f4 = feat >> 2;
@@ -100,7 +103,7 @@ col_reduce_kernel(const float* __restrict__ x, int64_t ldx, const float* __restr
         __syncthreads();
         if (rl < 2 && c < feat) {       // row lane 0 finishes the first sum, lane 1 the second
             const float4 s0 = sh[rl][0][cu], s1 = sh[rl][1][cu], s2 = sh[rl][2][cu], s3 = sh[rl][3][cu];
-            float* o = part + ((int64_t)blockIdx.x * 2 + rl) * feat + c;
+            float* o = part + ((int64_t)bid * 2 + rl) * feat + c;
             o[0] = (s0.x + s1.x) + (s2.x + s3.x); o[1] = (s0.y + s1.y) + (s2.y + s3.y);
             o[2] = (s0.z + s1.z) + (s2.z + s3.z); o[3] = (s0.w + s1.w) + (s2.w + s3.w);
         }
@@ -234,7 +237,7 @@ extern "C" int stemgnn_bn_stats(int64_t rows, int64_t feat, const float* x, int6
     float* part = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
     bn::Cols none{nullptr, nullptr, nullptr, nullptr};
     SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
-                                                                      none, 0, 0.f, 1.f, nullptr, part));
+                                                                      none, 0, 0.f, 1.f, nullptr, part, l2_pingpong() ? 1 : 0));
     SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
@@ -277,7 +280,7 @@ extern "C" int stemgnn_bn_act_backward(int64_t rows, int64_t feat, const float* 
     bn::Cols cc{mean, invstd, gamma, beta};
     const float inv_keep = 1.f / (1.f - p);
     SG_LAUNCH(bn::col_reduce_kernel<1><<<pl.blocks, 256, 0, stream>>>(x, ldx, gy, ldg, rows, (int)feat, pl.rows_per_block, cc,
-                                                                      relu, p, inv_keep, seed, part));
+                                                                      relu, p, inv_keep, seed, part, l2_pingpong() ? 1 : 0));
     SG_LAUNCH(bn::col_final_kernel<1><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, sum_g, sum_gx));
     if (gx) {
         SG_CHECK_ARG(ldgx >= feat && ldgx % 4 == 0, "ldgx");
@@ -358,7 +361,7 @@ extern "C" int stemgnn_bn_stats_static(int64_t rows, int64_t feat, const float* 
     // nothing in the scratch has to start at zero: col_reduce writes every partial col_final reads
     bn::Cols none{nullptr, nullptr, nullptr, nullptr};
     SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
-                                                                      none, 0, 0.f, 1.f, nullptr, part));
+                                                                      none, 0, 0.f, 1.f, nullptr, part, l2_pingpong() ? 1 : 0));
     SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;

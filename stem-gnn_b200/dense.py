@@ -31,32 +31,40 @@ def _rowmajor(t):
 
 K_SLAB = 768       # columns accumulated in TMEM per call once a product is cut into slabs (= K_SINGLE: same bound)
 K_SINGLE = 768     # widest product done in one call (measured max error 7.5e-9 * K of the output scale)
+# Beyond 1,536 columns in total (Cora's 1,436 + 1,436) slabs of 768 leave 1.03e-5 (measured, C1): the truncation of
+# a slab's accumulator is relative to the slab's own partial sum, so the total goes like sqrt(slab) -- 256 there.
+K_SLAB_WIDE, K_WIDE = 256, 1536
 
 
 def linear_raw(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
                bias: Optional[torch.Tensor] = None, w_transposed: bool = False,
-               out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+               out: Optional[torch.Tensor] = None, accumulate: bool = False,
+               row_div: Optional[torch.Tensor] = None) -> torch.Tensor:
     """out[m, n] = sum_s srcs[s][m, :] . weights[s][n, :] (+ bias[n]); with w_transposed the
     weights are [k, n] and the product is srcs[s] @ weights[s].  One stemgnn_linear call while
     sum(k) <= K_SINGLE; wider products are cut into column slabs of K_SLAB whose partial products are
     added round-to-nearest by the epilogue (accumulate), keeping the 1e-5 bound."""
-    if sum(int(a.size(1)) for a in srcs) > K_SINGLE:
+    ktot_all = sum(int(a.size(1)) for a in srcs)
+    if ktot_all > K_SINGLE:
+        slab = K_SLAB_WIDE if ktot_all > K_WIDE else K_SLAB
         pieces = []
         for a, w in zip(srcs, weights):
-            for lo in range(0, a.size(1), K_SLAB):
-                hi = min(a.size(1), lo + K_SLAB)
+            for lo in range(0, a.size(1), slab):
+                hi = min(a.size(1), lo + slab)
                 pieces.append((a[:, lo:hi], w[lo:hi] if w_transposed else w[:, lo:hi]))
         pieces.sort(key=lambda pc: -pc[0].size(1))   # full slabs first, the remainders pair up
         calls, cur, cur_k = [], [], 0
-        for pc in pieces:                       # at most two sources and K_SLAB columns per call
+        for pc in pieces:                       # at most two sources and `slab` columns per call
             k = pc[0].size(1)
-            if cur and (len(cur) == 2 or cur_k + k > K_SLAB):
+            if cur and (len(cur) == 2 or cur_k + k > slab):
                 calls.append(cur); cur, cur_k = [], 0
             cur.append(pc); cur_k += k
         calls.append(cur)
         for i, grp in enumerate(calls):
             out = linear_raw([g[0] for g in grp], [g[1] for g in grp], bias if i == 0 else None,
                              w_transposed, out, accumulate or i > 0)
+        if row_div is not None:                 # the division belongs to the finished sum of the slabs
+            out = out / row_div.view(-1, 1)
         return out
     ns = len(srcs)
     if ns not in (1, 2) or len(weights) != ns:
@@ -82,6 +90,10 @@ def linear_raw(srcs: Sequence[torch.Tensor], weights: Sequence[torch.Tensor],
     a.bias = _lib.ptr(_check(bias, "bias").contiguous()) if bias is not None else None
     a.out, a.ldo = out.data_ptr(), out.stride(0)
     a.accumulate = int(accumulate)
+    if row_div is not None:
+        if row_div.numel() != m or row_div.dtype != torch.float32 or not row_div.is_contiguous():
+            raise ValueError("row_div must be a contiguous float32 vector with one entry per row")
+        a.row_div = row_div.data_ptr()
     L = _lib.lib()
     need = C.c_size_t(0)
     _lib.check(L.stemgnn_linear_workspace(C.byref(a), C.byref(need)))

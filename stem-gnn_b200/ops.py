@@ -26,7 +26,8 @@ def _f32c(t, name):
 
 def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_cnt=None,
                     edge_feat=None, type_table=None, edge_type=None, edge_weight=None, row_x=None,
-                    act=ACT_NONE, backward=False, out_cols=None, gathered_rows=None, accumulate=False):
+                    act=ACT_NONE, backward=False, out_cols=None, gathered_rows=None, accumulate=False,
+                    row_add=None):
     """One stemgnn_aggregate call.  `out_cols=(lo, hi)` writes columns [lo, hi) of the wider `out`
     (and reads the same columns of `row_x`): the feature-sliced halo pipeline."""
     per_edge = edge_feat is not None or edge_type is not None or edge_weight is not None
@@ -38,6 +39,10 @@ def _aggregate_call(csr, n_gather_rows, gathered, out, *, row_cnt=None, gather_c
         edge_feat=_lib.ptr(edge_feat), type_table=_lib.ptr(type_table),
         edge_type=_lib.ptr(edge_type), edge_weight=_lib.ptr(edge_weight), row_x=_lib.ptr(row_x),
         act=act, backward=int(backward), out=_lib.ptr(out), accumulate=int(accumulate))
+    if row_add is not None:                      # out[r] = finish(sum) + row_add[r]; may alias out
+        a.row_add, a.row_add_ld = _lib.ptr(row_add), row_add.stride(0)
+        if out_cols is not None:
+            a.row_add = row_add.data_ptr() + 4 * out_cols[0]
     hub = getattr(csr, "hub", None)
     if hub is not None and os.environ.get("STEMGNN_AGG_NO_HUB") != "1":      # A/B switch for scripts/agg_bench.py
         a.hub_ws, a.hub_ws_bytes = hub.data_ptr(), hub.numel()
@@ -110,6 +115,52 @@ class _Aggregate(torch.autograd.Function):
         return g_x, None, None, None, None, None, None, None, None
 
 
+class HaloExchange:
+    """One halo exchange of a partitioned graph, cut in two so that a caller can put other work between the
+    start of the transfers and the aggregation that consumes them (sage.py: the dense products of the layer
+    that do not need the aggregate).  Constructing it issues every transfer on the collective's stream;
+    `aggregate` waits (stream-ordered) and runs K1 / K2 on the owned rows."""
+
+    def __init__(self, pg, local, backward):
+        self.pg, self.backward, self.local = pg, backward, local
+        if pg.halo_mode == "blocks":
+            self.blocks = pg.exchange_blocks(local)
+            self.first = next(self.blocks)                 # every transfer is on the wire once the generator yields
+        else:
+            self.slices = pg.feature_slices(local.size(1))
+            if pg.world == 1 and pg._gather is None:
+                self.pending = [lambda: local]
+                self.slices = [(0, local.size(1))]
+            else:
+                self.pending = [pg.gather_cols_async(local, lo, hi) for lo, hi in self.slices]
+
+    def aggregate(self, out, row_cnt, row_x, act, row_add=None):
+        pg, backward = self.pg, self.backward
+        if pg.halo_mode == "blocks":
+            # overlapped exchange: the own block first, every other owner block as it lands, accumulated into
+            # `out`; the count division / backward relu mask / row_add belong to the finished sum: the last call
+            csrs = pg.block_csrs(backward)
+            last = pg.world - 1
+            items = [self.first]
+            i = 0
+            while True:
+                b, blk = items.pop() if items else next(self.blocks)
+                fin = i == last
+                _aggregate_call(csrs[b], blk.size(0), blk, out, row_cnt=row_cnt if fin else None,
+                                row_x=row_x if (fin and backward) else None,
+                                act=act if (fin or not backward) else ACT_NONE, backward=backward, accumulate=i > 0,
+                                row_add=row_add if fin else None)
+                if fin:
+                    return
+                i += 1
+        csr = pg.bwd_csr() if backward else pg.fwd_csr()
+        whole = len(self.slices) == 1
+        for (lo, hi), fin in zip(self.slices, self.pending):
+            full = fin()                                                           # wait for this slice only
+            _aggregate_call(csr, full.size(0), full, out, row_cnt=row_cnt, row_x=row_x, act=act, backward=backward,
+                            out_cols=None if whole else (lo, hi), row_add=row_add)
+
+
 class _PartAggregate(torch.autograd.Function):
     """The same aggregation on a 1-D destination-partitioned graph: x holds this rank's rows;
     the forward all-gathers the row blocks (halo exchange) and runs K1 on the owned destination
@@ -120,28 +171,7 @@ class _PartAggregate(torch.autograd.Function):
 
     @staticmethod
     def _run(pg, csr, local, out, row_cnt, row_x, act, backward):
-        if pg.halo_mode == "blocks":
-            # overlapped exchange: the own block first, every other owner block as it lands, accumulated into
-            # `out`; the count division / backward relu mask belong to the finished sum, i.e. to the last call
-            csrs = pg.block_csrs(backward)
-            last = pg.world - 1
-            for i, (b, blk) in enumerate(pg.exchange_blocks(local)):
-                fin = i == last
-                _aggregate_call(csrs[b], blk.size(0), blk, out, row_cnt=row_cnt if fin else None,
-                                row_x=row_x if (fin and backward) else None,
-                                act=act if (fin or not backward) else ACT_NONE, backward=backward, accumulate=i > 0)
-            return
-        F = local.size(1)
-        slices = pg.feature_slices(F)
-        if len(slices) == 1:
-            full = pg.gather_rows(local)
-            _aggregate_call(csr, full.size(0), full, out, row_cnt=row_cnt, row_x=row_x, act=act, backward=backward)
-            return
-        pending = [pg.gather_cols_async(local, lo, hi) for lo, hi in slices]      # all on the wire
-        for (lo, hi), fin in zip(slices, pending):
-            full = fin()                                                           # wait for this slice only
-            _aggregate_call(csr, full.size(0), full, out, row_cnt=row_cnt, row_x=row_x, act=act,
-                            backward=backward, out_cols=(lo, hi))
+        HaloExchange(pg, local, backward).aggregate(out, row_cnt, row_x, act)
 
     @staticmethod
     def forward(ctx, x, pg, reduce, act):

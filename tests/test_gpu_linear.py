@@ -201,3 +201,23 @@ def test_wide_products_are_slabbed_and_hold_the_bound(ks):
     wt = [w.t().contiguous() for w in ws]
     out_t = S.linear_raw(srcs, wt, None, w_transposed=True)
     assert torch.equal(out_t, out)
+
+
+def test_row_div_epilogue_equals_a_separate_ieee_division():
+    """stemgnn_linear(row_div): out[m, :] = (A @ W) / d[m] in the epilogue (ABI 6) -- the same bits as the product
+    followed by stemgnn_row_scale (MeanAggregation's g_out / count of the backward), with and without transposed W."""
+    import stemgnn_b200 as S
+    from stemgnn_b200 import dense, ops
+    g = torch.Generator().manual_seed(4)
+    m, n, k = 5003, 256, 128
+    a = torch.randn(m, k, generator=g).cuda()
+    w = torch.randn(n, k, generator=g).cuda()
+    d = torch.randint(1, 40, (m,), generator=g).float().cuda()
+    plain = dense.linear_raw([a], [w], None)
+    fused = dense.linear_raw([a], [w], None, row_div=d)
+    assert torch.equal(fused, ops._row_scale(plain, d))
+    gt = torch.randn(m, n, generator=g).cuda()
+    assert torch.equal(dense.linear_raw([gt], [w], None, w_transposed=True, row_div=d),
+                       ops._row_scale(dense.linear_raw([gt], [w], None, w_transposed=True), d))
+    with pytest.raises(S.StemGnnError):
+        dense.linear_raw([a], [w], None, out=plain.clone(), accumulate=True, row_div=d)
