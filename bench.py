@@ -620,11 +620,12 @@ def partition_modes(world):
     if world == 1:
         return [("single GPU (no exchange)", "gather", None, "p2p")]
     modes = [("all-gather, fp32 wire (bit-identical to one GPU)", "gather", None, "p2p"),
-             ("owner blocks overlapped, pairwise send/recv, fp32 wire", "blocks", None, "p2p"),
-             ("owner blocks overlapped, pairwise send/recv, bf16 wire", "blocks", "bf16", "p2p")]
-    if os.environ.get("STEMGNN_HALO_BCAST", "0") == "1":
-        modes += [("owner blocks overlapped, broadcasts, fp32 wire", "blocks", None, "bcast"),
-                  ("owner blocks overlapped, broadcasts, bf16 wire", "blocks", "bf16", "bcast")]
+             ("all-gather pipelined over 2 row chunks, fp32 wire", "chunks", None, "2"),
+             ("all-gather pipelined over 4 row chunks, fp32 wire", "chunks", None, "4"),
+             ("all-gather pipelined over 4 row chunks, bf16 wire", "chunks", "bf16", "4")]
+    if os.environ.get("STEMGNN_HALO_BLOCKS", "0") == "1":     # owner-block modes: P-fold cut of the row sums (P <= 4)
+        modes += [("owner blocks overlapped, pairwise send/recv, fp32 wire", "blocks", None, "p2p"),
+                  ("owner blocks overlapped, broadcasts, fp32 wire", "blocks", None, "bcast")]
     return modes
 
 
@@ -691,7 +692,9 @@ def measure_partition(w, dev, rank, world, steps, warmup, want_e2e=False):
     out_modes, extra = [], {}
     for label, mode, wire, transport in partition_modes(world):
         pg = S.PartitionedGraph(None, n, rank=rank, world=world, pre_split=split, halo_mode=mode,
-                                halo_transport=transport, halo_dtype=torch.bfloat16 if wire == "bf16" else None)
+                                halo_transport=transport if mode == "blocks" else "p2p",
+                                halo_chunks=int(transport) if mode == "chunks" else 4,
+                                halo_dtype=torch.bfloat16 if wire == "bf16" else None)
         step = make_step(pg)
         for _ in range(max(warmup, 3)):
             step(x_d)
@@ -748,7 +751,7 @@ def measure_partition(w, dev, rank, world, steps, warmup, want_e2e=False):
                halo_wait_ms=best["halo_wait_ms"], aggregate_ms=best["aggregate_ms"], dense_ms=best["dense_ms"],
                wire=best["wire"], halo_bytes_received_per_rank_per_step=best["halo_bytes_received_per_rank_per_step"],
                modes=out_modes,
-               parity="all-gather mode: bit-identical to one GPU; owner-block modes: same terms summed block by block, "
+               parity="all-gather mode: bit-identical to one GPU; row-chunk / owner-block modes: same terms summed group by group, "
                       "<= 1e-5 of the output scale on the fp32 wire (tests/test_gpu_partition.py, "
                       "scripts/check_partition_multi.py); bf16 wire: 2^-9 relative per gathered feature, opt-in",
                l2="working set (N x F fp32 >= 980 MB) exceeds the 126 MB L2")

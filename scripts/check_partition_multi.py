@@ -66,6 +66,9 @@ def main():
               f"fwd+bwd {ms.item():.3f} ms ({slices} feature slices)  unsliced {ms1:.3f} ms  "
               f"bf16 wire {msb:.3f} ms (max err fwd {errb:.1e} bwd {errg:.1e})  "
               f"{2 * e / ms.item() / 1e6:.1f} Medges/s (both directions)", flush=True)
+    if os.environ.get("STEMGNN_CHECK_GATHER_ONLY") == "1":
+        dist.destroy_process_group()
+        sys.exit(0 if t.item() else 1)
     # the overlapped exchange (halo_mode="blocks"): owner blocks aggregated as they land, 1e-5 of the output scale
     ok_blocks = True
     for transport in ("p2p", "bcast"):
@@ -81,6 +84,20 @@ def main():
                 ok_blocks = False
             if rank == 0:
                 print(f"  blocks/{transport}/{'bf16' if wire is not None else 'f32'}: fwd+bwd {mso:.3f} ms  "
+                      f"max err fwd {float(err[0]):.1e} bwd {float(err[1]):.1e}", flush=True)
+    for chunks in (2, 4, 8):
+        for wire in (None, torch.bfloat16):
+            pgo = S.PartitionedGraph(ei, n, halo_mode="chunks", halo_chunks=chunks, halo_dtype=wire)
+            xl.grad = None
+            oo = S.aggregate(xl, pgo, reduce="mean", act="relu"); oo.backward(go[lo:hi])
+            ef = ((oo.detach() - ref.detach()[lo:hi]).abs().max() / ref.detach().abs().max()).item()
+            eg = ((xl.grad - xs.grad[lo:hi]).abs().max() / xs.grad.abs().max()).item()
+            err = torch.tensor([ef, eg], device="cuda"); dist.all_reduce(err, op=dist.ReduceOp.MAX)
+            mso = timed(pgo)
+            if wire is None and float(err.max()) > 1e-5:
+                ok_blocks = False
+            if rank == 0:
+                print(f"  chunks/{chunks}/{'bf16' if wire is not None else 'f32'}: fwd+bwd {mso:.3f} ms  "
                       f"max err fwd {float(err[0]):.1e} bwd {float(err[1]):.1e}", flush=True)
     dist.destroy_process_group()
     sys.exit(0 if (t.item() and ok_blocks) else 1)

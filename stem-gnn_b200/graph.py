@@ -117,7 +117,10 @@ _CACHE_MAX = 8
 def structure_of(edge_index, num_nodes):
     """Cached GraphStructure for this edge_index tensor.  The key is (storage pointer, shape,
     in-place version counter, N); entries die with the tensor.  An Encoder calls every layer
-    with the same edge_index, so the two sorts run once per step."""
+    with the same edge_index, so the two sorts run once per step.
+    The version counter sees torch's in-place ops only: a caller that refills the SAME buffer through
+    `edge_index.data`, a custom kernel or a CUDA-graph replay must call `clear_structure_cache()` (what
+    bench.py's step does) or pass a GraphStructure it built itself -- otherwise the stale CSR is reused."""
     key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, int(num_nodes),
            edge_index.device.index)
     hit = _CACHE.get(key)

@@ -159,6 +159,9 @@ def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool, syn
     backward's column sums are taken over all ranks' rows, like full-batch BatchNorm on one GPU."""
     use_batch = bn.training or bn.running_mean is None
     f = z.size(1)
+    if use_batch and bn.training and (sync.batch_rows if sync is not None else z.size(0)) <= 1:
+        # what nn.BatchNorm1d (the reference's module, model/encoder.py:313) does for a one-row batch
+        raise ValueError(f"Expected more than 1 value per channel when training, got input size {tuple(z.shape)}")
     if use_batch:
         with torch.no_grad():
             mean, var = synced_batch_stats(z.detach(), sync) if sync is not None else batch_stats(z.detach())

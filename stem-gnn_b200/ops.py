@@ -123,8 +123,8 @@ class HaloExchange:
 
     def __init__(self, pg, local, backward):
         self.pg, self.backward, self.local = pg, backward, local
-        if pg.halo_mode == "blocks":
-            self.blocks = pg.exchange_blocks(local)
+        if pg.halo_mode in ("blocks", "chunks"):
+            self.blocks = pg.exchange_groups(local)
             self.first = next(self.blocks)                 # every transfer is on the wire once the generator yields
         else:
             self.slices = pg.feature_slices(local.size(1))
@@ -136,11 +136,12 @@ class HaloExchange:
 
     def aggregate(self, out, row_cnt, row_x, act, row_add=None):
         pg, backward = self.pg, self.backward
-        if pg.halo_mode == "blocks":
-            # overlapped exchange: the own block first, every other owner block as it lands, accumulated into
-            # `out`; the count division / backward relu mask / row_add belong to the finished sum: the last call
-            csrs = pg.block_csrs(backward)
-            last = pg.world - 1
+        if pg.halo_mode in ("blocks", "chunks"):
+            # overlapped exchange: the own block first, every other owner block (or: row chunk after row chunk) as
+            # it lands, accumulated into `out`; the count division / backward relu mask / row_add belong to the
+            # finished sum: the last call
+            csrs = pg.group_csrs(backward)
+            last = pg.n_groups - 1
             items = [self.first]
             i = 0
             while True:

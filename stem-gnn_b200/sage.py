@@ -44,7 +44,7 @@ class _SageLayer(torch.autograd.Function):
                 raise ValueError(f"x must hold this rank's {graph.num_nodes} rows")
             fwd = graph.fwd_csr()
             ex = ops.HaloExchange(graph, x, False)
-            if graph.halo_mode == "blocks" and graph.world > 1 and w_r is not None:
+            if graph.halo_mode != "gather" and graph.world > 1 and w_r is not None:
                 out = dense.linear_raw([x], [w_r], bias)            # while the blocks of x are on the wire
             ex.aggregate(agg, fwd.cnt if mean else None, None, ops.ACT_RELU)
         else:
@@ -91,7 +91,7 @@ class _SageLayer(torch.autograd.Function):
             g_x = dense.linear_raw([g], [w_r], None, w_transposed=True) if ctx.has_r else torch.empty_like(x)
             add = g_x if ctx.has_r else None
             if part:
-                if graph.halo_mode == "blocks" and add is not None:
+                if graph.halo_mode != "gather" and add is not None:
                     g_x = torch.empty_like(x)       # the chained block calls build their sum in `out`: no aliasing
                 ex.aggregate(g_x, None, x, ops.ACT_RELU, row_add=add)
             else:

@@ -148,3 +148,14 @@ def test_batch_split_over_ranks_equals_full_batch(world, relu):
         acc_g += bn2.bias.grad; acc_gx += bn2.weight.grad     # parameter gradients are this rank's share
     torch.testing.assert_close(acc_g, sum_g, rtol=1e-4, atol=1e-4)
     torch.testing.assert_close(acc_gx, sum_gx, rtol=1e-4, atol=1e-4)
+
+
+def test_one_row_batch_in_training_raises_like_torch():
+    bn = nn.BatchNorm1d(8).to(DEV).train()
+    x = torch.randn(1, 8, device=DEV)
+    with pytest.raises(ValueError, match="more than 1 value per channel"):
+        bn(x)                                                  # torch's own behaviour
+    with pytest.raises(ValueError, match="more than 1 value per channel"):
+        S.bn_act_drop(x, bn, relu=True, p=0.0, training=True)
+    bn.eval()
+    S.bn_act_drop(x, bn, relu=True, p=0.0, training=False)    # running statistics: fine

@@ -146,7 +146,7 @@ class _Blocks:
 
 
 @pytest.mark.parametrize("world", [2, 3, 8])
-@pytest.mark.parametrize("transport", ["p2p", "bcast"])
+@pytest.mark.parametrize("transport", ["p2p", "bcast", "chunks3", "chunks4"])
 @pytest.mark.parametrize("reduce,act,f", [("mean", "relu", 36), ("sum", "none", 256), ("mean", "relu", 256)])
 def test_overlapped_block_exchange_within_1e5_of_single_graph(world, transport, reduce, act, f):
     """halo_mode='blocks': the rank's rows are summed owner block by owner block (accumulate = 1) in the order the
@@ -169,7 +169,9 @@ def test_overlapped_block_exchange_within_1e5_of_single_graph(world, transport, 
     so, sg = ref.detach().abs().max().item(), xs.grad.abs().max().item()
     for rank, (lo, hi) in enumerate(S.partition_1d(n, world)):
         q = _Blocks([pad(x), pad(go / deg if reduce == "mean" else go)], per, world)
-        pg = S.PartitionedGraph(ei, n, rank=rank, world=world, halo_mode="blocks", halo_transport=transport, blocks=q)
+        kw = dict(halo_mode="chunks", halo_chunks=int(transport[-1])) if transport.startswith("chunks") else \
+            dict(halo_mode="blocks", halo_transport=transport)
+        pg = S.PartitionedGraph(ei, n, rank=rank, world=world, blocks=q, **kw)
         xl = x[lo:hi].clone().requires_grad_(True)
         out = S.aggregate(xl, pg, reduce=reduce, act=act)
         out.backward(go[lo:hi])
@@ -178,7 +180,7 @@ def test_overlapped_block_exchange_within_1e5_of_single_graph(world, transport, 
         assert (xl.grad - xs.grad[lo:hi]).abs().max().item() <= 1e-5 * sg
         # deterministic: the same call again gives the same bits
         q2 = _Blocks([pad(x)], per, world)
-        pg2 = S.PartitionedGraph(ei, n, rank=rank, world=world, halo_mode="blocks", halo_transport=transport, blocks=q2)
+        pg2 = S.PartitionedGraph(ei, n, rank=rank, world=world, blocks=q2, **kw)
         with torch.no_grad():
             out2 = S.aggregate(x[lo:hi].clone(), pg2, reduce=reduce, act=act)
         assert torch.equal(out2, out.detach())

@@ -79,7 +79,7 @@ class _Blocks:
         return [full[b * self.per:(b + 1) * self.per] for b in range(self.world)]
 
 
-@pytest.mark.parametrize("mode", ["gather", "blocks"])
+@pytest.mark.parametrize("mode", ["gather", "blocks", "chunks"])
 @pytest.mark.parametrize("world", [2, 4])
 def test_fused_layer_on_a_partition(mode, world):
     n, e, f, o = 1003, 9000, 64, 96
@@ -106,7 +106,7 @@ def test_fused_layer_on_a_partition(mode, world):
         if mode == "gather":
             pg = S.PartitionedGraph(ei, n, rank=rank, world=world, gather=_Queue([pad(x), g_agg_full]))
         else:
-            pg = S.PartitionedGraph(ei, n, rank=rank, world=world, halo_mode="blocks",
+            pg = S.PartitionedGraph(ei, n, rank=rank, world=world, halo_mode=mode, halo_chunks=3,
                                     blocks=_Blocks([pad(x), g_agg_full], per, world))
         xl = x[lo:hi].clone().requires_grad_(True)
         out = sage.sage_layer(xl, pg, "mean", lin_l, lin_r)

@@ -264,3 +264,67 @@ def test_block_exchange_delivers_every_owner_block_gloo(world, transport):
         p.join(150)
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert dict(ret) == {r: 1 for r in range(world)}
+
+
+def test_chunk_edges_cut_by_row_chunk_and_renumber_into_the_chunk_all_gather():
+    from stemgnn_b200.partition import block_size, chunk_edges, local_edges, partition_1d
+    g = torch.Generator().manual_seed(4)
+    n, e, world, chunks = 53, 900, 4, 3
+    ei = torch.randint(0, n, (2, e), generator=g)
+    per = block_size(n, world)
+    cr = -(-per // chunks)
+    for lo, hi in partition_1d(n, world):
+        for own_row in (1, 0):
+            loc, _ = local_edges(ei, lo, hi, own_row)
+            seen = torch.zeros(loc.size(1), dtype=torch.int64)
+            for c, (sub, pos) in enumerate(chunk_edges(loc, per, world, chunks, 1 - own_row)):
+                assert torch.all(pos[1:] > pos[:-1])
+                assert torch.equal(sub[own_row], loc[own_row, pos])
+                gl = loc[1 - own_row, pos]
+                b, l = gl // per, gl % per
+                assert torch.all(l // cr == c)
+                assert torch.equal(sub[1 - own_row], b * cr + (l - c * cr))        # row in the gather of the c-th chunks
+                assert sub.numel() == 0 or int(sub[1 - own_row].max()) < world * cr
+                seen[pos] += 1
+            assert torch.all(seen == 1)
+
+
+def _chunks_worker(rank, world, port, n, f, chunks, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from stemgnn_b200.partition import PartitionedGraph, block_size, partition_1d
+        g = torch.Generator().manual_seed(7)
+        x = torch.randn(n, f, generator=g)
+        per = block_size(n, world)
+        cr = -(-per // chunks)
+        lo, hi = partition_1d(n, world)[rank]
+        empty = torch.zeros(2, 0, dtype=torch.int64)
+        pg = PartitionedGraph(None, n, rank=rank, world=world, pre_split=(empty, empty), halo_mode="chunks",
+                              halo_chunks=chunks)
+        got = list(pg.exchange_groups(x[lo:hi]))
+        assert [c for c, _ in got] == list(range(chunks)) and pg.n_groups == chunks
+        for c, buf in got:
+            assert buf.shape == (world * cr, f)
+            for b, (blo, bhi) in enumerate(partition_1d(n, world)):
+                want = torch.zeros(chunks * cr, f)
+                want[:bhi - blo] = x[blo:bhi]
+                assert torch.equal(buf[b * cr:(b + 1) * cr], want[c * cr:(c + 1) * cr])
+        ret[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("world,chunks", [(2, 3), (3, 2)])
+def test_chunked_all_gather_delivers_every_row_chunk_gloo(world, chunks):
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = 35500 + (os.getpid() % 2000) + 11 * world + chunks
+    procs = [ctx.Process(target=_chunks_worker, args=(r, world, port, 103, 8, chunks, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(150)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert dict(ret) == {r: 1 for r in range(world)}
