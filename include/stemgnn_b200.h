@@ -37,6 +37,12 @@ const char* stemgnn_last_error(void);
  * stemgnn_aggregate_args; 5: accumulate appended to stemgnn_aggregate_args; 6: row_div appended to
  * stemgnn_linear_args, row_add / row_add_ld appended to stemgnn_aggregate_args. */
 int stemgnn_abi_version(void);
+/* SMs left free by the persistent one-CTA-per-SM kernels (stemgnn_linear, stemgnn_linear_wgrad) from now on;
+ * returns the previous value.  A NCCL collective running beside them (the halo exchange of a partitioned graph,
+ * the all-gather the reference's propagate at model/encoder.py:82 needs once the nodes are split over GPUs) holds a
+ * few dozen SMs whose remaining shared memory cannot take a 200 KB CTA: with a grid of all SMs those CTAs -- and
+ * their statically dealt share of the tiles -- would wait for the collective to END.  Process-wide, 0 by default. */
+int stemgnn_set_sm_reserve(int sms);
 /* number of CUDA kernels this library has launched in this process (all entry points) */
 uint64_t stemgnn_launch_count(void);
 

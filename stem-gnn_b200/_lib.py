@@ -63,6 +63,7 @@ SIGNATURES = {
     "stemgnn_last_error": (C.c_char_p, []),
     "stemgnn_abi_version": (_i32, []),
     "stemgnn_launch_count": (C.c_uint64, []),
+    "stemgnn_set_sm_reserve": (_i32, [_i32]),
     "stemgnn_csr_build_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
     "stemgnn_csr_build": (_i32, [_vp, _i64, _i64, _i32, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
     "stemgnn_csr_build_pair_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),

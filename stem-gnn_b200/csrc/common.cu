@@ -32,6 +32,13 @@ int sm_count() {
     });
     return n;
 }
+static std::atomic<int> g_sm_reserve{0};
+int persistent_sms() {
+    const int n = sm_count() - g_sm_reserve.load(std::memory_order_relaxed);
+    return n < 8 ? 8 : n;
+}
+int set_sm_reserve(int n) { return g_sm_reserve.exchange(n < 0 ? 0 : n, std::memory_order_relaxed); }
+
 bool l2_pingpong() {
     static const bool on = [] { const char* e = getenv("STEMGNN_L2_PINGPONG"); return e ? atoi(e) != 0 : true; }();
     return on;
@@ -40,4 +47,5 @@ bool l2_pingpong() {
 
 extern "C" const char* stemgnn_last_error(void) { return stemgnn::g_err; }
 extern "C" int stemgnn_abi_version(void) { return 6; }
+extern "C" int stemgnn_set_sm_reserve(int sms) { return stemgnn::set_sm_reserve(sms); }
 extern "C" uint64_t stemgnn_launch_count(void) { return stemgnn::launches(); }

@@ -11,6 +11,9 @@ namespace stemgnn {
 
 void set_error(const char* fmt, ...);
 int sm_count();  // cached per process (device of first use)
+// SMs the persistent one-CTA-per-SM kernels (K5, K6: ~200 KB of shared memory and all of TMEM per CTA) size their
+// grids by: sm_count() minus what stemgnn_set_sm_reserve left for a collective running beside them.
+int persistent_sms();
 void count_launch();  // process-wide launch counter behind stemgnn_launch_count()
 // Sweep direction of kernels that read a matrix the previous kernel of the step has just written / read front to
 // back: walking it back to front finds its tail (up to the 126 MB L2's worth) still cached instead of fetching all

@@ -410,7 +410,7 @@ extern "C" int stemgnn_linear(const stemgnn_linear_args* a, void* workspace, siz
     // The 256-row shape is ~6 % faster per tile there, but has half as many work items: when those
     // do not fill whole rounds of the grid the tail eats the gain (M = 43,008, N = 768: 504 items =
     // 3.4 rounds of 148 CTAs -> 557 us against 455 us with 1,008 items of 128 rows).
-    const int sms = sm_count();
+    const int sms = persistent_sms();
     auto fill = [&](int mhh) {
         const int64_t it = ((a->m + 128 * mhh - 1) / (128 * mhh)) * n_tiles;
         const int64_t rounds = (it + sms - 1) / sms;

@@ -437,7 +437,7 @@ int wg_plan(const stemgnn_linear_wgrad_args* a, WgPlan& pl) {
     SG_CHECK_ARG(pl.combos <= wgrad::MAX_COMBOS, "weight matrix too large: more than 64 tiles of 256 x 256");
     // Rows per item: at most SLAB (accuracy), shrunk so that the items fill whole rounds of the grid
     // (169,343 rows: 331 slabs of 512 x 2 tiles = 4.47 rounds of 148 CTAs -> 365 slabs of 464 = 4.93)
-    const int sms = sm_count();
+    const int sms = persistent_sms();
     {
         const int64_t slabs0 = (a->m + wgrad::SLAB - 1) / wgrad::SLAB;
         const int64_t geff = (int64_t)(sms / pl.combos) * pl.combos;      // the grid (see below)

@@ -17,6 +17,7 @@ sums, in the same order, as on one GPU: partitioned results are bit-identical to
 The integer bookkeeping below is plain torch and runs on any device (tests/test_partition_cpu.py
 checks it on CPU with gloo); the kernels are the same C-ABI calls as the single-GPU path.
 """
+import os
 from typing import Callable, List, Optional, Tuple
 
 import torch
@@ -148,6 +149,8 @@ class PartitionedGraph:
             raise ValueError("halo_mode is 'gather', 'blocks' or 'chunks'; halo_transport is 'p2p' or 'bcast'")
         self.halo_mode, self.halo_transport, self._blocks = halo_mode, halo_transport, blocks
         self.halo_chunks = max(1, int(halo_chunks))
+        # SMs the dense kernels leave to NCCL while an exchange is in flight (sage.py); STEMGNN_SM_RESERVE for the A/B
+        self.sm_reserve = int(os.environ.get("STEMGNN_SM_RESERVE", "32"))
 
     def batch_sync(self):
         """Collectives for full-batch BatchNorm over the partition (norm_act.BatchSync), or None when

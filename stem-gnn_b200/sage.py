@@ -21,13 +21,33 @@ import os
 
 import torch
 
-from . import dense, ops
+from . import _lib, dense, ops
 from .partition import PartitionedGraph
 
 # The count division inside the epilogue of g @ W_l (stemgnn_linear row_div) saves the K2a pass (0.058 ms on the
 # arxiv-shaped step) but __fdiv_rn per element makes the GEMM epilogue-bound: 0.543 -> 0.603 ms for the step's four
 # K5 calls (profiles/r02_summary.md) -- a wash, so the separate pass stays the default; =1 switches the epilogue on.
 _ROW_DIV_IN_EPILOGUE = os.environ.get("STEMGNN_ROW_DIV_EPILOGUE", "0") == "1"
+
+
+class _beside_collective:
+    """Dense products launched while a halo exchange is in flight: K5 / K6 are persistent one-CTA-per-SM kernels
+    (~200 KB of shared memory each), and the SMs NCCL's copy CTAs sit on cannot take such a CTA, so with a grid of
+    all SMs a statically dealt share of the tiles would wait for the collective to END (8 B200s: dense 3.5 -> 5.4 ms
+    per step).  Inside this context the grids leave `pg.sm_reserve` SMs (NCCL runs up to 32 channels here) free."""
+
+    def __init__(self, pg):
+        self.n = int(getattr(pg, "sm_reserve", 32)) if (isinstance(pg, PartitionedGraph) and pg.world > 1
+                                                        and pg._blocks is None and pg._gather is None) else 0
+
+    def __enter__(self):
+        if self.n:
+            self.prev = _lib.lib().stemgnn_set_sm_reserve(self.n)
+
+    def __exit__(self, *exc):
+        if self.n:
+            _lib.lib().stemgnn_set_sm_reserve(self.prev)
+        return False
 
 
 class _SageLayer(torch.autograd.Function):
@@ -45,7 +65,8 @@ class _SageLayer(torch.autograd.Function):
             fwd = graph.fwd_csr()
             ex = ops.HaloExchange(graph, x, False)
             if graph.halo_mode != "gather" and graph.world > 1 and w_r is not None:
-                out = dense.linear_raw([x], [w_r], bias)            # while the blocks of x are on the wire
+                with _beside_collective(graph):
+                    out = dense.linear_raw([x], [w_r], bias)        # while the blocks of x are on the wire
             ex.aggregate(agg, fwd.cnt if mean else None, None, ops.ACT_RELU)
         else:
             if x.size(0) != graph.num_nodes:
@@ -83,12 +104,14 @@ class _SageLayer(torch.autograd.Function):
             if part:
                 ex = ops.HaloExchange(graph, g_agg, True)       # on the wire while the products below run
         gws, gb = [None, None], None
-        if need_wl or need_wr or need_b:
-            srcs = [agg, x] if ctx.has_r else [agg]
-            gws, gb = dense.linear_wgrad_raw(g, srcs, want_bias=need_b)
-            gws = list(gws) + [None] * (2 - len(gws))
+        with _beside_collective(graph if ex is not None else None):
+            if need_wl or need_wr or need_b:
+                srcs = [agg, x] if ctx.has_r else [agg]
+                gws, gb = dense.linear_wgrad_raw(g, srcs, want_bias=need_b)
+                gws = list(gws) + [None] * (2 - len(gws))
+            if need_x:
+                g_x = dense.linear_raw([g], [w_r], None, w_transposed=True) if ctx.has_r else torch.empty_like(x)
         if need_x:
-            g_x = dense.linear_raw([g], [w_r], None, w_transposed=True) if ctx.has_r else torch.empty_like(x)
             add = g_x if ctx.has_r else None
             if part:
                 if graph.halo_mode != "gather" and add is not None:
