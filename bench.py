@@ -189,6 +189,27 @@ def build_models(w, device, S):
     return enc, vq, opt
 
 
+class _SumSquares(torch.autograd.Function):
+    """sum(q^2) of the stand-in task loss with a ONE-pass backward.  Written as `q.square().mean()` autograd runs
+    mean -> expand -> div -> pow backward: five passes over the 173 MB matrix, one of them the strided
+    `elementwise_kernel` of the expanded gradient (90 us) -- 0.29 ms of a 3.5 ms step spent on the bench's own
+    loss expression (ncu launch list, round 2).  Same value, same gradient 2 * q * g."""
+
+    @staticmethod
+    def forward(ctx, q):
+        ctx.save_for_backward(q)
+        return torch.linalg.vector_norm(q).square()
+
+    @staticmethod
+    def backward(ctx, g):
+        (q,) = ctx.saved_tensors
+        return torch._foreach_mul([q], g * 2.0)[0]       # tensor x 0-dim tensor through the vectorised list kernel
+
+
+def mean_square(q, denom=None):
+    return _SumSquares.apply(q) / (q.numel() if denom is None else denom)
+
+
 def make_step(enc, vq, opt, S, world):
     import torch.distributed as dist
     params = [p for p in enc.parameters()]
@@ -198,7 +219,7 @@ def make_step(enc, vq, opt, S, world):
         opt.zero_grad(set_to_none=True)
         z = enc(x, ei)
         q, ind, vq_loss, _ = vq(z)
-        loss = q.square().mean() + vq_loss.sum()
+        loss = mean_square(q) + vq_loss.sum()
         loss.backward()
         if world > 1:
             flat = torch.cat([p.grad.reshape(-1) for p in params])
@@ -321,7 +342,7 @@ def cpu_baseline_step_fn(w, threads):
             opt.zero_grad(set_to_none=True)
             z = enc(x, ei)
             q, ind, vq_loss, _ = vq(z)
-            loss = q.square().mean() + vq_loss.sum()
+            loss = mean_square(q) + vq_loss.sum()
             loss.backward()
             opt.step()
             return float(loss.detach())
@@ -342,7 +363,7 @@ def cpu_baseline_step_fn(w, threads):
         z = enc(x, ei)
         q, ind, vq_loss, _ = vq_forward_ref(z, state, training=True, ema_update=True, decay=0.8,
                                             commitment_weight=1.0)
-        loss = q.square().mean() + vq_loss.sum()
+        loss = mean_square(q) + vq_loss.sum()
         loss.backward()
         opt.step()
         return float(loss.detach())
@@ -572,12 +593,19 @@ def run_ours(args, w):
     def finish():
         if world > 1:
             torch.cuda.synchronize()
-            if graph is not None:
-                # tearing NCCL down while a captured graph still holds its collectives hangs
-                # (torch 2.11 / NCCL 2.28): the work is done, leave without the teardown
-                sys.stdout.flush(); sys.stderr.flush()
-                os._exit(0)
-            dist.destroy_process_group()
+            sys.stdout.flush(); sys.stderr.flush()
+            # Tearing NCCL down while a captured graph still holds its collectives hung in round 1 (torch 2.11 /
+            # NCCL 2.28).  The graph is released first and the teardown runs under a 30 s timer: if it still does not
+            # return, the process leaves with the result line already printed instead of hanging the launcher.
+            timer = threading.Timer(30.0, lambda: os._exit(0))
+            timer.daemon = True
+            timer.start()
+            try:
+                if graph is not None:
+                    graph.reset()
+                dist.destroy_process_group()
+            finally:
+                timer.cancel()
 
     if rank != 0:
         finish()
@@ -694,7 +722,7 @@ def measure_partition(w, dev, rank, world, steps, warmup, want_e2e=False):
             opt.zero_grad(set_to_none=True)
             z = enc(x, pg)
             q, ind, vq_loss, _ = vq(z)
-            loss = (q.square().sum() / (n * q.size(1))) + vq_loss.sum() * ((hi - lo) / n)
+            loss = mean_square(q, n * q.size(1)) + vq_loss.sum() * ((hi - lo) / n)
             loss.backward()
             if world > 1:
                 flat = torch.cat([p.grad.reshape(-1) for p in params])

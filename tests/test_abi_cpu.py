@@ -28,6 +28,13 @@ def test_library_exports_every_declared_symbol():
     assert h.stemgnn_abi_version() == _lib.ABI_VERSION
 
 
+def test_sm_reserve_is_a_host_side_setting_that_returns_the_previous_value():
+    h = _lib.lib()
+    assert h.stemgnn_set_sm_reserve(32) == 0
+    assert h.stemgnn_set_sm_reserve(-5) == 32            # negative values clamp to 0
+    assert h.stemgnn_set_sm_reserve(0) == 0
+
+
 def test_argument_errors_are_reported_without_a_gpu():
     import ctypes as C
     h = _lib.lib()
