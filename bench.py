@@ -595,9 +595,13 @@ def run_ours(args, w):
             torch.cuda.synchronize()
             sys.stdout.flush(); sys.stderr.flush()
             # Tearing NCCL down while a captured graph still holds its collectives hung in round 1 (torch 2.11 /
-            # NCCL 2.28).  The graph is released first and the teardown runs under a 30 s timer: if it still does not
+            # NCCL 2.28).  The graph is released first and the teardown runs under a 15 s timer: if it still does not
             # return, the process leaves with the result line already printed instead of hanging the launcher.
-            timer = threading.Timer(30.0, lambda: os._exit(0))
+            def give_up():
+                sys.stderr.write("bench.py: NCCL teardown did not return within 15 s; leaving without it\n")
+                sys.stderr.flush()
+                os._exit(0)
+            timer = threading.Timer(15.0, give_up)
             timer.daemon = True
             timer.start()
             try:
