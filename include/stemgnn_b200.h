@@ -270,6 +270,15 @@ int stemgnn_linear_wgrad(const stemgnn_linear_wgrad_args* args_host, void* works
 int stemgnn_bn_workspace(int64_t rows, int64_t feat, size_t* bytes_host);
 int stemgnn_bn_stats(int64_t rows, int64_t feat, const float* x, int64_t ldx, float* mean, float* var,
                      void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
+/* stemgnn_bn_stats plus what nn.BatchNorm1d does with the statistics of a training batch (F.batch_norm under
+ * model/encoder.py:313), in the tail of the same two launches instead of ten [feat]-sized tensor ops per layer:
+ * invstd = rsqrt(var + eps); when running_mean / running_var are given, running = running * (1 - m) + stat * m with
+ * the unbiased variance var * rows / (rows - 1), m = momentum, or 1 / *num_batches_tracked when momentum < 0 (the
+ * cumulative average of momentum=None; the caller increments the module's device counter first).  Each product and
+ * sum is rounded separately, like the tensor ops. */
+int stemgnn_bn_train_stats(int64_t rows, int64_t feat, const float* x, int64_t ldx, float eps, double momentum,
+                           const int64_t* num_batches_tracked, float* running_mean, float* running_var, float* mean,
+                           float* var, float* invstd, void* workspace, size_t workspace_bytes, stemgnn_stream_t stream);
 /* stemgnn_bn_stats without a caller workspace and without any allocation.  No counterpart in the
  * reference: added for callers that cannot call cudaMalloc (code
  * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, arithmetic

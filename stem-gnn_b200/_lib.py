@@ -80,6 +80,7 @@ SIGNATURES = {
     "stemgnn_linear_wgrad": (_i32, [C.POINTER(LinearWgradArgs), _vp, C.c_size_t, _vp]),
     "stemgnn_bn_workspace": (_i32, [_i64, _i64, C.POINTER(C.c_size_t)]),
     "stemgnn_bn_stats": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "stemgnn_bn_train_stats": (_i32, [_i64, _i64, _vp, _i64, _f32, _f64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp]),
     "stemgnn_bn_stats_static": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _vp]),
     "stemgnn_bn_act_forward": (_i32, [_i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp, _vp, _i64, _vp]),
     "stemgnn_bn_act_backward": (_i32, [_i64, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _i32, _f32, _vp, _i32,

@@ -116,10 +116,22 @@ col_reduce_kernel(const float* __restrict__ x, int64_t ldx, const float* __restr
 // 32 warps per 32 columns: with ~444 block partials a warp sums 14 of them, all 28 loads in flight at once (8
 // warps walked 55 partials each in dependent batches: 14 us per launch, six launches per bench step).
 constexpr int CF_WARPS = 32;
+// What nn.BatchNorm1d does with the batch statistics in training, as the tail of the statistics kernel instead of ten
+// [F]-sized torch kernels per layer: invstd = rsqrt(var + eps); running_mean = running_mean * (1 - m) + mean * m;
+// running_var = running_var * (1 - m) + var * n / (n - 1) * m -- every product and sum rounded separately like the
+// tensor ops they replace; m = momentum, or 1 / num_batches_tracked (cumulative average, momentum None) read from
+// the module's device counter (the caller increments it first).
+struct TrainTail {
+    float* invstd; float eps;
+    float* running_mean; float* running_var;   // NULL: no running statistics
+    float momentum, keep;                      // m and 1 - m (rounded from the double difference); m < 0: cumulative average
+    const int64_t* num_batches_tracked;        // device counter (already incremented by the caller) or NULL
+    float unbias;                              // n / max(n - 1, 1)
+};
 template <int MODE>
 __global__ void __launch_bounds__(CF_WARPS * 32)
 col_final_kernel(const float* __restrict__ part, int blocks, int feat, int64_t rows, const float* __restrict__ x,
-                 float* __restrict__ out0, float* __restrict__ out1) {
+                 float* __restrict__ out0, float* __restrict__ out1, const TrainTail tt) {
     __shared__ float sh[2][CF_WARPS][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
@@ -136,8 +148,20 @@ col_final_kernel(const float* __restrict__ part, int blocks, int feat, int64_t r
         for (int i = 0; i < CF_WARPS; ++i) { s1 += sh[0][i][lane]; s2 += sh[1][i][lane]; }
         if (MODE == 0) {
             const float n = (float)rows, m1 = s1 / n;
-            out0[c] = __ldg(x + c) + m1;
-            out1[c] = fmaxf(s2 / n - m1 * m1, 0.f);
+            const float mean = __ldg(x + c) + m1, var = fmaxf(s2 / n - m1 * m1, 0.f);
+            out0[c] = mean;
+            out1[c] = var;
+            if (tt.invstd) {
+                tt.invstd[c] = rsqrtf(__fadd_rn(var, tt.eps));
+                if (tt.running_mean) {
+                    const bool cma = tt.momentum < 0.f;
+                    const float m = cma ? __fdiv_rn(1.0f, (float)*tt.num_batches_tracked) : tt.momentum;
+                    const float keep = cma ? __fsub_rn(1.0f, m) : tt.keep;
+                    tt.running_mean[c] = __fadd_rn(__fmul_rn(tt.running_mean[c], keep), __fmul_rn(mean, m));
+                    tt.running_var[c] = __fadd_rn(__fmul_rn(tt.running_var[c], keep),
+                                                  __fmul_rn(__fmul_rn(var, tt.unbias), m));
+                }
+            }
         } else {
             out0[c] = s1; out1[c] = s2;
         }
@@ -238,7 +262,30 @@ extern "C" int stemgnn_bn_stats(int64_t rows, int64_t feat, const float* x, int6
     bn::Cols none{nullptr, nullptr, nullptr, nullptr};
     SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
                                                                       none, 0, 0.f, 1.f, nullptr, part, l2_pingpong() ? 1 : 0));
-    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
+    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var, bn::TrainTail{}));
+    SG_CHECK_LAUNCH();
+    return STEMGNN_OK;
+}
+
+extern "C" int stemgnn_bn_train_stats(int64_t rows, int64_t feat, const float* x, int64_t ldx, float eps,
+                                      double momentum, const int64_t* num_batches_tracked, float* running_mean,
+                                      float* running_var, float* mean, float* var, float* invstd, void* workspace,
+                                      size_t workspace_bytes, stemgnn_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (int rc = bn_check(rows, feat, x, ldx)) return rc;
+    SG_CHECK_ARG(rows > 1, "Expected more than 1 value per channel when training");
+    if (feat == 0) return STEMGNN_OK;
+    const BnPlan pl = bn_plan(rows, feat);
+    SG_CHECK_ARG(mean && var && invstd && workspace && workspace_bytes >= pl.bytes, "mean/var/invstd NULL or workspace too small");
+    SG_CHECK_ARG((running_mean == nullptr) == (running_var == nullptr), "running_mean and running_var go together");
+    SG_CHECK_ARG(!(running_mean && momentum < 0.0 && !num_batches_tracked), "cumulative average needs num_batches_tracked");
+    float* part = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
+    bn::Cols none{nullptr, nullptr, nullptr, nullptr};
+    bn::TrainTail tt{invstd, eps, running_mean, running_var, (float)momentum, (float)(1.0 - momentum), num_batches_tracked,
+                     (float)((double)rows / (double)(rows - 1))};
+    SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
+                                                                      none, 0, 0.f, 1.f, nullptr, part, l2_pingpong() ? 1 : 0));
+    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var, tt));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }
@@ -281,7 +328,7 @@ extern "C" int stemgnn_bn_act_backward(int64_t rows, int64_t feat, const float* 
     const float inv_keep = 1.f / (1.f - p);
     SG_LAUNCH(bn::col_reduce_kernel<1><<<pl.blocks, 256, 0, stream>>>(x, ldx, gy, ldg, rows, (int)feat, pl.rows_per_block, cc,
                                                                       relu, p, inv_keep, seed, part, l2_pingpong() ? 1 : 0));
-    SG_LAUNCH(bn::col_final_kernel<1><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, sum_g, sum_gx));
+    SG_LAUNCH(bn::col_final_kernel<1><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, sum_g, sum_gx, bn::TrainTail{}));
     if (gx) {
         SG_CHECK_ARG(ldgx >= feat && ldgx % 4 == 0, "ldgx");
         SG_LAUNCH(bn::apply_kernel<true><<<ew_grid(rows * (feat / 4)), 256, 0, stream>>>(
@@ -362,7 +409,7 @@ extern "C" int stemgnn_bn_stats_static(int64_t rows, int64_t feat, const float* 
     bn::Cols none{nullptr, nullptr, nullptr, nullptr};
     SG_LAUNCH(bn::col_reduce_kernel<0><<<pl.blocks, 256, 0, stream>>>(x, ldx, nullptr, 0, rows, (int)feat, pl.rows_per_block,
                                                                       none, 0, 0.f, 1.f, nullptr, part, l2_pingpong() ? 1 : 0));
-    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var));
+    SG_LAUNCH(bn::col_final_kernel<0><<<(unsigned)((feat + 31) / 32), bn::CF_WARPS * 32, 0, stream>>>(part, pl.blocks, (int)feat, rows, x, mean, var, bn::TrainTail{}));
     SG_CHECK_LAUNCH();
     return STEMGNN_OK;
 }

@@ -63,6 +63,23 @@ def batch_stats(x):
     return mean, var
 
 
+def train_stats(x, eps, momentum, num_batches_tracked, running_mean, running_var):
+    """(mean, biased var, invstd) of a training batch and, in the same launches, nn.BatchNorm1d's running-statistics
+    update (stemgnn_bn_train_stats).  momentum None = cumulative average over `num_batches_tracked` (already
+    incremented by the caller)."""
+    x = _rows16(x)
+    n, f = x.shape
+    mean = torch.empty(f, dtype=torch.float32, device=x.device)
+    var, invstd = torch.empty_like(mean), torch.empty_like(mean)
+    ws = _ws(n, f, x.device)
+    with _lib.traced("bn_stats", n * f * 4, 0, 2):
+        _lib.check(_lib.lib().stemgnn_bn_train_stats(
+            n, f, x.data_ptr(), x.stride(0), float(eps), -1.0 if momentum is None else float(momentum),
+            _lib.ptr(num_batches_tracked), _lib.ptr(running_mean), _lib.ptr(running_var), mean.data_ptr(),
+            var.data_ptr(), invstd.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream()))
+    return mean, var, invstd
+
+
 class BatchSync:
     """Collectives that make the batch statistics those of ALL ranks' rows when one batch (graph) is
     split over several processes (the 1-D partition): `gather(v)` returns every rank's
@@ -162,7 +179,16 @@ def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool, syn
     if use_batch and bn.training and (sync.batch_rows if sync is not None else z.size(0)) <= 1:
         # what nn.BatchNorm1d (the reference's module, model/encoder.py:313) does for a one-row batch
         raise ValueError(f"Expected more than 1 value per channel when training, got input size {tuple(z.shape)}")
-    if use_batch:
+    fused_tail = use_batch and sync is None and bn.training
+    if fused_tail:
+        # statistics, invstd and the running-statistics update in the two launches of the statistics pass
+        with torch.no_grad():
+            track = bn.track_running_stats and bn.running_mean is not None
+            if track:
+                bn.num_batches_tracked.add_(1)
+            mean, var, invstd = train_stats(z.detach(), bn.eps, bn.momentum, bn.num_batches_tracked if track else None,
+                                            bn.running_mean if track else None, bn.running_var if track else None)
+    elif use_batch:
         with torch.no_grad():
             mean, var = synced_batch_stats(z.detach(), sync) if sync is not None else batch_stats(z.detach())
             if bn.training and bn.track_running_stats and bn.running_mean is not None:
@@ -176,8 +202,9 @@ def bn_act_drop(z, bn: nn.BatchNorm1d, relu: bool, p: float, training: bool, syn
                 bn.running_var.mul_(1 - m).add_(var * (n / max(n - 1, 1)) * m)
     else:
         mean, var = bn.running_mean, bn.running_var
-    with torch.no_grad():
-        invstd = torch.rsqrt(var + bn.eps)
+    if not fused_tail:
+        with torch.no_grad():
+            invstd = torch.rsqrt(var + bn.eps)
     gamma = bn.weight if bn.weight is not None else torch.ones(f, device=z.device)
     beta = bn.bias if bn.bias is not None else torch.zeros(f, device=z.device)
     p_eff = float(p) if training else 0.0
