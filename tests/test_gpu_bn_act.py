@@ -159,3 +159,24 @@ def test_one_row_batch_in_training_raises_like_torch():
         S.bn_act_drop(x, bn, relu=True, p=0.0, training=True)
     bn.eval()
     S.bn_act_drop(x, bn, relu=True, p=0.0, training=False)    # running statistics: fine
+
+
+@pytest.mark.parametrize("momentum", [0.1, 0.3, None])
+def test_running_statistics_over_several_batches_follow_torch(momentum):
+    """stemgnn_bn_train_stats: invstd and the running-statistics update (momentum m, or the cumulative average of
+    momentum=None driven by the module's device counter) done by the statistics kernel's tail, three batches in a
+    row, against nn.BatchNorm1d itself."""
+    f = 64
+    g = torch.Generator().manual_seed(9)
+    bn_a = nn.BatchNorm1d(f, momentum=momentum).to(DEV).train()
+    bn_b = copy.deepcopy(bn_a)
+    for step in range(3):
+        x = (torch.randn(500 + 37 * step, f, generator=g) * (1 + step) + step).to(DEV)
+        ya = S.bn_act_drop(x, bn_a, relu=False, p=0.0, training=True)
+        yb = bn_b(x)
+        _close(ya, yb, 1e-5)
+        assert int(bn_a.num_batches_tracked) == int(bn_b.num_batches_tracked) == step + 1
+        _close(bn_a.running_mean, bn_b.running_mean, 1e-6)
+        _close(bn_a.running_var, bn_b.running_var, 1e-6)
+    bn_c = nn.BatchNorm1d(f, track_running_stats=False).to(DEV).train()      # no running statistics at all
+    _close(S.bn_act_drop(x, bn_c, relu=False, p=0.0, training=True), bn_c(x), 1e-5)
