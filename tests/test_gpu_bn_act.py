@@ -176,7 +176,7 @@ def test_running_statistics_over_several_batches_follow_torch(momentum):
         yb = bn_b(x)
         _close(ya, yb, 1e-5)
         assert int(bn_a.num_batches_tracked) == int(bn_b.num_batches_tracked) == step + 1
-        _close(bn_a.running_mean, bn_b.running_mean, 1e-6)
-        _close(bn_a.running_var, bn_b.running_var, 1e-6)
+        _close(bn_a.running_mean, bn_b.running_mean, 1e-5)      # the batch mean itself carries fp32 summation noise
+        _close(bn_a.running_var, bn_b.running_var, 1e-5)
     bn_c = nn.BatchNorm1d(f, track_running_stats=False).to(DEV).train()      # no running statistics at all
     _close(S.bn_act_drop(x, bn_c, relu=False, p=0.0, training=True), bn_c(x), 1e-5)
