@@ -690,6 +690,193 @@ aggregate_hub_ring_kernel(const AggParams a) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Plain mode, one 16-byte chunk per lane (F <= 128): the EDGE-STREAM kernel with shared-memory staging.
+//
+// ncu on the row-per-warp kernel at F = 128 (arxiv-shaped layer 0): 2.0 TB/s of DRAM traffic, L2 hit 49 %, warps
+// active 40 % -- bound by latency x bytes in flight: the gathered rows wait in registers (32 payload registers per
+// thread, 64 in all -> 32 warps per SM, one 7-edge row each, and nothing in flight while a warp fetches rowptr / col).
+// Here a warp owns 8 consecutive rows, i.e. ONE contiguous run of CSR slots, and streams that run in batches of 8
+// edges whatever the row boundaries are: every lane copies its 16-byte column chunk of the 8 source rows with
+// cp.async into a per-warp ring of two 4 KB slots, two batches always in flight, no payload registers (24 warps x
+// 8 KB per SM).  A lane reads back only what it copied itself, so cp.async.wait_group is all the synchronisation
+// there is.  Batches are consumed edge by edge in CSR order; when the edge counter reaches a row's end the row is
+// finished (division, mask, row_add, store) and the next one starts -- the additions of a row are the same, in the
+// same order, as in aggregate_kernel: same bits.  A run that contains a hub row (>= 256 edges, handed to the hub
+// launch) is walked row by row instead.
+constexpr int ES_BATCH = 8;                      // edges per batch
+constexpr int ES_SMEM_BYTES = 64 * 1024;         // per CTA: (8 / CH) warps x 2 slots x 8 edges x CH x 512 B
+
+// CH = 16-byte chunks per lane: 1 (F <= 128, 8 warps per CTA) or 2 (F <= 256, 4 warps per CTA, the same 64 KB)
+template <int CH, bool RELU_MSG, bool MASK_END>
+__global__ void __launch_bounds__(256 / CH, 3)
+aggregate_edge_stream_kernel(const AggParams a) {
+    extern __shared__ float4 es_ring[];
+    constexpr int WPB = 8 / CH;                  // warps per CTA
+    constexpr int SLOT4 = ES_BATCH * CH * 32;    // float4 per slot
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t r0 = ((int64_t)blockIdx.x * WPB + wib) * STREAM_ROWS;
+    if (r0 >= a.n_rows) return;
+    const int nr = (int)(a.n_rows - r0 < STREAM_ROWS ? a.n_rows - r0 : STREAM_ROWS);
+    const int F = a.F;
+    const bool hints = a.hints != 0;
+    const uint64_t pol = policy_evict_first();
+    const int E = (int)a.num_edges;
+    int foff[CH];
+    bool fok[CH];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) { foff[c] = (c * 32 + lane) * 4; fok[c] = foff[c] < F; }
+    float4* ring = es_ring + wib * (2 * SLOT4);
+
+    int rp = 0;
+    if (lane <= nr) rp = ld_stream_i32(a.rowptr + r0 + lane, pol, hints);
+    float cnt_l = 1.f;
+    if (a.row_cnt && lane < nr) cnt_l = __ldg(a.row_cnt + r0 + lane);
+    const int e0 = __shfl_sync(0xffffffffu, rp, 0), e1 = __shfl_sync(0xffffffffu, rp, nr);
+
+    // a hub row in the run: leave it to the hub launch and walk the other rows one by one (rare)
+    bool has_hub = false;
+    if (a.hub != nullptr) {
+        const int nxt = __shfl_down_sync(0xffffffffu, rp, 1);
+        has_hub = __any_sync(0xffffffffu, lane < nr && nxt - rp >= HUB_ROW_EDGES);
+    }
+
+    Vec<4> acc[CH], rx[CH];
+    auto finish_row = [&](int r) {
+        const int64_t row = r0 + r;
+        const float rc = __shfl_sync(0xffffffffu, cnt_l, r);
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+            if (!fok[c]) continue;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float v = acc[c].v[k];
+                if (a.row_cnt) v = __fdiv_rn(v, rc);
+                if (MASK_END) v = rx[c].v[k] > 0.f ? v : 0.f;
+                acc[c].v[k] = v;
+            }
+            if (a.row_add) {
+                Vec<4> ad;
+                ad.load_plain(a.row_add + row * a.row_add_ld + foff[c]);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) acc[c].v[k] = __fadd_rn(acc[c].v[k], ad.v[k]);
+            }
+            st_stream_f4(a.out + row * a.out_ld + foff[c], acc[c].v, pol, hints);
+        }
+    };
+    auto start_row = [&](int r) {
+        const int64_t row = r0 + r;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { acc[c].v[k] = 0.f; rx[c].v[k] = 0.f; }
+            if (a.accumulate && fok[c]) acc[c].load_plain(a.out + row * a.out_ld + foff[c]);
+            if (MASK_END && fok[c]) rx[c].load(a.row_x + row * a.row_x_ld + foff[c]);
+        }
+    };
+
+    if (has_hub) {
+        for (int r = 0; r < nr; ++r) {
+            const int beg = __shfl_sync(0xffffffffu, rp, r), end = __shfl_sync(0xffffffffu, rp, r + 1);
+            if (end - beg >= HUB_ROW_EDGES) {
+                if (lane == 0) {
+                    if (end - beg >= HUB_BIG_EDGES) a.hub[4 + atomicAdd(a.hub, 1)] = (int)(r0 + r);
+                    else a.hub[4 + a.hub_cap - 1 - atomicAdd(a.hub + 1, 1)] = (int)(r0 + r);
+                }
+                continue;
+            }
+            start_row(r);
+            for (int p = beg; p < end; ++p) {
+                const int idx = __ldg(a.col + p);
+#pragma unroll
+                for (int c = 0; c < CH; ++c) {
+                    if (!fok[c]) continue;
+                    Vec<4> g;
+                    g.load(a.gathered + (int64_t)idx * F + foff[c]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        float m = g.v[k];
+                        if (RELU_MSG) m = m > 0.f ? m : 0.f;
+                        acc[c].v[k] = __fadd_rn(acc[c].v[k], m);
+                    }
+                }
+            }
+            finish_row(r);
+        }
+        return;
+    }
+
+    // index window: w0 = col[wb + lane], w1 = col[wb + 32 + lane]
+    int wb = e0 & ~31;
+    int w0 = wb + lane < E ? ld_stream_i32(a.col + wb + lane, pol, hints) : 0;
+    int w1 = wb + 32 + lane < E ? ld_stream_i32(a.col + wb + 32 + lane, pol, hints) : 0;
+    const int nb = (e1 - e0 + ES_BATCH - 1) / ES_BATCH;
+    auto issue = [&](int b) {                    // copies of batch b into slot b & 1 (an empty group past the end)
+        if (b < nb) {
+            const int p0 = e0 + b * ES_BATCH;
+            if (p0 >= wb + 32) {                 // the first block is used up: slide (the new block is needed 3 batches on)
+                w0 = w1;
+                wb += 32;
+                w1 = wb + 32 + lane < E ? ld_stream_i32(a.col + wb + 32 + lane, pol, hints) : 0;
+            }
+            float4* slot = ring + (b & 1) * SLOT4;
+#pragma unroll
+            for (int u = 0; u < ES_BATCH; ++u) {
+                const int i = p0 + u - wb;       // warp-uniform, in [0, 64)
+                const int idx = __shfl_sync(0xffffffffu, i < 32 ? w0 : w1, i & 31);
+                const float* srow = a.gathered + (int64_t)idx * F;
+#pragma unroll
+                for (int c = 0; c < CH; ++c)
+                    if (p0 + u < e1 && fok[c]) cp_async16(slot + (u * CH + c) * 32 + lane, srow + foff[c]);
+            }
+        }
+        cp_async_commit();
+    };
+    issue(0);
+    issue(1);
+    int r = 0;
+    int row_end = __shfl_sync(0xffffffffu, rp, 1);
+    start_row(0);
+    for (int b = 0; b < nb; ++b) {
+        cp_async_wait<1>();                      // this lane's copies of batch b have landed
+        const float4* slot = ring + (b & 1) * SLOT4;
+        const int p0 = e0 + b * ES_BATCH;
+        float4 v[ES_BATCH][CH];
+#pragma unroll
+        for (int u = 0; u < ES_BATCH; ++u)
+#pragma unroll
+            for (int c = 0; c < CH; ++c) v[u][c] = slot[(u * CH + c) * 32 + lane];
+        issue(b + 2);                            // into the slot just read (its copies land hundreds of cycles later)
+#pragma unroll
+        for (int u = 0; u < ES_BATCH; ++u) {
+            const int p = p0 + u;
+            if (p >= e1) break;
+            while (p == row_end) {               // rows that ended (empty ones included)
+                finish_row(r);
+                ++r;
+                row_end = __shfl_sync(0xffffffffu, rp, r + 1);
+                start_row(r);
+            }
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                const float m[4] = {v[u][c].x, v[u][c].y, v[u][c].z, v[u][c].w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float t = m[k];
+                    if (RELU_MSG) t = t > 0.f ? t : 0.f;
+                    acc[c].v[k] = __fadd_rn(acc[c].v[k], t);
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+    for (;;) {                                   // the last row with edges and the empty rows behind it
+        finish_row(r);
+        if (++r >= nr) break;
+        start_row(r);
+    }
+}
+
 // Second launch of an aggregation whose caller lent a hub scratch.  The number of hubs is only known on
 // the device: a fixed grid (two CTAs per SM, fewer when the edge count bounds the work items below that)
 // drains the list, and leaves at once if it is empty.  It is a programmatic dependent launch: the grid's
@@ -765,10 +952,33 @@ static int stream_min_f() {
     return f;
 }
 
+template <int CH, bool BWD, bool RELU>
+static bool launch_edge_stream(const AggParams& p, cudaStream_t s) {
+    static const bool ok = cudaFuncSetAttribute(aggregate_edge_stream_kernel<CH, !BWD && RELU, BWD && RELU>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, ES_SMEM_BYTES) == cudaSuccess;
+    if (!ok) return false;
+    constexpr int ROWS_PER_BLOCK = (8 / CH) * STREAM_ROWS;
+    const unsigned grid = (unsigned)((p.n_rows + ROWS_PER_BLOCK - 1) / ROWS_PER_BLOCK);
+    SG_LAUNCH(aggregate_edge_stream_kernel<CH, !BWD && RELU, BWD && RELU><<<grid, 256 / CH, ES_SMEM_BYTES, s>>>(p));
+    if (p.hub != nullptr) launch_hub<MODE_PLAIN, BWD, RELU>(p, s);
+    return true;
+}
+
+// plain messages: the cp.async edge-stream kernel for 64 < F <= 128 (STEMGNN_AGG_EDGE_STREAM=0 keeps aggregate_kernel)
+// and, with STEMGNN_AGG_EDGE_STREAM=2, for 128 < F <= 256 as well (A/B against aggregate_stream_kernel)
+static int edge_stream_mode() {
+    static const int m = [] { const char* e = getenv("STEMGNN_AGG_EDGE_STREAM"); return e ? atoi(e) : 1; }();
+    return m;
+}
+
 template <int MODE, bool BWD, bool RELU>
 static void dispatch_shape(const AggParams& p, bool vec4, cudaStream_t s) {
     if (!vec4) { launch<1, 32, 8, MODE, BWD, RELU>(p, s); return; }
     if constexpr (MODE == MODE_PLAIN) {
+        if (!(BWD && p.gather_cnt)) {
+            if (edge_stream_mode() >= 1 && p.F > 64 && p.F <= 128 && launch_edge_stream<1, BWD, RELU>(p, s)) return;
+            if (edge_stream_mode() >= 2 && p.F > 128 && p.F <= 256 && launch_edge_stream<2, BWD, RELU>(p, s)) return;
+        }
         if (p.F > stream_min_f() && p.F <= 1024 && !(BWD && p.gather_cnt)) {
             const int ch = (p.F + 127) / 128;
             if (ch <= 1) launch_stream<1, BWD, RELU>(p, s);
